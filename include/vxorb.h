@@ -1,0 +1,221 @@
+/*
+ * vxorb.h — C ABI of the B200-native ORB extract + Hamming match hot path.
+ *
+ * This is the drop-in boundary for VisionX-SLAM's front-end feature path.  Every entry
+ * point is `extern "C"`, takes plain pointers and sizes, returns an int status
+ * (0 = VXORB_OK, negative = error; text via vxorb_last_error) and never throws or aborts.
+ * Host buffers are caller-owned; the library owns every byte of device memory.
+ *
+ * Reference interfaces replaced (paths relative to the reference tree):
+ *   core/feature/feature_extractor.h:10-16   FeatureExtractor::Extract(Frame&)
+ *   core/feature/orb_extractor.cpp:5-7       cv::ORB::create(n_features, scale, levels)
+ *   core/feature/orb_extractor.cpp:13        cv::ORB::detectAndCompute(image, noArray, kps, desc)
+ *   core/feature/feature_matcher.h:7-13      FeatureMatcher::Match(last, curr, matches)
+ *   core/feature/orb_matcher.cpp:22-25       cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, knn, 2)
+ *   core/feature/orb_matcher.cpp:27-36       ratio test  m1.distance < nn_ratio * m2.distance
+ *   core/frontend/tracking.cpp:211-222       caller's post-filter  d <= max(2*min_dist, 30)
+ *
+ * Output order is canonical: keypoints (and descriptor rows) are sorted by
+ * (octave asc, y asc, x asc) in level coordinates; matches by ascending query index.
+ * A handle is not thread-safe; distinct handles (one per GPU / host thread) are independent.
+ */
+#ifndef VXORB_H_
+#define VXORB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VXORB_OK 0
+#define VXORB_E_INVALID (-1)  /* bad argument (null pointer, size out of the handle's limits)   */
+#define VXORB_E_CUDA (-2)     /* CUDA runtime / launch failure; see vxorb_last_error            */
+#define VXORB_E_CAPACITY (-3) /* an output or internal list was too small; counts are still set */
+#define VXORB_E_NOMEM (-4)    /* host or device allocation failed                               */
+
+#define VXORB_DESC_BYTES 32   /* 256-bit rBRIEF descriptor                                      */
+#define VXORB_MAX_LEVELS 16
+
+/* Parameters of one extractor+matcher instance.  Defaults (vxorb_default_params) are the
+ * reference's: ORBExtractor(1000, 1.2f, 8) (orb_extractor.h:11-13), the remaining cv::ORB
+ * defaults (edge 31, patch 31, FAST threshold 20, Harris score, WTA_K 2) and
+ * ORBMatcher::Options{0.8f, 50} (orb_matcher.h:13-16). */
+typedef struct vxorb_params {
+    int n_features;     /* 1000 */
+    float scale_factor; /* 1.2f */
+    int n_levels;       /* 8    */
+    int edge_threshold; /* 31; only 31 is supported (tied to patch_size)                        */
+    int patch_size;     /* 31; only 31 is supported (pattern + umax table are for 31)           */
+    int fast_threshold; /* 20   */
+    float nn_ratio;     /* 0.8f */
+    int min_matches;    /* 50; advisory (the adapter logs a warning below it)                   */
+    int device_id;      /* CUDA device ordinal                                                  */
+    int max_width;      /* largest frame the handle accepts (device buffers are sized for it)   */
+    int max_height;
+    int max_batch;      /* largest number of frames per batched call                            */
+    int max_keypoints;  /* per-frame output capacity; 0 = n_features + n_features/4 + 64        */
+    int max_train;      /* largest train (and query) descriptor count for the match calls       */
+} vxorb_params;
+
+/* One keypoint as cv::ORB reports it (orb_extractor.cpp:19-24 keeps pt and response). */
+typedef struct vxorb_keypoint {
+    float x, y;     /* level-0 pixel coordinates: level position * scale(octave)              */
+    float response; /* Harris response                                                         */
+    float angle;    /* degrees in [0,360)                                                      */
+    int octave;     /* pyramid level                                                           */
+} vxorb_keypoint;
+
+/* One accepted match; mirrors cv::DMatch{queryIdx, trainIdx, imgIdx=0, distance}. */
+typedef struct vxorb_match_t {
+    int query_idx;
+    int train_idx;
+    int distance; /* Hamming distance, 0..256 */
+} vxorb_match_t;
+
+/* Raw 2-NN row; idx = -1 where fewer than two neighbours exist (cv knn row shorter than 2). */
+typedef struct vxorb_knn2_t {
+    int idx[2];
+    int dist[2];
+} vxorb_knn2_t;
+
+/* One FAST corner at level resolution (stage-isolation output). */
+typedef struct vxorb_corner {
+    int x, y, score;
+} vxorb_corner;
+
+typedef struct vxorb_handle vxorb_handle;
+
+void vxorb_default_params(vxorb_params* p);
+int vxorb_create(const vxorb_params* p, vxorb_handle** out);
+void vxorb_destroy(vxorb_handle* h);
+/* Message of the last failing call on this handle (or of the last failed vxorb_create when
+ * h == NULL).  Never NULL. */
+const char* vxorb_last_error(const vxorb_handle* h);
+const char* vxorb_version(void);
+
+/* Geometry helpers (pure host arithmetic, no device work): level sizes, scales and per-level
+ * keypoint quotas exactly as cv::ORB derives them. */
+int vxorb_level_geometry(const vxorb_handle* h, int width, int height, int* level_w, int* level_h,
+                         float* level_scale, int* level_quota);
+
+/* ---- extraction: replaces cv::ORB::detectAndCompute (orb_extractor.cpp:13) ----------------- */
+
+/* One 8-bit gray frame, `stride` bytes per row.  Writes up to kp_cap keypoints and kp_cap*32
+ * descriptor bytes in canonical order; *n_out = number of keypoints found.  If that exceeds
+ * kp_cap or the handle's max_keypoints the call returns VXORB_E_CAPACITY after writing the
+ * first min(...) entries.  Blank / too-small images give *n_out = 0 and VXORB_OK. */
+int vxorb_extract(vxorb_handle* h, const uint8_t* gray, int width, int height, size_t stride,
+                  int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out);
+
+/* Same for a 3-channel BGR frame (system.cpp:46 reads IMREAD_COLOR); the gray conversion
+ * (R*9798 + G*19235 + B*3735 + 2^14) >> 15 is fused into the level-0 load. */
+int vxorb_extract_bgr(vxorb_handle* h, const uint8_t* bgr, int width, int height, size_t stride,
+                      int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out);
+
+/* `batch` independent gray frames of identical size.  frames[i] points at frame i.  Outputs are
+ * frame-major: kp_out[i*kp_cap + k], desc_out[(i*kp_cap + k)*32], n_out[i]. */
+int vxorb_extract_batch(vxorb_handle* h, const uint8_t* const* frames, int batch, int width,
+                        int height, size_t stride, int kp_cap, vxorb_keypoint* kp_out,
+                        uint8_t* desc_out, int* n_out);
+
+/* ---- matching: replaces cv::BFMatcher(NORM_HAMMING).knnMatch(...,2) + ratio --------------- */
+
+/* Raw 2-NN table, one row per query, ties broken by lowest train index. */
+int vxorb_knn2(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt,
+               vxorb_knn2_t* knn_out);
+
+/* ORBMatcher::Match semantics (orb_matcher.cpp:11-43): 2-NN, keep the best iff a second
+ * neighbour exists and d1 < nn_ratio*d2 (float compare, as the reference), ascending query
+ * order.  nn_ratio <= 0 uses the handle's.  Either side empty gives *n_out = 0, VXORB_OK. */
+int vxorb_match(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt,
+                float nn_ratio, int out_cap, vxorb_match_t* out, int* n_out);
+
+/* Windowed variants = cv knnMatch with mask[i][j] = |xq_i - xt_j| <= radius && |yq_i - yt_j|
+ * <= radius (float compares on level-0 coordinates).  xy arrays are interleaved (x,y) floats. */
+int vxorb_knn2_windowed(vxorb_handle* h, const uint8_t* query, const float* query_xy, int nq,
+                        const uint8_t* train, const float* train_xy, int nt, float radius,
+                        vxorb_knn2_t* knn_out);
+int vxorb_match_windowed(vxorb_handle* h, const uint8_t* query, const float* query_xy, int nq,
+                         const uint8_t* train, const float* train_xy, int nt, float radius,
+                         float nn_ratio, int out_cap, vxorb_match_t* out, int* n_out);
+
+/* cv::BFMatcher(NORM_HAMMING, crossCheck=true).match: (i, j) kept iff j is i's nearest train
+ * row and i is j's nearest query row, both with lowest-index tie-break. */
+int vxorb_match_crosscheck(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train,
+                           int nt, int out_cap, vxorb_match_t* out, int* n_out);
+
+/* vxorb_match followed by the caller's post-filter (tracking.cpp:211-222, 292-304, 343-355):
+ * min_dist = min(100, min distance); keep distance <= max(2*min_dist, 30). */
+int vxorb_match_filtered(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train,
+                         int nt, float nn_ratio, int out_cap, vxorb_match_t* out, int* n_out);
+
+/* ---- streaming sequence path (BASELINE config 2): batched extract + frame-to-frame match ---
+ *
+ * A sequence is fed in chunks of `batch` consecutive frames.  Every frame is extracted; frame t
+ * is the train set and frame t-1 the query set of a windowed (radius > 0) or brute-force
+ * (radius <= 0) ratio-tested match, which is ORBMatcher::Match(last, curr) for every
+ * consecutive pair.  The last frame of a chunk stays on the device as the `last` of the next
+ * chunk; vxorb_track_reset forgets it (the first frame after a reset has no matches).
+ *
+ * vxorb_track_submit copies the frames from host memory and queues the work on one of the
+ * handle's pipeline slots; vxorb_track_wait blocks until that slot is done and copies results
+ * to the caller.  Up to vxorb_track_slots(h) submits may be in flight, so copies of one chunk
+ * overlap kernels of another.  Outputs are frame-major with strides kp_cap / match_cap. */
+int vxorb_track_slots(const vxorb_handle* h);
+int vxorb_track_reset(vxorb_handle* h);
+int vxorb_track_submit(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height,
+                       size_t stride, size_t frame_stride, float radius, int* slot_out);
+int vxorb_track_wait(vxorb_handle* h, int slot, int kp_cap, vxorb_keypoint* kp_out,
+                     uint8_t* desc_out, int* n_kp_out, int match_cap, vxorb_match_t* match_out,
+                     int* n_match_out);
+
+/* Device-resident form used to time the kernels alone: frames already uploaded with
+ * vxorb_resident_upload are re-processed by vxorb_resident_run (no host copies); results stay on
+ * the device and can be fetched with vxorb_resident_fetch. */
+int vxorb_resident_upload(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height,
+                          size_t stride, size_t frame_stride);
+int vxorb_resident_run(vxorb_handle* h, float radius);
+int vxorb_resident_fetch(vxorb_handle* h, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out,
+                         int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out);
+
+/* ---- measurement hooks ---------------------------------------------------------------------
+ * CUDA-event timing on the handle's own streams (torch.cuda.Event only sees torch's stream).
+ * vxorb_timer_begin/end bracket a region; stage times are accumulated per kernel family
+ * between vxorb_stage_times_reset and vxorb_stage_times. */
+#define VXORB_STAGE_PYRAMID 0
+#define VXORB_STAGE_FAST 1
+#define VXORB_STAGE_SELECT 2
+#define VXORB_STAGE_BLUR 3
+#define VXORB_STAGE_DESCRIBE 4
+#define VXORB_STAGE_MATCH 5
+#define VXORB_STAGE_COUNT 6
+int vxorb_sync(vxorb_handle* h);
+int vxorb_timer_begin(vxorb_handle* h);
+int vxorb_timer_end(vxorb_handle* h, float* ms_out);
+int vxorb_stage_times_reset(vxorb_handle* h, int enable);
+int vxorb_stage_times(vxorb_handle* h, float* ms_out /* [VXORB_STAGE_COUNT] */,
+                      int* launches_out /* [VXORB_STAGE_COUNT] */);
+/* Number of kernel launches issued by this handle since creation. */
+long long vxorb_launch_count(const vxorb_handle* h);
+/* Writes > L2-size bytes on the handle's stream so the next launch starts from a cold L2. */
+int vxorb_flush_l2(vxorb_handle* h);
+
+/* ---- stage isolation (parity tests only; each runs one kernel family on host buffers) ------ */
+int vxorb_debug_resize(vxorb_handle* h, const uint8_t* src, int sw, int sh, size_t sstride,
+                       uint8_t* dst, int dw, int dh, size_t dstride);
+/* FAST-9/16 + score + strict 3x3 NMS over one image; corners with border <= x < w-border (same
+ * for y), border >= 3, are written in row-major order.  cv::FastFeatureDetector == border 3. */
+int vxorb_debug_fast(vxorb_handle* h, const uint8_t* img, int width, int height, size_t stride,
+                     int threshold, int border, int cap, vxorb_corner* out, int* n_out);
+int vxorb_debug_blur(vxorb_handle* h, const uint8_t* src, int width, int height, size_t stride,
+                     uint8_t* dst, size_t dstride);
+/* Pyramid / blurred-pyramid level of frame `frame` of the most recent extract call. */
+int vxorb_debug_level(vxorb_handle* h, int frame, int level, int blurred, uint8_t* dst,
+                      size_t dstride);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VXORB_H_ */
