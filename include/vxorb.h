@@ -160,16 +160,26 @@ int vxorb_match_filtered(vxorb_handle* h, const uint8_t* query, int nq, const ui
  * chunk; vxorb_track_reset forgets it (the first frame after a reset has no matches).
  *
  * vxorb_track_submit copies the frames from host memory and queues the work on one of the
- * handle's pipeline slots; vxorb_track_wait blocks until that slot is done and copies results
- * to the caller.  Up to vxorb_track_slots(h) submits may be in flight, so copies of one chunk
- * overlap kernels of another.  Outputs are frame-major with strides kp_cap / match_cap. */
+ * handle's pipeline slots (one CUDA stream each); vxorb_track_wait blocks until that slot is
+ * done.  Up to vxorb_track_slots(h) submits may be in flight, so copies of one chunk overlap
+ * kernels of another.  Outputs are frame-major with strides kp_cap / match_cap. */
 int vxorb_track_slots(const vxorb_handle* h);
 int vxorb_track_reset(vxorb_handle* h);
+/* Output pointers are given at submit time (asynchronous I/O style) and must stay valid until the
+ * matching vxorb_track_wait returns; any of them may be NULL to skip that copy.  kp_cap and
+ * match_cap must equal the handle's max_keypoints (vxorb_keypoint_capacity).  n_kp_out[i] is the
+ * true keypoint count of frame i (rows beyond the capacity are dropped and the wait returns
+ * VXORB_E_CAPACITY).  For full copy/compute overlap pass pinned memory (vxorb_host_alloc). */
 int vxorb_track_submit(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height,
-                       size_t stride, size_t frame_stride, float radius, int* slot_out);
-int vxorb_track_wait(vxorb_handle* h, int slot, int kp_cap, vxorb_keypoint* kp_out,
-                     uint8_t* desc_out, int* n_kp_out, int match_cap, vxorb_match_t* match_out,
-                     int* n_match_out);
+                       size_t stride, size_t frame_stride, float radius, int kp_cap,
+                       vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_kp_out, int match_cap,
+                       vxorb_match_t* match_out, int* n_match_out, int* slot_out);
+int vxorb_track_wait(vxorb_handle* h, int slot);
+int vxorb_keypoint_capacity(const vxorb_handle* h);
+
+/* Page-locked host memory for the streaming path (cudaHostAlloc / cudaFreeHost). */
+void* vxorb_host_alloc(size_t bytes);
+void vxorb_host_free(void* p);
 
 /* Device-resident form used to time the kernels alone: frames already uploaded with
  * vxorb_resident_upload are re-processed by vxorb_resident_run (no host copies); results stay on

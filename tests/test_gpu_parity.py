@@ -1,0 +1,352 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the cv2 golden vectors.
+
+Bars (BASELINE.json north_star): FAST keypoint sets, Hamming distances and match indices
+bit-exact; Harris/orientation floats within 1e-4 relative (we assert bit equality and fall back to
+the stated tolerance only in `test_float_tolerance_statement`); descriptors bit-exact.
+Every test here needs a B200 and is marked gpu.
+"""
+import numpy as np
+import pytest
+
+import oracle
+import visionx_slam_b200 as vx
+from conftest import assert_kp_equal, load_golden, matches_as_rows
+from visionx_slam_b200.synth import sha256, synth_scene, synth_sequence
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def h():
+    with vx.VxOrb(max_width=1920, max_height=1088, max_batch=8, max_train=20000) as handle:
+        yield handle
+
+
+def _corners(c):
+    return np.stack([c["x"], c["y"], c["score"]], 1).astype(np.int32).reshape(-1, 3)
+
+
+def _knn_equal(a, b):
+    return np.array_equal(a["idx"], b["idx"]) and np.array_equal(
+        np.where(a["idx"] >= 0, a["dist"], 0), np.where(b["idx"] >= 0, b["dist"], 0))
+
+
+# ---- stage isolation -----------------------------------------------------------------------------
+
+@pytest.mark.parametrize("shape,dst", [((480, 640), (400, 533)), ((231, 309), (193, 257)), ((376, 1241), (313, 1034)),
+                                       ((97, 131), (41, 77)), ((50, 64), (100, 128)), ((33, 7), (33, 5))])
+def test_resize_stage(h, shape, dst):
+    rng = np.random.default_rng(shape[0] * 7 + dst[1])
+    src = rng.integers(0, 256, shape, dtype=np.uint8)
+    got = h.debug_resize(src, dst[1], dst[0])
+    assert np.array_equal(got, oracle.resize_linear_exact(src, dst[1], dst[0]))
+
+
+def test_pyramid_chain_golden(h, golden_c1):
+    g = golden_c1
+    a = g["frame_a"]
+    h.extract(a)
+    for l in range(8):
+        lvl = h.debug_level(0, l, 640, 480)
+        assert sha256(lvl) == str(g[f"a_level{l}_sha"]), f"pyramid level {l}"
+        bl = h.debug_level(0, l, 640, 480, blurred=True)
+        assert sha256(bl) == str(g[f"a_blur{l}_sha"]), f"blurred level {l}"
+
+
+@pytest.mark.parametrize("kind,shape,border,thr", [
+    ("synth", (480, 640), 3, 20), ("synth", (480, 640), 31, 20), ("noise", (240, 320), 3, 20),
+    ("noise", (97, 150), 31, 20), ("noise", (64, 64), 3, 40), ("synth", (134, 179), 3, 7),
+    ("noise", (20, 9), 3, 20), ("noise", (7, 7), 3, 20), ("noise", (70, 200), 3, 1)])
+def test_fast_stage(h, kind, shape, border, thr):
+    rng = np.random.default_rng(shape[0] + shape[1] + border)
+    img = synth_scene(shape[1], shape[0], 4) if kind == "synth" else rng.integers(0, 256, shape, dtype=np.uint8)
+    got = h.debug_fast(img, thr, border)
+    ref = oracle.fast9_nms(img, thr, border)
+    assert np.array_equal(_corners(got), _corners(ref))
+
+
+def test_fast_stage_golden(h, golden_c1):
+    g = golden_c1
+    levels = oracle.pyramid(g["frame_a"])
+    for l in range(8):
+        got = h.debug_fast(levels[l], 20, 3)
+        assert np.array_equal(_corners(got).astype(np.int16), g[f"a_fast{l}"]), f"FAST level {l}"
+
+
+@pytest.mark.parametrize("shape", [(480, 640), (134, 179), (65, 64), (31, 200), (5, 9), (1, 40), (40, 1), (3, 3)])
+def test_blur_stage(h, shape):
+    rng = np.random.default_rng(shape[0] * 3 + shape[1])
+    img = rng.integers(0, 256, shape, dtype=np.uint8)
+    assert np.array_equal(h.debug_blur(img), oracle.blur7(img))
+
+
+# ---- whole extraction ----------------------------------------------------------------------------
+
+def test_extract_c1_golden(h, golden_c1):
+    g = golden_c1
+    for tag in "ab":
+        kp, desc = h.extract(g["frame_" + tag])
+        assert_kp_equal(kp, g["kp_" + tag])
+        assert np.array_equal(desc, g["desc_" + tag])
+        kp2, desc2 = h.extract(g["frame_" + tag])  # idempotence / determinism
+        assert np.array_equal(kp, kp2) and np.array_equal(desc, desc2)
+
+
+@pytest.mark.parametrize("name", ["c3_1241x376.npz", "c4_1920x1080.npz"])
+def test_extract_large_shapes(name):
+    g = load_golden(name)
+    w, hh, n = int(g["w"]), int(g["h"]), int(g["n_features"])
+    img = synth_scene(w, hh, int(g["seed"]))
+    with vx.VxOrb(n_features=n, max_width=1920, max_height=1088) as hx:
+        kp, desc = hx.extract(img)
+    okp, odesc = oracle.orb_extract(img, n)
+    assert_kp_equal(kp, okp)
+    assert np.array_equal(desc, odesc)
+    if sha256(img) == str(g["frame_sha"]):
+        assert_kp_equal(kp, g["kp"])
+        assert np.array_equal(desc, g["desc"])
+
+
+@pytest.mark.parametrize("name", ["grid", "noise", "blank", "tiny60", "small80x70", "lowtex", "odd_357x291"])
+def test_extract_adversarial(h, golden_adv, name):
+    g = golden_adv
+    kp, desc = h.extract(g[name + "_img"])
+    assert_kp_equal(kp, g[name + "_kp"])
+    assert np.array_equal(desc, g[name + "_desc"])
+
+
+@pytest.mark.parametrize("tag", ["p500_4", "p300_s15_5", "p2000_8"])
+def test_extract_other_params(golden_adv, tag):
+    g = golden_adv
+    n, sf, nl = g[tag + "_params"]
+    img = synth_scene(640, 480, int(g["params_img_seed"]))
+    with vx.VxOrb(n_features=int(n), scale_factor=float(sf), n_levels=int(nl)) as hx:
+        kp, desc = hx.extract(img)
+    assert_kp_equal(kp, g[tag + "_kp"])
+    assert np.array_equal(desc, g[tag + "_desc"])
+
+
+def test_extract_bgr(golden_adv):
+    g = golden_adv
+    with vx.VxOrb(n_features=500, max_width=320, max_height=240) as hx:
+        kp, desc = hx.extract(g["bgr_img"])
+    assert_kp_equal(kp, g["bgr_kp"])
+    assert np.array_equal(desc, g["bgr_desc"])
+
+
+def test_extract_strided_input(h):
+    big = synth_scene(700, 500, 12)
+    view = big[10:490, 30:670]  # 480x640 window with a 700-byte row stride
+    kp, desc = h.extract(view)
+    okp, odesc = oracle.orb_extract(np.ascontiguousarray(view))
+    assert_kp_equal(kp, okp)
+    assert np.array_equal(desc, odesc)
+
+
+def test_extract_batch_equals_single(h):
+    frames = [synth_scene(640, 480, s) for s in (31, 32, 33, 34, 35)]
+    outs = h.extract_batch(frames)
+    for f, (kp, desc) in zip(frames, outs):
+        okp, odesc = oracle.orb_extract(f)
+        assert_kp_equal(kp, okp)
+        assert np.array_equal(desc, odesc)
+
+
+def test_extract_many_random_frames(h):
+    """Wider sample: 12 seeds x 2 shapes, oracle comparison."""
+    for seed in range(40, 52):
+        for (w, hh) in ((640, 480), (413, 297)):
+            img = synth_scene(w, hh, seed)
+            kp, desc = h.extract(img)
+            okp, odesc = oracle.orb_extract(img)
+            assert_kp_equal(kp, okp)
+            assert np.array_equal(desc, odesc), f"seed {seed} {w}x{hh}"
+
+
+def test_extract_capacity_error(golden_c1):
+    with vx.VxOrb(max_keypoints=300) as hx:
+        kp, desc, rc, n = hx.extract(golden_c1["frame_a"], return_code=True)
+    assert rc == vx.E_CAPACITY and n == 1000 and len(kp) == 300
+    assert np.array_equal(kp, golden_c1["kp_a"][:300])  # truncated prefix is still canonical order
+    assert np.array_equal(desc, golden_c1["desc_a"][:300])
+
+
+def test_float_tolerance_statement(h, golden_c1):
+    """north_star tolerance: Harris / orientation within 1e-4 relative (we are bit-equal)."""
+    kp, _ = h.extract(golden_c1["frame_a"])
+    ref = golden_c1["kp_a"]
+    np.testing.assert_allclose(kp["response"], ref["response"], rtol=1e-4)
+    np.testing.assert_allclose(kp["angle"], ref["angle"], rtol=1e-4)
+
+
+# ---- matching ------------------------------------------------------------------------------------
+
+def test_match_c1_golden(h, golden_c1):
+    g = golden_c1
+    da, db = g["desc_a"], g["desc_b"]
+    assert _knn_equal(h.knn2(da, db), g["knn"])
+    assert np.array_equal(matches_as_rows(h.match(da, db)), g["matches"])
+    qxy = np.stack([g["kp_a"]["x"], g["kp_a"]["y"]], 1)
+    txy = np.stack([g["kp_b"]["x"], g["kp_b"]["y"]], 1)
+    assert _knn_equal(h.knn2(da, db, qxy, txy, 32.0), g["knn_win32"])
+    assert np.array_equal(matches_as_rows(h.match(da, db, 0.8, qxy, txy, 32.0)), g["matches_win32"])
+    assert np.array_equal(matches_as_rows(h.match_crosscheck(da, db)), g["crosscheck"])
+
+
+@pytest.mark.parametrize("tag", ["ties", "nt1", "nt2", "rand", "dup"])
+def test_match_kat(h, golden_kat, tag):
+    g = golden_kat
+    q, t = g[tag + "_q"], g[tag + "_t"]
+    assert _knn_equal(h.knn2(q, t), g[tag + "_knn"])
+    assert np.array_equal(matches_as_rows(h.match(q, t)), g[tag + "_matches"])
+    assert np.array_equal(matches_as_rows(h.match_crosscheck(q, t)), g[tag + "_crosscheck"])
+
+
+def test_match_windowed_kat(h, golden_kat):
+    g = golden_kat
+    knn = h.knn2(g["dup_q"], g["dup_t"], g["dup_qxy"], g["dup_txy"], 64.0)
+    assert _knn_equal(knn, g["dup_knn_win64"])
+    m = h.match(g["dup_q"], g["dup_t"], 0.8, g["dup_qxy"], g["dup_txy"], 64.0)
+    assert np.array_equal(matches_as_rows(m), g["dup_matches_win64"])
+
+
+def test_match_empty_sides(h):
+    z = np.zeros((0, 32), np.uint8)
+    q = np.zeros((5, 32), np.uint8)
+    assert len(h.match(z, q)) == 0 and len(h.match(q, z)) == 0  # orb_matcher.cpp:18-20
+
+
+@pytest.mark.parametrize("nq,nt", [(1, 1), (1, 300), (129, 257), (1000, 1000), (2000, 2000), (4000, 16384)])
+def test_match_sizes_vs_oracle(h, nq, nt):
+    rng = np.random.default_rng(nq + nt)
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    k = min(nq, nt)
+    q[:k:2] = t[rng.permutation(nt)[:len(q[:k:2])]]  # plant exact and near duplicates
+    q[:k:4, 5] ^= 0x11
+    assert _knn_equal(h.knn2(q, t), oracle.knn2(q, t))
+    for ratio in (0.8, 0.6, 0.95):
+        assert np.array_equal(matches_as_rows(h.match(q, t, ratio)), matches_as_rows(oracle.match(q, t, ratio)))
+    assert np.array_equal(matches_as_rows(h.match_crosscheck(q, t)), matches_as_rows(oracle.match_crosscheck(q, t)))
+    m = oracle.match(q, t, 0.8)
+    assert np.array_equal(matches_as_rows(h.match_filtered(q, t)), matches_as_rows(oracle.postfilter(m)))
+
+
+def test_match_properties_full_size(h):
+    """Size-independent properties at C4 size: self-match, distance = popcount, ordering."""
+    rng = np.random.default_rng(99)
+    t = rng.integers(0, 256, (16384, 32), dtype=np.uint8)
+    q = t[:4000]
+    knn = h.knn2(q, t)
+    assert np.array_equal(knn["idx"][:, 0], np.arange(4000)) and not knn["dist"][:, 0].any()
+    d1 = np.unpackbits(q ^ t[knn["idx"][:, 1]], axis=1).sum(1)
+    assert np.array_equal(d1, knn["dist"][:, 1])
+    m = h.match(q, t, 0.8)
+    assert np.all(np.diff(m["query_idx"]) > 0)
+
+
+# ---- streaming sequence path (BASELINE config 2) -------------------------------------------------
+
+def _oracle_sequence(frames, radius):
+    out = []
+    prev = None
+    for f in frames:
+        kp, desc = oracle.orb_extract(f)
+        if prev is None:
+            m = np.zeros(0, oracle.MATCH_DTYPE)
+        else:
+            pk, pd = prev
+            m = oracle.match(pd, desc, 0.8, np.stack([pk["x"], pk["y"]], 1) if radius > 0 else None,
+                             np.stack([kp["x"], kp["y"]], 1) if radius > 0 else None, radius)
+        out.append((kp, desc, m))
+        prev = (kp, desc)
+    return out
+
+
+@pytest.mark.parametrize("radius", [32.0, 0.0])
+def test_track_sequence_chunks(radius):
+    frames = synth_sequence(640, 480, 11, seed=3)
+    ref = _oracle_sequence(frames, radius)
+    with vx.VxOrb(max_batch=4) as hx:
+        got = []
+        for i in range(0, 11, 4):  # chunks of 4, 4, 3: carry crosses two chunk boundaries and 3 slots
+            got += hx.track(frames[i:i + 4], radius)
+        for i, ((kp, desc, m), (okp, odesc, om)) in enumerate(zip(got, ref)):
+            assert_kp_equal(kp, okp)
+            assert np.array_equal(desc, odesc)
+            assert np.array_equal(matches_as_rows(m), matches_as_rows(om)), f"frame {i}"
+        assert len(got[1][2]) > 200  # the sequence really matches frame to frame
+        hx.track_reset()
+        again = hx.track(frames[4:6], radius)
+        assert len(again[0][2]) == 0  # first frame after a reset has no predecessor
+        assert np.array_equal(matches_as_rows(again[1][2]), matches_as_rows(ref[5][2]))
+
+
+def test_track_pipelined_slots():
+    """Three chunks in flight on the three pipeline slots, pinned buffers, waits in order."""
+    frames = synth_sequence(640, 480, 9, seed=5)
+    ref = _oracle_sequence(frames, 32.0)
+    with vx.VxOrb(max_batch=3) as hx:
+        cap = hx.kp_cap
+        pin_in = vx.PinnedArray((9, 480, 640), np.uint8)
+        pin_in.array[:] = frames
+        outs = []
+        slots = []
+        for c in range(3):
+            o = dict(kp=vx.PinnedArray((3, cap), vx.KEYPOINT_DTYPE), desc=vx.PinnedArray((3, cap, 32), np.uint8),
+                     nk=vx.PinnedArray((3,), np.int32), mt=vx.PinnedArray((3, cap), vx.MATCH_DTYPE),
+                     nm=vx.PinnedArray((3,), np.int32))
+            outs.append(o)
+            slots.append(hx.track_submit(pin_in.array[3 * c:3 * c + 3], 32.0, o["kp"].array, o["desc"].array,
+                                         o["nk"].array, o["mt"].array, o["nm"].array))
+        assert sorted(slots) == [0, 1, 2]
+        for s in slots:
+            hx.track_wait(s)
+        for c in range(3):
+            o = outs[c]
+            for j in range(3):
+                okp, odesc, om = ref[3 * c + j]
+                n, nm = int(o["nk"].array[j]), int(o["nm"].array[j])
+                assert_kp_equal(o["kp"].array[j, :n], okp)
+                assert np.array_equal(o["desc"].array[j, :n], odesc)
+                assert np.array_equal(matches_as_rows(o["mt"].array[j, :nm]), matches_as_rows(om))
+
+
+def test_resident_equals_track():
+    frames = synth_sequence(640, 480, 6, seed=8)
+    with vx.VxOrb(max_batch=6) as hx:
+        t = hx.track(frames, 32.0)
+        hx.resident_upload(frames)
+        hx.resident_run(32.0)
+        r = hx.resident_fetch()
+        for (a, b, c), (d, e, f) in zip(t, r):
+            assert np.array_equal(a, d) and np.array_equal(b, e) and np.array_equal(c, f)
+        hx.resident_run(32.0)  # second run: frame 0 now matches against the carried last frame
+        r2 = hx.resident_fetch()
+        assert len(r2[0][2]) >= 0 and np.array_equal(r2[1][2], r[1][2])
+        st = hx.stage_times()
+        assert hx.launch_count() > 0 and st["fast"][1] > 0
+
+
+# ---- the reference's interface, as the reference's caller uses it --------------------------------
+
+def test_reference_interface_flow(golden_c1):
+    """tracking.cpp:42,208 — Extract(frame) on two frames, then Match(last, curr, matches)."""
+    g = golden_c1
+    extractor = vx.ORBExtractor()      # system.cpp:15
+    matcher = vx.ORBMatcher()          # system.cpp:16
+    last, curr = vx.Frame(0, 0.0, g["frame_a"]), vx.Frame(1, 0.1, g["frame_b"])
+    extractor.Extract(last)
+    extractor.Extract(curr)
+    assert len(last.Features()) == 1000 and last.Descriptors().shape == (1000, 32)
+    f0 = last.Features()[0]
+    assert f0.position == (float(g["kp_a"]["x"][0]), float(g["kp_a"]["y"][0]))
+    assert f0.response == float(g["kp_a"]["response"][0])
+    matches = [None]
+    n = matcher.Match(last, curr, matches)
+    assert n == len(g["matches"]) == len(matches)
+    rows = np.array([(m.queryIdx, m.trainIdx, int(m.distance)) for m in matches], np.int32)
+    assert np.array_equal(rows, g["matches"])
+    blank = vx.Frame(2, 0.2, np.zeros((480, 640), np.uint8))
+    extractor.Extract(blank)
+    assert len(blank.Features()) == 0 and matcher.Match(last, blank, matches) == 0 and matches == []

@@ -1,0 +1,1115 @@
+// api.cu — the C ABI of include/vxorb.h: handle, geometry tables, device workspaces, pipeline
+// slots (one CUDA stream each) and the host-buffer entry points.
+//
+// Boundary replaced (reference tree): FeatureExtractor::Extract (core/feature/feature_extractor.h:15,
+// orb_extractor.cpp:9-27) and FeatureMatcher::Match (core/feature/feature_matcher.h:11-12,
+// orb_matcher.cpp:11-43).  There is no CPU fallback anywhere in this file: every result comes from
+// the kernels in pyramid.cu / fast.cu / select.cu / blur.cu / describe.cu / match.cu, and a failed
+// CUDA call is reported as VXORB_E_CUDA.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "vxorb_internal.h"
+
+using namespace vxorb;
+
+namespace {
+
+constexpr int kSlots = 3;
+std::string g_create_error = "";
+std::mutex g_create_mutex;
+
+struct StageSpan {
+    int stage;
+    cudaEvent_t a, b;
+};
+
+struct Workspace {
+    DeviceBuffers db;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    int batch = 0;          // frames of the chunk in flight / last processed
+    bool in_flight = false;
+    int* h_status = nullptr;  // pinned: status word copied back with every chunk
+};
+
+}  // namespace
+
+struct vxorb_handle {
+    vxorb_params p;
+    int kp_cap = 0;
+    std::string err;
+    // geometry
+    int geo_w = 0, geo_h = 0;
+    LevelTab lt;  // batch field is set per launch
+    uint32_t* d_coef = nullptr;
+    size_t pyr_bytes = 0;
+    Workspace ws[kSlots];
+    int next_slot = 0;
+    int last_slot = -1;  // slot that processed the previous chunk; -1 after reset
+    // last frame of the previous chunk (query side of the next chunk's first pair)
+    uint8_t* carry_desc = nullptr;
+    float* carry_xy = nullptr;
+    int* carry_n = nullptr;
+    // standalone match scratch (host-buffer API)
+    uint8_t *m_q = nullptr, *m_t = nullptr;
+    float *m_qxy = nullptr, *m_txy = nullptr;
+    int* m_n = nullptr;  // [0] = nq, [1] = nt
+    vxorb_knn2_t *m_knn = nullptr, *m_back = nullptr;
+    vxorb_match_t* m_out = nullptr;
+    int* m_out_n = nullptr;
+    int m_cap = 0;
+    // single-image stage scratch
+    uint8_t *s_a = nullptr, *s_b = nullptr;
+    size_t s_bytes = 0;
+    // measurement
+    cudaEvent_t t_begin = nullptr, t_end = nullptr;
+    bool stage_enabled = false;
+    std::vector<StageSpan> spans;
+    std::vector<cudaEvent_t> event_pool;
+    float stage_ms[VXORB_STAGE_COUNT] = {0};
+    int stage_launches[VXORB_STAGE_COUNT] = {0};
+    long long launches = 0;
+    uint8_t* flush_buf = nullptr;
+    size_t flush_bytes = 0;
+};
+
+namespace {
+
+int fail(vxorb_handle* h, int code, const std::string& msg) {
+    if (h) h->err = msg;
+    return code;
+}
+
+#define CK(expr)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (expr);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            return fail(h, e__ == cudaErrorMemoryAllocation ? VXORB_E_NOMEM : VXORB_E_CUDA,        \
+                        std::string(#expr) + ": " + cudaGetErrorString(e__));                      \
+    } while (0)
+
+inline int round_half_even(float v) { return (int)lrintf(v); }
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// cv::ORB level sizes, scales and quotas.
+void level_geometry(const vxorb_params& p, int W, int H, int* lw, int* lh, float* ls, int* quota) {
+    const double sf = (double)p.scale_factor;
+    for (int l = 0; l < p.n_levels; ++l) {
+        const float sc = (float)pow(sf, (double)l);
+        const float inv = 1.0f / sc;
+        ls[l] = sc;
+        lw[l] = round_half_even((float)W * inv);
+        lh[l] = round_half_even((float)H * inv);
+    }
+    const float factor = (float)(1.0 / sf);
+    float nd = (float)p.n_features * (1.0f - factor) / (1.0f - (float)pow((double)factor, (double)p.n_levels));
+    int sum = 0;
+    for (int l = 0; l < p.n_levels - 1; ++l) {
+        quota[l] = round_half_even(nd);
+        sum += quota[l];
+        nd *= factor;
+    }
+    quota[p.n_levels - 1] = std::max(p.n_features - sum, 0);
+}
+
+void free_workspace(Workspace& w) {
+    DeviceBuffers& d = w.db;
+    cudaFree(d.pyr); cudaFree(d.blur); cudaFree(d.cand); cudaFree(d.cand_n); cudaFree(d.resp);
+    cudaFree(d.fin_key); cudaFree(d.fin_resp); cudaFree(d.fin_n); cudaFree(d.kp); cudaFree(d.desc);
+    cudaFree(d.xy); cudaFree(d.kp_n); cudaFree(d.kp_total); cudaFree(d.knn); cudaFree(d.match);
+    cudaFree(d.match_n); cudaFree(d.status);
+    d = DeviceBuffers();
+}
+
+void free_geometry(vxorb_handle* h) {
+    for (auto& w : h->ws) free_workspace(w);
+    cudaFree(h->d_coef);
+    cudaFree(h->carry_desc);
+    cudaFree(h->carry_xy);
+    cudaFree(h->carry_n);
+    h->d_coef = nullptr;
+    h->carry_desc = nullptr;
+    h->carry_xy = nullptr;
+    h->carry_n = nullptr;
+    h->geo_w = h->geo_h = 0;
+}
+
+// (Re)builds the level table and device buffers for w x h frames.  All slots must be idle.
+int ensure_geometry(vxorb_handle* h, int W, int H) {
+    if (W == h->geo_w && H == h->geo_h) return VXORB_OK;
+    if (W < 1 || H < 1 || W > h->p.max_width || H > h->p.max_height || W >= 4096 || H >= 4096)
+        return fail(h, VXORB_E_INVALID, "frame size outside the handle's max_width/max_height (or >= 4096)");
+    for (auto& w : h->ws)
+        if (w.in_flight) return fail(h, VXORB_E_INVALID, "geometry change while a track slot is in flight");
+    CK(cudaDeviceSynchronize());
+    free_geometry(h);
+
+    const vxorb_params& p = h->p;
+    const int B = p.max_batch;
+    LevelTab& lt = h->lt;
+    memset(&lt, 0, sizeof(lt));
+    lt.n_levels = p.n_levels;
+    lt.batch = B;
+    level_geometry(p, W, H, lt.w, lt.h, lt.scale, lt.quota);
+    size_t off = 0, cand_off = 0, fin_off = 0;
+    int coef_off = 0;
+    std::vector<uint32_t> coef;
+    lt.fast_tile_begin[0] = lt.blur_tile_begin[0] = 0;
+    for (int l = 0; l < p.n_levels; ++l) {
+        if (lt.w[l] < 1 || lt.h[l] < 1) {  // pyramid bottoms out: drop the remaining levels
+            lt.n_levels = l;
+            break;
+        }
+        lt.pitch[l] = (int)align_up((size_t)lt.w[l], kPitchAlign);
+        lt.fstride[l] = (unsigned long long)lt.pitch[l] * lt.h[l];
+        lt.off[l] = off;
+        off += align_up((size_t)lt.fstride[l] * B, 256);
+        lt.active[l] = (lt.w[l] > 2 * kEdge && lt.h[l] > 2 * kEdge && lt.quota[l] > 0) ? 1 : 0;
+        const int ew = lt.w[l] - 2 * kEdge, eh = lt.h[l] - 2 * kEdge;  // emission domain
+        lt.cand_cap[l] = lt.active[l] ? ((ew + 1) / 2 + 1) * ((eh + 1) / 2 + 1) : 0;
+        lt.cand_off[l] = cand_off;
+        cand_off += (size_t)lt.cand_cap[l] * B;
+        lt.fin_cap[l] = std::min(lt.cand_cap[l], h->kp_cap);
+        lt.fin_off[l] = fin_off;
+        fin_off += (size_t)lt.fin_cap[l] * B;
+        lt.fast_tiles_x[l] = lt.active[l] ? (ew + 63) / 64 : 0;
+        const int fty = lt.active[l] ? (eh + 31) / 32 : 0;
+        lt.fast_tile_begin[l + 1] = lt.fast_tile_begin[l] + lt.fast_tiles_x[l] * fty;
+        lt.blur_tiles_x[l] = (lt.w[l] + 63) / 64;
+        lt.blur_tile_begin[l + 1] = lt.blur_tile_begin[l] + lt.blur_tiles_x[l] * ((lt.h[l] + 31) / 32);
+        lt.coef_off[l] = coef_off;
+        if (l > 0) {
+            coef.resize((size_t)coef_off + lt.w[l] + lt.h[l]);
+            build_resize_taps(lt.w[l - 1], lt.w[l], coef.data() + coef_off);
+            build_resize_taps(lt.h[l - 1], lt.h[l], coef.data() + coef_off + lt.w[l]);
+            coef_off += lt.w[l] + lt.h[l];
+        }
+    }
+    for (int l = lt.n_levels; l < kMaxLevels; ++l) {
+        lt.fast_tile_begin[l + 1] = lt.fast_tile_begin[lt.n_levels];
+        lt.blur_tile_begin[l + 1] = lt.blur_tile_begin[lt.n_levels];
+    }
+    h->pyr_bytes = off;
+    if (!coef.empty()) {
+        CK(cudaMalloc(&h->d_coef, coef.size() * 4));
+        CK(cudaMemcpy(h->d_coef, coef.data(), coef.size() * 4, cudaMemcpyHostToDevice));
+    }
+    const size_t cap = (size_t)h->kp_cap;
+    CK(cudaMalloc(&h->carry_desc, cap * 32));
+    CK(cudaMalloc(&h->carry_xy, cap * 8));
+    CK(cudaMalloc(&h->carry_n, sizeof(int)));
+    CK(cudaMemset(h->carry_n, 0, sizeof(int)));
+    for (auto& w : h->ws) {
+        DeviceBuffers& d = w.db;
+        d.coef = h->d_coef;
+        CK(cudaMalloc(&d.pyr, std::max<size_t>(off, 256)));
+        CK(cudaMalloc(&d.blur, std::max<size_t>(off, 256)));
+        CK(cudaMemset(d.pyr, 0, std::max<size_t>(off, 256)));
+        CK(cudaMemset(d.blur, 0, std::max<size_t>(off, 256)));
+        CK(cudaMalloc(&d.cand, std::max<size_t>(cand_off, 1) * 4));
+        CK(cudaMalloc(&d.resp, std::max<size_t>(cand_off, 1) * 4));
+        CK(cudaMalloc(&d.fin_key, std::max<size_t>(fin_off, 1) * 4));
+        CK(cudaMalloc(&d.fin_resp, std::max<size_t>(fin_off, 1) * 4));
+        CK(cudaMalloc(&d.cand_n, sizeof(int) * kMaxLevels * B));
+        CK(cudaMalloc(&d.fin_n, sizeof(int) * kMaxLevels * B));
+        CK(cudaMalloc(&d.kp, sizeof(vxorb_keypoint) * cap * (B + 1)));
+        CK(cudaMalloc(&d.desc, 32 * cap * (B + 1)));
+        CK(cudaMalloc(&d.xy, 8 * cap * (B + 1)));
+        CK(cudaMalloc(&d.kp_n, sizeof(int) * (B + 1)));
+        CK(cudaMalloc(&d.kp_total, sizeof(int) * (B + 1)));
+        CK(cudaMemset(d.kp_n, 0, sizeof(int) * (B + 1)));
+        CK(cudaMemset(d.kp_total, 0, sizeof(int) * (B + 1)));
+        CK(cudaMalloc(&d.knn, sizeof(vxorb_knn2_t) * cap * B));
+        CK(cudaMalloc(&d.match, sizeof(vxorb_match_t) * cap * B));
+        CK(cudaMalloc(&d.match_n, sizeof(int) * B));
+        CK(cudaMalloc(&d.status, sizeof(int) * 4));
+        CK(cudaMemset(d.status, 0, sizeof(int) * 4));
+    }
+    h->geo_w = W;
+    h->geo_h = H;
+    h->last_slot = -1;
+    return VXORB_OK;
+}
+
+cudaEvent_t take_event(vxorb_handle* h) {
+    if (!h->event_pool.empty()) {
+        cudaEvent_t e = h->event_pool.back();
+        h->event_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+struct StageScope {
+    vxorb_handle* h;
+    cudaStream_t s;
+    int stage;
+    cudaEvent_t a = nullptr;
+    StageScope(vxorb_handle* h_, cudaStream_t s_, int stage_) : h(h_), s(s_), stage(stage_) {
+        if (h->stage_enabled) {
+            a = take_event(h);
+            cudaEventRecord(a, s);
+        }
+    }
+    void end(int launches) {
+        h->launches += launches;
+        h->stage_launches[stage] += launches;
+        if (h->stage_enabled) {
+            cudaEvent_t b = take_event(h);
+            cudaEventRecord(b, s);
+            h->spans.push_back({stage, a, b});
+        }
+    }
+};
+
+// Queues the extraction kernels for `batch` frames whose level 0 already sits in ws.db.pyr.
+// Outputs go to frame slots 1..batch of kp/desc/xy/kp_n (slot 0 is the streaming carry).
+int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
+    LevelTab lt = h->lt;
+    // Frame strides inside a level plane do not depend on the batch, only the launch extent does.
+    lt.batch = batch;
+    cudaStream_t s = ws.stream;
+    DeviceBuffers d = ws.db;
+    CK(cudaMemsetAsync(d.cand_n, 0, sizeof(int) * kMaxLevels * h->p.max_batch, s));
+    CK(cudaMemsetAsync(d.status, 0, sizeof(int) * 4, s));
+    // cand_n / fin_n are indexed [level * batch + frame] with the launch's batch
+    {
+        StageScope sc(h, s, VXORB_STAGE_PYRAMID);
+        sc.end(launch_pyramid(lt, d, s));
+    }
+    {
+        StageScope sc(h, s, VXORB_STAGE_FAST);
+        sc.end(launch_fast(lt, d, h->p.fast_threshold, kEdge, s));
+    }
+    {
+        StageScope sc(h, s, VXORB_STAGE_SELECT);
+        sc.end(launch_select(lt, d, s));
+    }
+    {
+        StageScope sc(h, s, VXORB_STAGE_BLUR);
+        sc.end(launch_blur(lt, d, s));
+    }
+    {
+        StageScope sc(h, s, VXORB_STAGE_DESCRIBE);
+        DeviceBuffers o = d;  // shift outputs by one frame slot
+        o.kp = d.kp + h->kp_cap;
+        o.desc = d.desc + (size_t)h->kp_cap * 32;
+        o.xy = d.xy + (size_t)h->kp_cap * 2;
+        o.kp_n = d.kp_n + 1;
+        o.kp_total = d.kp_total + 1;
+        sc.end(launch_describe(lt, o, h->kp_cap, s));
+    }
+    CK(cudaGetLastError());
+    return VXORB_OK;
+}
+
+// Queues the frame-to-frame match of slots (p, p+1), p = 0..batch-1.
+int enqueue_track_match(vxorb_handle* h, Workspace& ws, int batch, float radius) {
+    cudaStream_t s = ws.stream;
+    DeviceBuffers& d = ws.db;
+    StageScope sc(h, s, VXORB_STAGE_MATCH);
+    MatchArgs a;
+    a.q_desc = d.desc;
+    a.t_desc = d.desc + (size_t)h->kp_cap * 32;
+    a.q_xy = d.xy;
+    a.t_xy = d.xy + (size_t)h->kp_cap * 2;
+    a.q_n = d.kp_n;
+    a.t_n = d.kp_n + 1;
+    a.q_pair_stride = a.t_pair_stride = h->kp_cap;
+    a.max_q = h->kp_cap;
+    a.pairs = batch;
+    a.radius = radius;
+    a.knn = d.knn;
+    a.knn_stride = h->kp_cap;
+    int n = launch_knn2(a, s);
+    n += launch_match_compact(d.knn, nullptr, h->kp_cap, 0, d.kp_n, batch, h->p.nn_ratio, 0, d.match, h->kp_cap,
+                              d.match_n, s);
+    sc.end(n);
+    CK(cudaGetLastError());
+    return VXORB_OK;
+}
+
+// Copies `batch` host frames into level 0 of the workspace.
+int upload_frames(vxorb_handle* h, Workspace& ws, const uint8_t* frames, int batch, int W, int H, size_t stride,
+                  size_t frame_stride) {
+    const LevelTab& lt = h->lt;
+    uint8_t* dst = ws.db.pyr + lt.off[0];
+    if (frame_stride == stride * (size_t)H) {
+        CK(cudaMemcpy2DAsync(dst, lt.pitch[0], frames, stride, W, (size_t)H * batch, cudaMemcpyHostToDevice,
+                             ws.stream));
+    } else {
+        for (int f = 0; f < batch; ++f)
+            CK(cudaMemcpy2DAsync(dst + (size_t)f * lt.fstride[0], lt.pitch[0], frames + (size_t)f * frame_stride,
+                                 stride, W, H, cudaMemcpyHostToDevice, ws.stream));
+    }
+    return VXORB_OK;
+}
+
+int check_status(vxorb_handle* h, int status) {
+    if (status == 0) return VXORB_OK;
+    char buf[160];
+    snprintf(buf, sizeof(buf),
+             "capacity exceeded (flags 0x%x: 1=candidate list, 2=per-level list, 4=max_keypoints per frame)", status);
+    return fail(h, VXORB_E_CAPACITY, buf);
+}
+
+int ensure_match_scratch(vxorb_handle* h, int rows) {
+    if (rows <= h->m_cap) return VXORB_OK;
+    cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);
+    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n);
+    h->m_cap = 0;
+    const size_t r = (size_t)rows;
+    CK(cudaMalloc(&h->m_q, r * 32));
+    CK(cudaMalloc(&h->m_t, r * 32));
+    CK(cudaMalloc(&h->m_qxy, r * 8));
+    CK(cudaMalloc(&h->m_txy, r * 8));
+    CK(cudaMalloc(&h->m_n, sizeof(int) * 4));
+    CK(cudaMalloc(&h->m_knn, sizeof(vxorb_knn2_t) * r));
+    CK(cudaMalloc(&h->m_back, sizeof(vxorb_knn2_t) * r));
+    CK(cudaMalloc(&h->m_out, sizeof(vxorb_match_t) * r));
+    CK(cudaMalloc(&h->m_out_n, sizeof(int) * 4));
+    h->m_cap = rows;
+    return VXORB_OK;
+}
+
+// Host-buffer knn: uploads both descriptor sets and runs the knn kernel into m_knn (and, for the
+// cross-check, the reverse direction into m_back).
+int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy,
+                 int nt, float radius, bool reverse_too) {
+    if (nq < 0 || nt < 0 || (nq > 0 && !q) || (nt > 0 && !t)) return fail(h, VXORB_E_INVALID, "bad descriptor arguments");
+    if (nq > h->p.max_train || nt > h->p.max_train || nt >= (1 << 20) || nq >= (1 << 20))
+        return fail(h, VXORB_E_INVALID, "descriptor count exceeds max_train");
+    int rc = ensure_match_scratch(h, std::max(std::max(nq, nt), 1));
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    const int n[2] = {nq, nt};
+    CK(cudaMemcpyAsync(h->m_n, n, sizeof(n), cudaMemcpyHostToDevice, s));
+    if (nq) CK(cudaMemcpyAsync(h->m_q, q, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    if (nt) CK(cudaMemcpyAsync(h->m_t, t, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
+    const bool win = radius > 0.f && qxy && txy;
+    if (win) {
+        if (nq) CK(cudaMemcpyAsync(h->m_qxy, qxy, (size_t)nq * 8, cudaMemcpyHostToDevice, s));
+        if (nt) CK(cudaMemcpyAsync(h->m_txy, txy, (size_t)nt * 8, cudaMemcpyHostToDevice, s));
+    }
+    StageScope sc(h, s, VXORB_STAGE_MATCH);
+    MatchArgs a;
+    a.q_desc = h->m_q; a.t_desc = h->m_t;
+    a.q_xy = win ? h->m_qxy : nullptr; a.t_xy = win ? h->m_txy : nullptr;
+    a.q_n = h->m_n; a.t_n = h->m_n + 1;
+    a.q_pair_stride = a.t_pair_stride = 0;
+    a.max_q = nq; a.pairs = 1; a.radius = win ? radius : 0.f;
+    a.knn = h->m_knn; a.knn_stride = 0;
+    int launches = launch_knn2(a, s);
+    if (reverse_too) {
+        MatchArgs b = a;
+        b.q_desc = h->m_t; b.t_desc = h->m_q;
+        b.q_n = h->m_n + 1; b.t_n = h->m_n;
+        b.max_q = nt; b.knn = h->m_back;
+        launches += launch_knn2(b, s);
+    }
+    sc.end(launches);
+    CK(cudaGetLastError());
+    return VXORB_OK;
+}
+
+int run_match_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy,
+                   int nt, float radius, float nn_ratio, int mode, int out_cap, vxorb_match_t* out, int* n_out) {
+    if (!n_out || out_cap < 0 || (out_cap > 0 && !out)) return fail(h, VXORB_E_INVALID, "bad output arguments");
+    *n_out = 0;
+    if (nq <= 0 || nt <= 0) {  // orb_matcher.cpp:18-20: either side empty -> no matches
+        if (nq < 0 || nt < 0) return fail(h, VXORB_E_INVALID, "negative descriptor count");
+        return VXORB_OK;
+    }
+    int rc = run_knn_host(h, q, qxy, nq, t, txy, nt, radius, mode == 2);
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    if (nn_ratio <= 0.f) nn_ratio = h->p.nn_ratio;
+    h->launches += launch_match_compact(h->m_knn, mode == 2 ? h->m_back : nullptr, 0, 0, h->m_n, 1, nn_ratio, mode,
+                                        h->m_out, h->m_cap, h->m_out_n, s);
+    h->stage_launches[VXORB_STAGE_MATCH] += 1;
+    CK(cudaGetLastError());
+    int n = 0;
+    CK(cudaMemcpyAsync(&n, h->m_out_n, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    *n_out = n;
+    const int m = std::min(n, out_cap);
+    if (m > 0) {
+        CK(cudaMemcpyAsync(out, h->m_out, sizeof(vxorb_match_t) * (size_t)m, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+    }
+    if (n > out_cap) return fail(h, VXORB_E_CAPACITY, "match output buffer too small");
+    return VXORB_OK;
+}
+
+int ensure_stage_scratch(vxorb_handle* h, size_t bytes) {
+    if (bytes <= h->s_bytes) return VXORB_OK;
+    cudaFree(h->s_a); cudaFree(h->s_b);
+    h->s_a = h->s_b = nullptr;
+    h->s_bytes = 0;
+    CK(cudaMalloc(&h->s_a, bytes));
+    CK(cudaMalloc(&h->s_b, bytes));
+    h->s_bytes = bytes;
+    return VXORB_OK;
+}
+
+}  // namespace
+
+// ================================================================================================
+extern "C" {
+
+const char* vxorb_version(void) { return "vxorb 0.1 (sm_100a)"; }
+
+void vxorb_default_params(vxorb_params* p) {
+    if (!p) return;
+    p->n_features = 1000;  // orb_extractor.h:11
+    p->scale_factor = 1.2f;
+    p->n_levels = 8;
+    p->edge_threshold = 31;
+    p->patch_size = 31;
+    p->fast_threshold = 20;
+    p->nn_ratio = 0.8f;    // orb_matcher.h:14
+    p->min_matches = 50;   // orb_matcher.h:15
+    p->device_id = 0;
+    p->max_width = 640;
+    p->max_height = 480;
+    p->max_batch = 1;
+    p->max_keypoints = 0;
+    p->max_train = 16384;
+}
+
+const char* vxorb_last_error(const vxorb_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int vxorb_create(const vxorb_params* p, vxorb_handle** out) {
+    std::lock_guard<std::mutex> lock(g_create_mutex);
+    if (!p || !out) {
+        g_create_error = "null argument";
+        return VXORB_E_INVALID;
+    }
+    *out = nullptr;
+    if (p->n_features < 1 || p->n_levels < 1 || p->n_levels > kMaxLevels || !(p->scale_factor > 1.0f) ||
+        p->edge_threshold != 31 || p->patch_size != 31 || p->fast_threshold < 1 || p->fast_threshold > 254 ||
+        p->max_batch < 1 || p->max_width < 1 || p->max_height < 1 || p->max_train < 1) {
+        g_create_error = "unsupported parameters (edge_threshold and patch_size must be 31; scale_factor > 1)";
+        return VXORB_E_INVALID;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                         " — this library has no CPU fallback";
+        return VXORB_E_CUDA;
+    }
+    if (p->device_id < 0 || p->device_id >= ndev) {
+        g_create_error = "device_id out of range";
+        return VXORB_E_INVALID;
+    }
+    vxorb_handle* h = new (std::nothrow) vxorb_handle();
+    if (!h) {
+        g_create_error = "out of host memory";
+        return VXORB_E_NOMEM;
+    }
+    h->p = *p;
+    h->kp_cap = p->max_keypoints > 0 ? p->max_keypoints : p->n_features + p->n_features / 4 + 64;
+    auto bail = [&](cudaError_t err, const char* what) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
+        vxorb_destroy(h);
+        return VXORB_E_CUDA;
+    };
+    if ((e = cudaSetDevice(p->device_id)) != cudaSuccess) return bail(e, "cudaSetDevice");
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, p->device_id)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
+    if (prop.major < 10) {
+        g_create_error = "device is not sm_100 class; this library ships sm_100a code only";
+        vxorb_destroy(h);
+        return VXORB_E_CUDA;
+    }
+    for (auto& w : h->ws) {
+        if ((e = cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "stream");
+        if ((e = cudaEventCreateWithFlags(&w.done, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
+        if ((e = cudaHostAlloc(&w.h_status, sizeof(int) * 4, cudaHostAllocDefault)) != cudaSuccess) return bail(e, "pinned");
+        w.h_status[0] = 0;
+    }
+    if ((e = cudaEventCreate(&h->t_begin)) != cudaSuccess) return bail(e, "event");
+    if ((e = cudaEventCreate(&h->t_end)) != cudaSuccess) return bail(e, "event");
+    if ((e = init_device_tables()) != cudaSuccess) return bail(e, "pattern upload");
+    *out = h;
+    return VXORB_OK;
+}
+
+void vxorb_destroy(vxorb_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->p.device_id);
+    cudaDeviceSynchronize();
+    free_geometry(h);
+    for (auto& w : h->ws) {
+        if (w.stream) cudaStreamDestroy(w.stream);
+        if (w.done) cudaEventDestroy(w.done);
+        if (w.h_status) cudaFreeHost(w.h_status);
+    }
+    cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);
+    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n);
+    cudaFree(h->s_a); cudaFree(h->s_b); cudaFree(h->flush_buf);
+    for (auto& sp : h->spans) {
+        cudaEventDestroy(sp.a);
+        cudaEventDestroy(sp.b);
+    }
+    for (auto e : h->event_pool) cudaEventDestroy(e);
+    if (h->t_begin) cudaEventDestroy(h->t_begin);
+    if (h->t_end) cudaEventDestroy(h->t_end);
+    delete h;
+}
+
+int vxorb_level_geometry(const vxorb_handle* h, int width, int height, int* level_w, int* level_h,
+                         float* level_scale, int* level_quota) {
+    if (!h || width < 1 || height < 1) return VXORB_E_INVALID;
+    int lw[kMaxLevels], lh[kMaxLevels], q[kMaxLevels];
+    float ls[kMaxLevels];
+    level_geometry(h->p, width, height, lw, lh, ls, q);
+    for (int l = 0; l < h->p.n_levels; ++l) {
+        if (level_w) level_w[l] = lw[l];
+        if (level_h) level_h[l] = lh[l];
+        if (level_scale) level_scale[l] = ls[l];
+        if (level_quota) level_quota[l] = q[l];
+    }
+    return VXORB_OK;
+}
+
+// ---- extraction ----------------------------------------------------------------------------------
+
+static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const uint8_t* bgr, int batch, int W, int H,
+                          size_t stride, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (batch < 1 || batch > h->p.max_batch) return fail(h, VXORB_E_INVALID, "batch outside 1..max_batch");
+    if (!n_out || kp_cap < 0 || (kp_cap > 0 && (!kp_out || !desc_out)))
+        return fail(h, VXORB_E_INVALID, "null output pointer");
+    CK(cudaSetDevice(h->p.device_id));
+    int rc = ensure_geometry(h, W, H);
+    if (rc) return rc;
+    Workspace& ws = h->ws[0];
+    if (ws.in_flight) return fail(h, VXORB_E_INVALID, "slot 0 busy with a track submit; wait for it first");
+    const LevelTab& lt = h->lt;
+    uint8_t* l0 = ws.db.pyr + lt.off[0];
+    if (bgr) {
+        if (stride < (size_t)W * 3) return fail(h, VXORB_E_INVALID, "stride smaller than a BGR row");
+        rc = ensure_stage_scratch(h, stride * (size_t)H);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(h->s_a, bgr, stride * (size_t)H, cudaMemcpyHostToDevice, ws.stream));
+        h->launches += launch_gray_from_bgr(h->s_a, stride, 0, l0, W, H, lt.pitch[0], (size_t)lt.fstride[0], 1, ws.stream);
+        h->stage_launches[VXORB_STAGE_PYRAMID] += 1;
+    } else {
+        if (stride < (size_t)W) return fail(h, VXORB_E_INVALID, "stride smaller than a row");
+        for (int f = 0; f < batch; ++f) {
+            if (!frames[f]) return fail(h, VXORB_E_INVALID, "null frame pointer");
+            CK(cudaMemcpy2DAsync(l0 + (size_t)f * lt.fstride[0], lt.pitch[0], frames[f], stride, W, H,
+                                 cudaMemcpyHostToDevice, ws.stream));
+        }
+    }
+    rc = enqueue_extract(h, ws, batch);
+    if (rc) return rc;
+    std::vector<int> counts((size_t)batch * 2 + 4);
+    CK(cudaMemcpyAsync(counts.data(), ws.db.kp_n + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
+    CK(cudaMemcpyAsync(counts.data() + batch, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
+    CK(cudaMemcpyAsync(counts.data() + 2 * batch, ws.db.status, sizeof(int) * 4, cudaMemcpyDeviceToHost, ws.stream));
+    CK(cudaStreamSynchronize(ws.stream));
+    bool truncated = false;
+    for (int f = 0; f < batch; ++f) {
+        const int n = counts[f], total = counts[batch + f];
+        n_out[f] = total;
+        const int m = std::min(n, kp_cap);
+        if (total > m) truncated = true;
+        if (m > 0) {
+            CK(cudaMemcpyAsync(kp_out + (size_t)f * kp_cap, ws.db.kp + (size_t)(f + 1) * h->kp_cap,
+                               sizeof(vxorb_keypoint) * m, cudaMemcpyDeviceToHost, ws.stream));
+            CK(cudaMemcpyAsync(desc_out + (size_t)f * kp_cap * 32, ws.db.desc + (size_t)(f + 1) * h->kp_cap * 32,
+                               (size_t)m * 32, cudaMemcpyDeviceToHost, ws.stream));
+        }
+    }
+    CK(cudaStreamSynchronize(ws.stream));
+    h->last_slot = -1;  // the synchronous extract calls do not take part in a tracked sequence
+    const int status = counts[2 * batch];
+    if (status & 3) return check_status(h, status);
+    if (truncated) return fail(h, VXORB_E_CAPACITY, "more keypoints than kp_cap / max_keypoints; output truncated");
+    return VXORB_OK;
+}
+
+int vxorb_extract(vxorb_handle* h, const uint8_t* gray, int width, int height, size_t stride, int kp_cap,
+                  vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!gray) return fail(h, VXORB_E_INVALID, "null image");
+    return extract_common(h, &gray, nullptr, 1, width, height, stride, kp_cap, kp_out, desc_out, n_out);
+}
+
+int vxorb_extract_bgr(vxorb_handle* h, const uint8_t* bgr, int width, int height, size_t stride, int kp_cap,
+                      vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!bgr) return fail(h, VXORB_E_INVALID, "null image");
+    return extract_common(h, nullptr, bgr, 1, width, height, stride, kp_cap, kp_out, desc_out, n_out);
+}
+
+int vxorb_extract_batch(vxorb_handle* h, const uint8_t* const* frames, int batch, int width, int height,
+                        size_t stride, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!frames) return fail(h, VXORB_E_INVALID, "null frame array");
+    return extract_common(h, frames, nullptr, batch, width, height, stride, kp_cap, kp_out, desc_out, n_out);
+}
+
+// ---- matching ------------------------------------------------------------------------------------
+
+static int knn_common(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, const uint8_t* t,
+                      const float* txy, int nt, float radius, vxorb_knn2_t* knn_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (nq > 0 && !knn_out) return fail(h, VXORB_E_INVALID, "null output");
+    CK(cudaSetDevice(h->p.device_id));
+    if (nq <= 0) return nq < 0 ? fail(h, VXORB_E_INVALID, "negative count") : VXORB_OK;
+    int rc = run_knn_host(h, q, qxy, nq, t, txy, nt, radius, false);
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    CK(cudaMemcpyAsync(knn_out, h->m_knn, sizeof(vxorb_knn2_t) * (size_t)nq, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return VXORB_OK;
+}
+
+int vxorb_knn2(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, vxorb_knn2_t* knn_out) {
+    return knn_common(h, query, nullptr, nq, train, nullptr, nt, 0.f, knn_out);
+}
+
+int vxorb_knn2_windowed(vxorb_handle* h, const uint8_t* query, const float* query_xy, int nq, const uint8_t* train,
+                        const float* train_xy, int nt, float radius, vxorb_knn2_t* knn_out) {
+    if (h && (!query_xy || !train_xy || !(radius > 0.f)))
+        return fail(h, VXORB_E_INVALID, "windowed match needs positions and radius > 0");
+    return knn_common(h, query, query_xy, nq, train, train_xy, nt, radius, knn_out);
+}
+
+int vxorb_match(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, float nn_ratio,
+                int out_cap, vxorb_match_t* out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    return run_match_host(h, query, nullptr, nq, train, nullptr, nt, 0.f, nn_ratio, 0, out_cap, out, n_out);
+}
+
+int vxorb_match_windowed(vxorb_handle* h, const uint8_t* query, const float* query_xy, int nq, const uint8_t* train,
+                         const float* train_xy, int nt, float radius, float nn_ratio, int out_cap,
+                         vxorb_match_t* out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!query_xy || !train_xy || !(radius > 0.f))
+        return fail(h, VXORB_E_INVALID, "windowed match needs positions and radius > 0");
+    CK(cudaSetDevice(h->p.device_id));
+    return run_match_host(h, query, query_xy, nq, train, train_xy, nt, radius, nn_ratio, 0, out_cap, out, n_out);
+}
+
+int vxorb_match_crosscheck(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, int out_cap,
+                           vxorb_match_t* out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    return run_match_host(h, query, nullptr, nq, train, nullptr, nt, 0.f, 1.f, 2, out_cap, out, n_out);
+}
+
+int vxorb_match_filtered(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, float nn_ratio,
+                         int out_cap, vxorb_match_t* out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    return run_match_host(h, query, nullptr, nq, train, nullptr, nt, 0.f, nn_ratio, 1, out_cap, out, n_out);
+}
+
+// ---- streaming sequence path ---------------------------------------------------------------------
+
+int vxorb_track_slots(const vxorb_handle* h) { return h ? kSlots : 0; }
+int vxorb_keypoint_capacity(const vxorb_handle* h) { return h ? h->kp_cap : 0; }
+
+int vxorb_track_reset(vxorb_handle* h) {
+    if (!h) return VXORB_E_INVALID;
+    for (auto& w : h->ws)
+        if (w.in_flight) return fail(h, VXORB_E_INVALID, "reset while a slot is in flight");
+    h->last_slot = -1;
+    return VXORB_OK;
+}
+
+// Carry of the sequence across chunks.  The last frame of every chunk is copied to the handle's
+// carry buffers on the producing stream (before its `done` event); the next chunk, on whatever
+// stream it runs, waits for that event and copies the carry into its own frame slot 0.  Reads and
+// writes of the carry are therefore ordered by stream order + the done events alone, independent
+// of when the caller waits on a slot.
+static int enqueue_carry_in(vxorb_handle* h, Workspace& ws) {
+    cudaStream_t s = ws.stream;
+    const size_t cap = (size_t)h->kp_cap;
+    if (h->last_slot < 0) {
+        CK(cudaMemsetAsync(ws.db.kp_n, 0, sizeof(int), s));
+        return VXORB_OK;
+    }
+    Workspace& prev = h->ws[h->last_slot];
+    if (&prev != &ws) CK(cudaStreamWaitEvent(s, prev.done, 0));
+    CK(cudaMemcpyAsync(ws.db.desc, h->carry_desc, cap * 32, cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemcpyAsync(ws.db.xy, h->carry_xy, cap * 8, cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemcpyAsync(ws.db.kp_n, h->carry_n, sizeof(int), cudaMemcpyDeviceToDevice, s));
+    return VXORB_OK;
+}
+
+static int enqueue_carry_out(vxorb_handle* h, Workspace& ws, int batch) {
+    cudaStream_t s = ws.stream;
+    const size_t cap = (size_t)h->kp_cap;
+    CK(cudaMemcpyAsync(h->carry_desc, ws.db.desc + cap * 32 * batch, cap * 32, cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemcpyAsync(h->carry_xy, ws.db.xy + cap * 2 * batch, cap * 8, cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemcpyAsync(h->carry_n, ws.db.kp_n + batch, sizeof(int), cudaMemcpyDeviceToDevice, s));
+    return VXORB_OK;
+}
+
+int vxorb_track_submit(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height, size_t stride,
+                       size_t frame_stride, float radius, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out,
+                       int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out, int* slot_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!frames || !slot_out) return fail(h, VXORB_E_INVALID, "null argument");
+    if (batch < 1 || batch > h->p.max_batch) return fail(h, VXORB_E_INVALID, "batch outside 1..max_batch");
+    if (stride < (size_t)width) return fail(h, VXORB_E_INVALID, "stride smaller than a row");
+    if ((kp_out || desc_out) && kp_cap != h->kp_cap)
+        return fail(h, VXORB_E_INVALID, "track outputs must use kp_cap == the handle's max_keypoints");
+    if (match_out && match_cap != h->kp_cap)
+        return fail(h, VXORB_E_INVALID, "track outputs must use match_cap == the handle's max_keypoints");
+    CK(cudaSetDevice(h->p.device_id));
+    int rc = ensure_geometry(h, width, height);
+    if (rc) return rc;
+    const int slot = h->next_slot;
+    Workspace& ws = h->ws[slot];
+    if (ws.in_flight) return fail(h, VXORB_E_INVALID, "all pipeline slots in flight; call vxorb_track_wait first");
+    cudaStream_t s = ws.stream;
+    rc = upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
+    if (rc) return rc;
+    rc = enqueue_extract(h, ws, batch);
+    if (rc) return rc;
+    rc = enqueue_carry_in(h, ws);
+    if (rc) return rc;
+    rc = enqueue_track_match(h, ws, batch, radius);
+    if (rc) return rc;
+    rc = enqueue_carry_out(h, ws, batch);
+    if (rc) return rc;
+    CK(cudaEventRecord(ws.done, s));  // descriptors, matches and the carry of this chunk are final
+    const size_t cap = (size_t)h->kp_cap;
+    if (kp_out) CK(cudaMemcpyAsync(kp_out, ws.db.kp + cap, sizeof(vxorb_keypoint) * cap * batch, cudaMemcpyDeviceToHost, s));
+    if (desc_out) CK(cudaMemcpyAsync(desc_out, ws.db.desc + cap * 32, 32 * cap * batch, cudaMemcpyDeviceToHost, s));
+    if (n_kp_out) CK(cudaMemcpyAsync(n_kp_out, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+    if (match_out) CK(cudaMemcpyAsync(match_out, ws.db.match, sizeof(vxorb_match_t) * cap * batch, cudaMemcpyDeviceToHost, s));
+    if (n_match_out) CK(cudaMemcpyAsync(n_match_out, ws.db.match_n, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(ws.h_status, ws.db.status, sizeof(int) * 4, cudaMemcpyDeviceToHost, s));
+    ws.batch = batch;
+    ws.in_flight = true;
+    h->last_slot = slot;
+    h->next_slot = (slot + 1) % kSlots;
+    *slot_out = slot;
+    return VXORB_OK;
+}
+
+int vxorb_track_wait(vxorb_handle* h, int slot) {
+    if (!h) return VXORB_E_INVALID;
+    if (slot < 0 || slot >= kSlots) return fail(h, VXORB_E_INVALID, "bad slot");
+    Workspace& ws = h->ws[slot];
+    if (!ws.in_flight) return fail(h, VXORB_E_INVALID, "slot not in flight");
+    CK(cudaSetDevice(h->p.device_id));
+    CK(cudaStreamSynchronize(ws.stream));
+    ws.in_flight = false;
+    return check_status(h, ws.h_status[0]);
+}
+
+int vxorb_resident_upload(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height, size_t stride,
+                          size_t frame_stride) {
+    if (!h) return VXORB_E_INVALID;
+    if (!frames) return fail(h, VXORB_E_INVALID, "null frames");
+    if (batch < 1 || batch > h->p.max_batch) return fail(h, VXORB_E_INVALID, "batch outside 1..max_batch");
+    CK(cudaSetDevice(h->p.device_id));
+    int rc = ensure_geometry(h, width, height);
+    if (rc) return rc;
+    Workspace& ws = h->ws[0];
+    if (ws.in_flight) return fail(h, VXORB_E_INVALID, "slot 0 in flight");
+    rc = upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
+    if (rc) return rc;
+    CK(cudaMemsetAsync(ws.db.kp_n, 0, sizeof(int), ws.stream));
+    CK(cudaStreamSynchronize(ws.stream));
+    ws.batch = batch;
+    h->last_slot = -1;
+    return VXORB_OK;
+}
+
+int vxorb_resident_run(vxorb_handle* h, float radius) {
+    if (!h) return VXORB_E_INVALID;
+    Workspace& ws = h->ws[0];
+    if (ws.batch < 1 || h->geo_w == 0) return fail(h, VXORB_E_INVALID, "no resident frames; call vxorb_resident_upload");
+    CK(cudaSetDevice(h->p.device_id));
+    int rc = enqueue_extract(h, ws, ws.batch);
+    if (rc) return rc;
+    rc = enqueue_track_match(h, ws, ws.batch, radius);
+    if (rc) return rc;
+    // the chunk's last frame becomes the carry of the next run, as in the streaming path
+    const size_t cap = (size_t)h->kp_cap;
+    CK(cudaMemcpyAsync(ws.db.desc, ws.db.desc + cap * 32 * ws.batch, cap * 32, cudaMemcpyDeviceToDevice, ws.stream));
+    CK(cudaMemcpyAsync(ws.db.xy, ws.db.xy + cap * 2 * ws.batch, cap * 8, cudaMemcpyDeviceToDevice, ws.stream));
+    CK(cudaMemcpyAsync(ws.db.kp_n, ws.db.kp_n + ws.batch, sizeof(int), cudaMemcpyDeviceToDevice, ws.stream));
+    return VXORB_OK;
+}
+
+int vxorb_resident_fetch(vxorb_handle* h, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_kp_out,
+                         int match_cap, vxorb_match_t* match_out, int* n_match_out) {
+    if (!h) return VXORB_E_INVALID;
+    Workspace& ws = h->ws[0];
+    if (ws.batch < 1) return fail(h, VXORB_E_INVALID, "no resident frames");
+    if ((kp_out || desc_out) && kp_cap != h->kp_cap) return fail(h, VXORB_E_INVALID, "kp_cap must equal max_keypoints");
+    if (match_out && match_cap != h->kp_cap) return fail(h, VXORB_E_INVALID, "match_cap must equal max_keypoints");
+    CK(cudaSetDevice(h->p.device_id));
+    cudaStream_t s = ws.stream;
+    const size_t cap = (size_t)h->kp_cap;
+    const int batch = ws.batch;
+    int status[4] = {0, 0, 0, 0};
+    if (kp_out) CK(cudaMemcpyAsync(kp_out, ws.db.kp + cap, sizeof(vxorb_keypoint) * cap * batch, cudaMemcpyDeviceToHost, s));
+    if (desc_out) CK(cudaMemcpyAsync(desc_out, ws.db.desc + cap * 32, 32 * cap * batch, cudaMemcpyDeviceToHost, s));
+    if (n_kp_out) CK(cudaMemcpyAsync(n_kp_out, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+    if (match_out) CK(cudaMemcpyAsync(match_out, ws.db.match, sizeof(vxorb_match_t) * cap * batch, cudaMemcpyDeviceToHost, s));
+    if (n_match_out) CK(cudaMemcpyAsync(n_match_out, ws.db.match_n, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(status, ws.db.status, sizeof(status), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return check_status(h, status[0]);
+}
+
+// ---- pinned host memory --------------------------------------------------------------------------
+
+void* vxorb_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+    return p;
+}
+
+void vxorb_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+// ---- measurement ---------------------------------------------------------------------------------
+
+int vxorb_sync(vxorb_handle* h) {
+    if (!h) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    for (auto& w : h->ws) CK(cudaStreamSynchronize(w.stream));
+    return VXORB_OK;
+}
+
+// Joins every slot stream into slot 0's stream and records there.
+static int record_joined(vxorb_handle* h, cudaEvent_t ev) {
+    cudaStream_t s0 = h->ws[0].stream;
+    for (int i = 1; i < kSlots; ++i) {
+        cudaEvent_t e = take_event(h);
+        CK(cudaEventRecord(e, h->ws[i].stream));
+        CK(cudaStreamWaitEvent(s0, e, 0));
+        h->event_pool.push_back(e);  // safe: the wait has been enqueued
+    }
+    CK(cudaEventRecord(ev, s0));
+    return VXORB_OK;
+}
+
+int vxorb_timer_begin(vxorb_handle* h) {
+    if (!h) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    int rc = record_joined(h, h->t_begin);
+    if (rc) return rc;
+    // later work on the other slots must not start before the begin mark
+    for (int i = 1; i < kSlots; ++i) CK(cudaStreamWaitEvent(h->ws[i].stream, h->t_begin, 0));
+    return VXORB_OK;
+}
+
+int vxorb_timer_end(vxorb_handle* h, float* ms_out) {
+    if (!h || !ms_out) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    int rc = record_joined(h, h->t_end);
+    if (rc) return rc;
+    CK(cudaEventSynchronize(h->t_end));
+    CK(cudaEventElapsedTime(ms_out, h->t_begin, h->t_end));
+    return VXORB_OK;
+}
+
+int vxorb_stage_times_reset(vxorb_handle* h, int enable) {
+    if (!h) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    int rc = vxorb_sync(h);
+    if (rc) return rc;
+    for (auto& sp : h->spans) {
+        h->event_pool.push_back(sp.a);
+        h->event_pool.push_back(sp.b);
+    }
+    h->spans.clear();
+    for (int i = 0; i < VXORB_STAGE_COUNT; ++i) {
+        h->stage_ms[i] = 0.f;
+        h->stage_launches[i] = 0;
+    }
+    h->stage_enabled = enable != 0;
+    return VXORB_OK;
+}
+
+int vxorb_stage_times(vxorb_handle* h, float* ms_out, int* launches_out) {
+    if (!h) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    int rc = vxorb_sync(h);
+    if (rc) return rc;
+    for (auto& sp : h->spans) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, sp.a, sp.b));
+        h->stage_ms[sp.stage] += ms;
+        h->event_pool.push_back(sp.a);
+        h->event_pool.push_back(sp.b);
+    }
+    h->spans.clear();
+    for (int i = 0; i < VXORB_STAGE_COUNT; ++i) {
+        if (ms_out) ms_out[i] = h->stage_ms[i];
+        if (launches_out) launches_out[i] = h->stage_launches[i];
+    }
+    return VXORB_OK;
+}
+
+long long vxorb_launch_count(const vxorb_handle* h) { return h ? h->launches : 0; }
+
+int vxorb_flush_l2(vxorb_handle* h) {
+    if (!h) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    if (!h->flush_buf) {
+        h->flush_bytes = (size_t)256 << 20;  // 2x the 126 MB L2
+        CK(cudaMalloc(&h->flush_buf, h->flush_bytes));
+    }
+    h->launches += launch_flush(h->flush_buf, h->flush_bytes, h->ws[0].stream);
+    CK(cudaGetLastError());
+    return VXORB_OK;
+}
+
+// ---- stage isolation -----------------------------------------------------------------------------
+
+int vxorb_debug_resize(vxorb_handle* h, const uint8_t* src, int sw, int sh, size_t sstride, uint8_t* dst, int dw,
+                       int dh, size_t dstride) {
+    if (!h) return VXORB_E_INVALID;
+    if (!src || !dst || sw < 1 || sh < 1 || dw < 1 || dh < 1 || sw >= 65536 || sh >= 65536)
+        return fail(h, VXORB_E_INVALID, "bad resize arguments");
+    CK(cudaSetDevice(h->p.device_id));
+    const int sp = (int)align_up((size_t)sw, kPitchAlign), dp = (int)align_up((size_t)dw, kPitchAlign);
+    int rc = ensure_stage_scratch(h, std::max((size_t)sp * sh, (size_t)dp * dh) + (size_t)(dw + dh) * 4 + 256);
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    std::vector<uint32_t> taps((size_t)dw + dh);
+    build_resize_taps(sw, dw, taps.data());
+    build_resize_taps(sh, dh, taps.data() + dw);
+    uint32_t* d_taps = reinterpret_cast<uint32_t*>(h->s_b + align_up((size_t)dp * dh, 256));
+    CK(cudaMemcpy2DAsync(h->s_a, sp, src, sstride, sw, sh, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_taps, taps.data(), taps.size() * 4, cudaMemcpyHostToDevice, s));
+    h->launches += launch_resize_single(h->s_a, sw, sh, sp, h->s_b, dw, dh, dp, d_taps, d_taps + dw, s);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy2DAsync(dst, dstride, h->s_b, dp, dw, dh, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return VXORB_OK;
+}
+
+// FAST / blur stage tests run a one-level, one-frame LevelTab through the production kernels.
+static int single_level_tab(vxorb_handle* h, int W, int H, int border, LevelTab* out, DeviceBuffers* db, size_t* cand_cap) {
+    LevelTab lt;
+    memset(&lt, 0, sizeof(lt));
+    lt.n_levels = 1;
+    lt.batch = 1;
+    lt.w[0] = W;
+    lt.h[0] = H;
+    lt.pitch[0] = (int)align_up((size_t)W, kPitchAlign);
+    lt.fstride[0] = (unsigned long long)lt.pitch[0] * H;
+    lt.scale[0] = 1.f;
+    const int ew = W - 2 * border, eh = H - 2 * border;
+    lt.active[0] = (ew > 0 && eh > 0) ? 1 : 0;
+    lt.cand_cap[0] = lt.active[0] ? ((ew + 1) / 2 + 1) * ((eh + 1) / 2 + 1) : 0;
+    lt.fast_tiles_x[0] = lt.active[0] ? (ew + 63) / 64 : 0;
+    lt.fast_tile_begin[1] = lt.active[0] ? lt.fast_tiles_x[0] * ((eh + 31) / 32) : 0;
+    lt.blur_tiles_x[0] = (W + 63) / 64;
+    lt.blur_tile_begin[1] = lt.blur_tiles_x[0] * ((H + 31) / 32);
+    for (int l = 1; l < kMaxLevels; ++l) {
+        lt.fast_tile_begin[l + 1] = lt.fast_tile_begin[1];
+        lt.blur_tile_begin[l + 1] = lt.blur_tile_begin[1];
+    }
+    const size_t img = align_up((size_t)lt.fstride[0], 256);
+    const size_t need = img + (size_t)lt.cand_cap[0] * 4 + 256;
+    int rc = ensure_stage_scratch(h, need);
+    if (rc) return rc;
+    *db = DeviceBuffers();
+    db->pyr = h->s_a;
+    db->blur = h->s_b;
+    db->cand = reinterpret_cast<uint32_t*>(h->s_b + img);  // FAST test: candidates behind the (unused) blur plane
+    db->cand_n = reinterpret_cast<int*>(h->s_a + img);
+    *cand_cap = (size_t)lt.cand_cap[0];
+    *out = lt;
+    return VXORB_OK;
+}
+
+int vxorb_debug_fast(vxorb_handle* h, const uint8_t* img, int width, int height, size_t stride, int threshold,
+                     int border, int cap, vxorb_corner* out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!img || !n_out || width < 1 || height < 1 || width >= 4096 || height >= 4096 || border < 3 || threshold < 1 ||
+        threshold > 254 || cap < 0 || (cap > 0 && !out))
+        return fail(h, VXORB_E_INVALID, "bad FAST arguments");
+    CK(cudaSetDevice(h->p.device_id));
+    *n_out = 0;
+    LevelTab lt;
+    DeviceBuffers db;
+    size_t ccap = 0;
+    int rc = single_level_tab(h, width, height, border, &lt, &db, &ccap);
+    if (rc) return rc;
+    if (!lt.active[0]) return VXORB_OK;
+    cudaStream_t s = h->ws[0].stream;
+    CK(cudaMemsetAsync(h->s_a, 0, h->s_bytes, s));
+    CK(cudaMemcpy2DAsync(db.pyr, lt.pitch[0], img, stride, width, height, cudaMemcpyHostToDevice, s));
+    h->launches += launch_fast(lt, db, threshold, border, s);
+    CK(cudaGetLastError());
+    int n = 0;
+    CK(cudaMemcpyAsync(&n, db.cand_n, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    if ((size_t)n > ccap) return fail(h, VXORB_E_CAPACITY, "candidate list overflow");
+    std::vector<uint32_t> packed((size_t)n);
+    if (n) {
+        CK(cudaMemcpyAsync(packed.data(), db.cand, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+    }
+    // the kernel emits per tile; present in row-major order like cv::FastFeatureDetector
+    std::sort(packed.begin(), packed.end(), [](uint32_t a, uint32_t b) { return (a & 0xffffffu) < (b & 0xffffffu); });
+    *n_out = n;
+    for (int i = 0; i < n && i < cap; ++i) {
+        out[i].x = (int)(packed[i] & 0xfffu);
+        out[i].y = (int)((packed[i] >> 12) & 0xfffu);
+        out[i].score = (int)(packed[i] >> 24);
+    }
+    return n > cap ? fail(h, VXORB_E_CAPACITY, "corner output buffer too small") : VXORB_OK;
+}
+
+int vxorb_debug_blur(vxorb_handle* h, const uint8_t* src, int width, int height, size_t stride, uint8_t* dst,
+                     size_t dstride) {
+    if (!h) return VXORB_E_INVALID;
+    if (!src || !dst || width < 1 || height < 1 || width >= 65536 || height >= 65536)
+        return fail(h, VXORB_E_INVALID, "bad blur arguments");
+    CK(cudaSetDevice(h->p.device_id));
+    LevelTab lt;
+    DeviceBuffers db;
+    size_t ccap = 0;
+    int rc = single_level_tab(h, width, height, 3, &lt, &db, &ccap);
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    CK(cudaMemcpy2DAsync(db.pyr, lt.pitch[0], src, stride, width, height, cudaMemcpyHostToDevice, s));
+    h->launches += launch_blur(lt, db, s);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy2DAsync(dst, dstride, db.blur, lt.pitch[0], width, height, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return VXORB_OK;
+}
+
+int vxorb_debug_level(vxorb_handle* h, int frame, int level, int blurred, uint8_t* dst, size_t dstride) {
+    if (!h) return VXORB_E_INVALID;
+    if (h->geo_w == 0 || !dst || level < 0 || level >= h->lt.n_levels || frame < 0 || frame >= h->p.max_batch)
+        return fail(h, VXORB_E_INVALID, "bad level query");
+    CK(cudaSetDevice(h->p.device_id));
+    const LevelTab& lt = h->lt;
+    const uint8_t* base = (blurred ? h->ws[0].db.blur : h->ws[0].db.pyr) + lt.off[level] + (size_t)frame * lt.fstride[level];
+    CK(cudaMemcpy2D(dst, dstride, base, lt.pitch[level], lt.w[level], lt.h[level], cudaMemcpyDeviceToHost));
+    return VXORB_OK;
+}
+
+}  // extern "C"

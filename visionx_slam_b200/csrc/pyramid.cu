@@ -1,0 +1,131 @@
+// pyramid.cu — gray conversion and the chained fixed-point pyramid.
+//
+// Replaces, for orb_extractor.cpp:13 (cv::ORB::detectAndCompute):
+//   * cvtColor(BGR2GRAY) applied when the frame has 3 channels (system.cpp:46 feeds IMREAD_COLOR)
+//   * the 7 chained cv::resize(prev, INTER_LINEAR_EXACT) calls that build levels 1..7
+// Arithmetic: 8.8 fixed-point taps per axis computed on the host in double,
+// horizontal pass in 16 bits, vertical pass in 32 bits, (v + 2^15) >> 16.  Bit-exact integer work.
+//
+// Roofline: HBM.  Algorithmic bytes per frame = read(level l-1) + write(level l) summed over
+// l = 1..7 (1 569 878 B at 640x480).  One launch per level covers the whole batch (grid.z = frame).
+#include <math.h>
+
+#include "vxorb_internal.h"
+
+namespace vxorb {
+
+// Taps for one axis: ofs | c1 << 16, with c0 = 256 - c1 (INTER_LINEAR_EXACT coefficient rule).
+void build_resize_taps(int ssize, int dsize, uint32_t* taps) {
+    const double scale = 1.0 / ((double)dsize / (double)ssize);
+    for (int i = 0; i < dsize; ++i) {
+        double f = scale * ((double)i + 0.5) - 0.5;
+        int i0 = (int)floor(f);
+        uint32_t ofs, c1;
+        if (i0 < 0) {
+            ofs = 0;
+            c1 = 0;
+        } else if (i0 >= ssize - 1) {
+            ofs = (uint32_t)(ssize - 1);
+            c1 = 0;
+        } else {
+            ofs = (uint32_t)i0;
+            c1 = (uint32_t)lrint((f - (double)i0) * 256.0);
+        }
+        taps[i] = ofs | (c1 << 16);
+    }
+}
+
+__global__ void __launch_bounds__(256) bgr2gray_kernel(const uint8_t* __restrict__ bgr, size_t bgr_pitch,
+                                                       size_t bgr_fstride, uint8_t* __restrict__ dst,
+                                                       int w, int h, int pitch, size_t fstride) {
+    const int x0 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int y = blockIdx.y * 8 + threadIdx.y;
+    if (x0 >= w || y >= h) return;
+    const uint8_t* s = bgr + (size_t)blockIdx.z * bgr_fstride + (size_t)y * bgr_pitch + (size_t)x0 * 3;
+    uint32_t out = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (x0 + k < w) {
+            uint32_t b = s[3 * k], g = s[3 * k + 1], r = s[3 * k + 2];
+            out |= ((r * 9798u + g * 19235u + b * 3735u + (1u << 14)) >> 15) << (8 * k);
+        }
+    }
+    *reinterpret_cast<uint32_t*>(dst + (size_t)blockIdx.z * fstride + (size_t)y * pitch + x0) = out;
+}
+
+// One thread produces four horizontally adjacent output pixels (one 32-bit store).  A block of
+// 32x8 threads covers a 128x8 output strip; its source footprint (~154 B x ~10 rows at 1.2x) is
+// read through L1 with the two source rows of a thread adjacent in memory.
+__global__ void __launch_bounds__(256)
+resize_kernel(const uint8_t* __restrict__ src, int sw, int sh, int spitch, size_t sfstride,
+              uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
+              const uint32_t* __restrict__ xtab, const uint32_t* __restrict__ ytab) {
+    const int x0 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int y = blockIdx.y * 8 + threadIdx.y;
+    if (x0 >= dw || y >= dh) return;
+    src += (size_t)blockIdx.z * sfstride;
+    dst += (size_t)blockIdx.z * dfstride;
+    const uint32_t ty = __ldg(ytab + y);
+    const int j0 = (int)(ty & 0xffffu);
+    const uint32_t cy1 = ty >> 16, cy0 = 256u - cy1;
+    const int j1 = min(j0 + 1, sh - 1);
+    const uint8_t* r0 = src + (size_t)j0 * spitch;
+    const uint8_t* r1 = src + (size_t)j1 * spitch;
+    uint32_t out = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int x = x0 + k;
+        if (x < dw) {
+            const uint32_t tx = __ldg(xtab + x);
+            const int i0 = (int)(tx & 0xffffu);
+            const uint32_t cx1 = tx >> 16, cx0 = 256u - cx1;
+            const int i1 = min(i0 + 1, sw - 1);
+            const uint32_t h0 = __ldg(r0 + i0) * cx0 + __ldg(r0 + i1) * cx1;  // 8.8
+            const uint32_t h1 = __ldg(r1 + i0) * cx0 + __ldg(r1 + i1) * cx1;
+            const uint32_t v = (h0 * cy0 + h1 * cy1 + (1u << 15)) >> 16;      // <= 255
+            out |= v << (8 * k);
+        }
+    }
+    *reinterpret_cast<uint32_t*>(dst + (size_t)y * dpitch + x0) = out;
+}
+
+int launch_gray_from_bgr(const uint8_t* bgr, size_t bgr_pitch, size_t bgr_fstride, uint8_t* dst, int w,
+                         int h, int pitch, size_t fstride, int batch, cudaStream_t s) {
+    dim3 block(32, 8), grid((w + 127) / 128, (h + 7) / 8, batch);
+    bgr2gray_kernel<<<grid, block, 0, s>>>(bgr, bgr_pitch, bgr_fstride, dst, w, h, pitch, fstride);
+    return 1;
+}
+
+int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh,
+                         int dpitch, const uint32_t* xtab, const uint32_t* ytab, cudaStream_t s) {
+    dim3 block(32, 8), grid((dw + 127) / 128, (dh + 7) / 8, 1);
+    resize_kernel<<<grid, block, 0, s>>>(src, sw, sh, spitch, 0, dst, dw, dh, dpitch, 0, xtab, ytab);
+    return 1;
+}
+
+int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
+    int launches = 0;
+    for (int l = 1; l < lt.n_levels; ++l) {
+        dim3 block(32, 8), grid((lt.w[l] + 127) / 128, (lt.h[l] + 7) / 8, lt.batch);
+        resize_kernel<<<grid, block, 0, s>>>(db.pyr + lt.off[l - 1], lt.w[l - 1], lt.h[l - 1], lt.pitch[l - 1],
+                                             (size_t)lt.fstride[l - 1], db.pyr + lt.off[l], lt.w[l], lt.h[l],
+                                             lt.pitch[l], (size_t)lt.fstride[l], db.coef + lt.coef_off[l],
+                                             db.coef + lt.coef_off[l] + lt.w[l]);
+        ++launches;
+    }
+    return launches;
+}
+
+// Streams `bytes` of writes so the next kernel starts from a cold L2 (bench hygiene).
+__global__ void flush_kernel(uint4* p, size_t n16, uint32_t tag) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n16; i += stride) p[i] = make_uint4(tag, tag, tag, tag);
+}
+
+int launch_flush(uint8_t* buf, size_t bytes, cudaStream_t s) {
+    flush_kernel<<<148 * 8, 256, 0, s>>>(reinterpret_cast<uint4*>(buf), bytes / 16, 0u);
+    return 1;
+}
+
+}  // namespace vxorb

@@ -1,0 +1,102 @@
+// vxorb_internal.h — shared declarations of the sm_100a ORB extract + match library.
+//
+// Data layout in HBM.  Everything is level-major so that one launch covers all
+// frames of a batch with blockIdx.{y|z} = frame:
+//   pyr / blur : for level l, frame f, row y : base + off[l] + f*fstride[l] + y*pitch[l]
+//                (u8, pitch = width rounded up to 32 B, planes 256 B aligned)
+//   cand       : FAST corners after NMS, packed u32 = score<<24 | y<<12 | x, per (level, frame)
+//   resp       : Harris response per candidate slot (f32), written only for retained candidates
+//   fin        : final per-level keypoints (packed key, response), sorted by (y, x)
+//   kp / desc  : frame-major outputs in canonical (octave, y, x) order
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/vxorb.h"
+
+namespace vxorb {
+
+constexpr int kMaxLevels = VXORB_MAX_LEVELS;
+constexpr int kEdge = 31;        // cv::ORB edgeThreshold (only value supported)
+constexpr int kHalfPatch = 15;   // patchSize 31
+constexpr int kPitchAlign = 32;
+
+// Per-geometry tables passed to kernels by value (kernel parameters live in the constant bank).
+struct LevelTab {
+    int n_levels;
+    int batch;                       // frames in this launch
+    int w[kMaxLevels], h[kMaxLevels], pitch[kMaxLevels];
+    unsigned long long off[kMaxLevels];      // byte offset of the level plane (frame 0)
+    unsigned long long fstride[kMaxLevels];  // bytes between frames inside the level plane
+    float scale[kMaxLevels];
+    int quota[kMaxLevels];
+    int active[kMaxLevels];          // level takes part in detection (w > 62 && h > 62 && quota > 0)
+    int cand_cap[kMaxLevels];        // capacity of the candidate list of one (level, frame)
+    unsigned long long cand_off[kMaxLevels];  // element offset of (level, frame 0) in cand/resp
+    int fin_cap[kMaxLevels];
+    unsigned long long fin_off[kMaxLevels];
+    // tile bookkeeping: tiles of level l are [tile_begin[l], tile_begin[l+1]) in blockIdx.x
+    int fast_tiles_x[kMaxLevels], fast_tile_begin[kMaxLevels + 1];
+    int blur_tiles_x[kMaxLevels], blur_tile_begin[kMaxLevels + 1];
+    int coef_off[kMaxLevels];        // offset (in u32) of level l's resize tables: x[w_l] then y[h_l]
+};
+
+struct DeviceBuffers {
+    uint8_t* pyr = nullptr;
+    uint8_t* blur = nullptr;
+    uint32_t* coef = nullptr;     // resize taps: ofs | c1 << 16
+    uint32_t* cand = nullptr;
+    int* cand_n = nullptr;        // [level][frame]
+    float* resp = nullptr;
+    uint32_t* fin_key = nullptr;
+    float* fin_resp = nullptr;
+    int* fin_n = nullptr;         // [level][frame]
+    vxorb_keypoint* kp = nullptr; // [frame][kp_cap]
+    uint8_t* desc = nullptr;      // [frame][kp_cap][32]
+    float* xy = nullptr;          // [frame][kp_cap][2]  level-0 positions for windowed matching
+    int* kp_n = nullptr;          // [frame] written count (<= kp_cap)
+    int* kp_total = nullptr;      // [frame] true count (overflow detection)
+    vxorb_knn2_t* knn = nullptr;  // [pair][kp_cap]
+    vxorb_match_t* match = nullptr; // [pair][kp_cap]
+    int* match_n = nullptr;       // [pair]
+    int* status = nullptr;        // device-side overflow flags
+};
+
+// ---- kernel launchers (each in its own .cu) ----------------------------------------------------
+// All take the stream explicitly; none synchronises.  Return the number of kernel launches issued.
+int launch_gray_from_bgr(const uint8_t* bgr, size_t bgr_pitch, size_t bgr_fstride, uint8_t* dst,
+                         int w, int h, int pitch, size_t fstride, int batch, cudaStream_t s);
+int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
+int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh,
+                         int dpitch, const uint32_t* xtab, const uint32_t* ytab, cudaStream_t s);
+int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s);
+int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
+int launch_blur(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
+int launch_describe(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, cudaStream_t s);
+
+// knn over `pairs` independent (query, train) descriptor sets laid out with a fixed stride (rows).
+struct MatchArgs {
+    const uint8_t* q_desc; const uint8_t* t_desc;   // [pair][stride][32]
+    const float* q_xy; const float* t_xy;           // [pair][stride][2] or nullptr
+    const int* q_n; const int* t_n;                 // [pair] row counts (device)
+    long long q_pair_stride, t_pair_stride;         // rows between consecutive pairs
+    int max_q;                                      // upper bound of q_n (grid sizing)
+    int pairs;
+    float radius;                                   // <= 0: brute force
+    vxorb_knn2_t* knn;                              // [pair][knn_stride]
+    int knn_stride;
+};
+int launch_knn2(const MatchArgs& a, cudaStream_t s);
+// mode 0: ratio test; mode 1: ratio test + caller's post-filter; mode 2: cross-check with `back`
+int launch_match_compact(const vxorb_knn2_t* knn, const vxorb_knn2_t* back, int knn_stride, int back_stride,
+                         const int* q_n, int pairs, float nn_ratio, int mode, vxorb_match_t* out,
+                         int out_stride, int* out_n, cudaStream_t s);
+int launch_flush(uint8_t* buf, size_t bytes, cudaStream_t s);
+
+cudaError_t init_device_tables();
+void build_resize_taps(int ssize, int dsize, uint32_t* taps);
+
+}  // namespace vxorb
