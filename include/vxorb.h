@@ -212,6 +212,10 @@ long long vxorb_launch_count(const vxorb_handle* h);
 /* Writes > L2-size bytes on the handle's stream so the next launch starts from a cold L2. */
 int vxorb_flush_l2(vxorb_handle* h);
 
+/* Integer-pipe calibration for the match roofline: runs a register-only XOR+POPC+IADD kernel on
+ * every SM and reports the sustained 32-bit popcount rate (lane operations per second). */
+int vxorb_measure_popc_rate(vxorb_handle* h, double* popc_per_s_out);
+
 /* ---- stage isolation (parity tests only; each runs one kernel family on host buffers) ------ */
 int vxorb_debug_resize(vxorb_handle* h, const uint8_t* src, int sw, int sh, size_t sstride,
                        uint8_t* dst, int dw, int dh, size_t dstride);

@@ -82,6 +82,7 @@ _SYMBOLS = [
     ("vxorb_stage_times", _i, [_vp, _vp, _vp]),
     ("vxorb_launch_count", C.c_longlong, [_vp]),
     ("vxorb_flush_l2", _i, [_vp]),
+    ("vxorb_measure_popc_rate", _i, [_vp, _vp]),
     ("vxorb_debug_resize", _i, [_vp, _vp, _i, _i, _sz, _vp, _i, _i, _sz]),
     ("vxorb_debug_fast", _i, [_vp, _vp, _i, _i, _sz, _i, _i, _i, _vp, _vp]),
     ("vxorb_debug_blur", _i, [_vp, _vp, _i, _i, _sz, _vp, _sz]),
@@ -349,6 +350,12 @@ class VxOrb:
 
     def launch_count(self):
         return int(self._lib.vxorb_launch_count(self._h))
+
+    def measure_popc_rate(self):
+        """Sustained 32-bit popcount lane-ops per second of this GPU (register-only kernel)."""
+        v = C.c_double(0)
+        self._check(self._lib.vxorb_measure_popc_rate(self._h, C.byref(v)))
+        return v.value
 
     def flush_l2(self):
         self._check(self._lib.vxorb_flush_l2(self._h))

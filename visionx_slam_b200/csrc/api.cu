@@ -981,6 +981,32 @@ int vxorb_flush_l2(vxorb_handle* h) {
     return VXORB_OK;
 }
 
+int vxorb_measure_popc_rate(vxorb_handle* h, double* popc_per_s_out) {
+    if (!h || !popc_per_s_out) return VXORB_E_INVALID;
+    CK(cudaSetDevice(h->p.device_id));
+    int rc = ensure_match_scratch(h, 64);
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    const int blocks = 148 * 8, iters = 4096;
+    cudaEvent_t a = take_event(h), b = take_event(h);
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {  // first rep is the warm-up
+        CK(cudaEventRecord(a, s));
+        h->launches += launch_popc_peak(reinterpret_cast<uint32_t*>(h->m_out), blocks, iters, s);
+        CK(cudaEventRecord(b, s));
+        CK(cudaEventSynchronize(b));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, a, b));
+        const double rate = (double)blocks * 256.0 * iters * 8.0 / (ms * 1e-3);
+        if (rep > 0 && rate > best) best = rate;
+    }
+    h->event_pool.push_back(a);
+    h->event_pool.push_back(b);
+    CK(cudaGetLastError());
+    *popc_per_s_out = best;
+    return VXORB_OK;
+}
+
 // ---- stage isolation -----------------------------------------------------------------------------
 
 int vxorb_debug_resize(vxorb_handle* h, const uint8_t* src, int sw, int sh, size_t sstride, uint8_t* dst, int dw,

@@ -174,6 +174,33 @@ match_compact_kernel(const vxorb_knn2_t* __restrict__ knn, const vxorb_knn2_t* _
     if (tid == 0) out_n[pair] = s_base;
 }
 
+// Integer-pipe calibration: every thread runs `iters` rounds of 8 independent XOR+POPC+IADD chains
+// (the inner loop of the knn kernel without its memory traffic).  Used by bench.py to measure the
+// popcount peak the match stage is normalised against.
+__global__ void __launch_bounds__(256) popc_peak_kernel(uint32_t* out, int iters, uint32_t seed) {
+    uint32_t a[8], acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        a[k] = seed * (threadIdx.x + 1u) + 0x9e3779b9u * (k + 1u) + blockIdx.x;
+        acc[k] = 0;
+    }
+    uint32_t x = seed ^ threadIdx.x;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += __popc(a[k] ^ x);
+        x = x * 1664525u + 1013904223u;
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r += acc[k];
+    if (r == 0xffffffffu) out[0] = r;  // keeps the chain alive; practically never taken
+}
+
+int launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t s) {
+    popc_peak_kernel<<<blocks, 256, 0, s>>>(out, iters, 12345u);
+    return 1;
+}
+
 int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     if (a.pairs <= 0 || a.max_q <= 0) return 0;
     dim3 grid((a.max_q + kQPerBlock - 1) / kQPerBlock, a.pairs);

@@ -95,6 +95,7 @@ int launch_match_compact(const vxorb_knn2_t* knn, const vxorb_knn2_t* back, int 
                          const int* q_n, int pairs, float nn_ratio, int mode, vxorb_match_t* out,
                          int out_stride, int* out_n, cudaStream_t s);
 int launch_flush(uint8_t* buf, size_t bytes, cudaStream_t s);
+int launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t s);
 
 cudaError_t init_device_tables();
 void build_resize_taps(int ssize, int dsize, uint32_t* taps);
