@@ -1,0 +1,68 @@
+// adapter_main.cpp — drives the C++ adapters the way the reference's front end does
+// (tracking.cpp:42 Extract on every frame; tracking.cpp:208 Match(init, current)).
+//
+//   adapter_main <in.bin> <out.bin>
+// in.bin : int32 n_frames, w, h, channels; then n_frames * h * w * channels bytes
+// out.bin: per frame: int32 n; n * (double x, double y, float response); n * 32 descriptor bytes
+//          then per consecutive pair (i-1 -> i): int32 m; m * (int32 q, int32 t, float dist)
+//          then the same for MatchFiltered.
+#include <cstdio>
+#include <cstdlib>
+#include <memory>
+#include <vector>
+
+#include "cuda_orb_extractor.h"
+#include "cuda_orb_matcher.h"
+
+using namespace visionx;
+
+int main(int argc, char** argv) {
+    if (argc != 3) return 2;
+    FILE* fi = fopen(argv[1], "rb");
+    if (!fi) return 3;
+    int hdr[4];
+    if (fread(hdr, 4, 4, fi) != 4) return 3;
+    const int n = hdr[0], w = hdr[1], h = hdr[2], ch = hdr[3];
+    std::vector<unsigned char> pix((size_t)w * h * ch);
+    std::shared_ptr<FeatureExtractor> extractor = std::make_shared<CudaORBExtractor>();  // system.cpp:15
+    std::shared_ptr<FeatureMatcher> matcher = std::make_shared<CudaORBMatcher>();        // system.cpp:16
+    std::vector<Frame::Ptr> frames;
+    for (int i = 0; i < n; ++i) {
+        if (fread(pix.data(), 1, pix.size(), fi) != pix.size()) return 3;
+        cv::Mat img(h, w, ch == 3 ? CV_8UC3 : CV_8UC1, pix.data(), (size_t)w * ch);
+        auto f = std::make_shared<Frame>((uint64_t)i, 0.1 * i, img);
+        extractor->Extract(*f);
+        frames.push_back(f);
+    }
+    fclose(fi);
+    FILE* fo = fopen(argv[2], "wb");
+    if (!fo) return 4;
+    for (auto& f : frames) {
+        const int k = (int)f->Features().size();
+        fwrite(&k, 4, 1, fo);
+        for (auto& ft : f->Features()) {
+            const double xy[2] = {ft.position.x(), ft.position.y()};
+            fwrite(xy, 8, 2, fo);
+            fwrite(&ft.response, 4, 1, fo);
+        }
+        if (k != f->Descriptors().rows || (k && f->Descriptors().cols != 32)) return 5;
+        for (int r = 0; r < k; ++r) fwrite(f->Descriptors().data + r * f->Descriptors().step, 1, 32, fo);
+    }
+    auto* cm = dynamic_cast<CudaORBMatcher*>(matcher.get());
+    for (int pass = 0; pass < 2; ++pass)
+        for (int i = 1; i < n; ++i) {
+            std::vector<cv::DMatch> matches(3);  // must be cleared by Match
+            const int m = pass == 0 ? matcher->Match(frames[i - 1], frames[i], matches)
+                                    : cm->MatchFiltered(frames[i - 1], frames[i], matches);
+            if (m != (int)matches.size()) return 6;
+            fwrite(&m, 4, 1, fo);
+            for (auto& d : matches) {
+                if (d.imgIdx != 0) return 7;
+                fwrite(&d.queryIdx, 4, 1, fo);
+                fwrite(&d.trainIdx, 4, 1, fo);
+                fwrite(&d.distance, 4, 1, fo);
+            }
+        }
+    fclose(fo);
+    return 0;
+}

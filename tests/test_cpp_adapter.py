@@ -1,0 +1,108 @@
+"""The C++ host side (visionx_slam_b200/cpp): the reference-facing classes CudaORBExtractor /
+CudaORBMatcher, compiled against tests/stubs (no OpenCV/Eigen/glog C++ headers in this image).
+
+CPU: the adapters compile with the reference's warning flags (-Wall -Wextra -Wpedantic,
+CMakeLists.txt:11-15) and the driver links against libvxorb.so.
+GPU: tests/cpp/adapter_main.cpp drives Extract on every frame and Match(last, curr) the way
+tracking.cpp:42,208 does; results are compared with the oracle bit for bit."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CPP = os.path.join(ROOT, "visionx_slam_b200", "cpp")
+EXE = os.path.join(CPP, "build", "adapter_main")
+
+
+def _build():
+    subprocess.check_call(["make", "-C", CPP, "-s"])
+
+
+def test_adapters_compile_and_link():
+    _build()
+    assert os.path.exists(EXE)
+    out = subprocess.run(["ldd", EXE], capture_output=True, text=True).stdout
+    assert "libvxorb.so" in out and "not found" not in out.split("libvxorb.so")[1].split("\n")[0]
+
+
+def test_adapters_derive_from_reference_interfaces():
+    h = open(os.path.join(CPP, "cuda_orb_extractor.h")).read()
+    assert "class CudaORBExtractor : public FeatureExtractor" in h and "void Extract(Frame& frame) override;" in h
+    m = open(os.path.join(CPP, "cuda_orb_matcher.h")).read()
+    assert "class CudaORBMatcher : public FeatureMatcher" in m
+    assert "int Match(const Frame::Ptr& last, const Frame::Ptr& curr, std::vector<cv::DMatch>& matches) override;" in m
+
+
+def _run_adapter(tmp_path, frames):
+    n, hh, w = frames.shape[:3]
+    ch = frames.shape[3] if frames.ndim == 4 else 1
+    fin, fout = tmp_path / "in.bin", tmp_path / "out.bin"
+    with open(fin, "wb") as f:
+        f.write(struct.pack("<4i", n, w, hh, ch))
+        f.write(np.ascontiguousarray(frames).tobytes())
+    r = subprocess.run([EXE, str(fin), str(fout)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    buf = open(fout, "rb").read()
+    pos = 0
+    feats = []
+    for _ in range(n):
+        (k,) = struct.unpack_from("<i", buf, pos)
+        pos += 4
+        rec = np.frombuffer(buf, np.dtype([("x", "<f8"), ("y", "<f8"), ("r", "<f4")]), k, pos)
+        pos += 20 * k
+        desc = np.frombuffer(buf, np.uint8, 32 * k, pos).reshape(k, 32)
+        pos += 32 * k
+        feats.append((rec, desc))
+    matches = []
+    for _ in range(2):
+        per = []
+        for _ in range(n - 1):
+            (m,) = struct.unpack_from("<i", buf, pos)
+            pos += 4
+            per.append(np.frombuffer(buf, np.dtype([("q", "<i4"), ("t", "<i4"), ("d", "<f4")]), m, pos))
+            pos += 12 * m
+        matches.append(per)
+    assert pos == len(buf)
+    return feats, matches[0], matches[1], r.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_adapter_matches_oracle(tmp_path):
+    import oracle
+    from conftest import matches_as_rows
+    from visionx_slam_b200.synth import synth_sequence
+    _build()
+    frames = synth_sequence(640, 480, 3, seed=21)
+    frames = np.concatenate([frames, np.zeros((1, 480, 640), np.uint8)])  # blank frame: 0 features, 0 matches
+    feats, m_plain, m_filt, log = _run_adapter(tmp_path, frames)
+    ref = [oracle.orb_extract(f) for f in frames]
+    for (rec, desc), (okp, odesc) in zip(feats, ref):
+        assert len(rec) == len(okp)
+        assert np.array_equal(rec["x"], okp["x"].astype(np.float64)) and np.array_equal(rec["y"], okp["y"].astype(np.float64))
+        assert np.array_equal(rec["r"], okp["response"])
+        assert np.array_equal(desc, odesc)
+    for i in range(1, len(frames)):
+        om = oracle.match(ref[i - 1][1], ref[i][1], 0.8)
+        got = m_plain[i - 1]
+        assert np.array_equal(np.stack([got["q"], got["t"], got["d"].astype(np.int32)], 1).reshape(-1, 3), matches_as_rows(om))
+        of = oracle.postfilter(om)
+        gf = m_filt[i - 1]
+        assert np.array_equal(np.stack([gf["q"], gf["t"], gf["d"].astype(np.int32)], 1).reshape(-1, 3), matches_as_rows(of))
+    assert len(feats[3][0]) == 0 and len(m_plain[2]) == 0
+    assert "Too few matches" in log  # orb_matcher.cpp:38-40 warning kept
+
+
+@pytest.mark.gpu
+def test_cpp_adapter_bgr(tmp_path):
+    import oracle
+    from visionx_slam_b200.synth import synth_scene
+    _build()
+    rng = np.random.default_rng(5)
+    g = synth_scene(320, 240, 9)
+    bgr = np.stack([np.clip(g.astype(int) + rng.integers(-20, 20, g.shape), 0, 255).astype(np.uint8) for _ in range(3)], 2)
+    feats, _, _, _ = _run_adapter(tmp_path, bgr[None])
+    okp, odesc = oracle.orb_extract(oracle.bgr2gray(bgr))
+    assert len(feats[0][0]) == len(okp) and np.array_equal(feats[0][1], odesc)

@@ -1,0 +1,65 @@
+// cuda_orb_extractor.cpp — see cuda_orb_extractor.h.  Marshals between Frame (core/frame/frame.h:
+// 25-64) and the C ABI; no image arithmetic happens here.
+#include "cuda_orb_extractor.h"
+
+#include <glog/logging.h>
+
+#include <stdexcept>
+
+namespace visionx {
+
+CudaORBExtractor::CudaORBExtractor(int n_features, float scale_factor, int n_levels, int device_id,
+                                   int max_width, int max_height) {
+    vxorb_params p;
+    vxorb_default_params(&p);
+    p.n_features = n_features;      // orb_extractor.cpp:6 cv::ORB::create(n_features, scale, levels)
+    p.scale_factor = scale_factor;
+    p.n_levels = n_levels;
+    p.device_id = device_id;
+    p.max_width = max_width;
+    p.max_height = max_height;
+    const int rc = vxorb_create(&p, &handle_);
+    if (rc != VXORB_OK)
+        throw std::runtime_error(std::string("CudaORBExtractor: vxorb_create failed: ") + vxorb_last_error(nullptr));
+    kp_cap_ = vxorb_keypoint_capacity(handle_);
+    kp_.resize(static_cast<size_t>(kp_cap_));
+}
+
+CudaORBExtractor::~CudaORBExtractor() { vxorb_destroy(handle_); }
+
+void CudaORBExtractor::Extract(Frame& frame) {
+    auto& features = frame.Features();
+    features.clear();  // orb_extractor.cpp:16
+    const cv::Mat& image = frame.Image();
+    cv::Mat desc(kp_cap_, VXORB_DESC_BYTES, CV_8UC1);
+    int n = 0;
+    int rc = VXORB_E_INVALID;
+    if (!image.empty() && image.depth() == CV_8U && (image.channels() == 1 || image.channels() == 3)) {
+        // cv::ORB converts 3-channel input to gray itself; system.cpp:46 feeds IMREAD_COLOR frames
+        auto fn = image.channels() == 3 ? vxorb_extract_bgr : vxorb_extract;
+        rc = fn(handle_, image.data, image.cols, image.rows, static_cast<size_t>(image.step), kp_cap_, kp_.data(),
+                desc.data, &n);
+    }
+    last_status_ = rc;
+    if (rc != VXORB_OK && rc != VXORB_E_CAPACITY) {
+        last_error_ = image.empty() ? "empty or unsupported image" : vxorb_last_error(handle_);
+        LOG(ERROR) << "[CudaORBExtractor] " << last_error_;
+        frame.Descriptors() = cv::Mat();
+        return;
+    }
+    if (rc == VXORB_E_CAPACITY) {
+        last_error_ = vxorb_last_error(handle_);
+        LOG(WARNING) << "[CudaORBExtractor] " << last_error_;
+    }
+    if (n > kp_cap_) n = kp_cap_;
+    features.reserve(static_cast<size_t>(n));
+    for (int i = 0; i < n; ++i) {  // orb_extractor.cpp:19-24
+        Feature f;
+        f.position = Eigen::Vector2d(kp_[i].x, kp_[i].y);
+        f.response = kp_[i].response;
+        features.emplace_back(f);
+    }
+    frame.Descriptors() = n > 0 ? desc.rowRange(0, n).clone() : cv::Mat();  // orb_extractor.cpp:26
+}
+
+}  // namespace visionx

@@ -1,0 +1,50 @@
+// cuda_orb_extractor.h — drop-in for visionx::ORBExtractor (core/feature/orb_extractor.h:9-20).
+//
+// Same constructor arguments and the same Extract(Frame&) contract as the reference class
+// (core/feature/orb_extractor.cpp:9-27): frame.Features() is replaced by one Feature per keypoint
+// (position = level-0 pixel coordinates as double, response = Harris response) and
+// frame.Descriptors() is assigned a freshly owned N x 32 CV_8UC1 matrix.  The arithmetic
+// cv::ORB::detectAndCompute did on the CPU (orb_extractor.cpp:13) runs in libvxorb.so's sm_100a
+// kernels through the C ABI of include/vxorb.h.  There is no CPU fallback: construction throws
+// std::runtime_error when no B200-class device / library is usable, and a failing device call
+// leaves the frame with zero features (the reference's "no features" path, tracking.cpp:179-184)
+// after logging the vxorb error text.
+//
+// Keypoint order is canonical (octave, y, x) instead of OpenCV's nth_element artefact order; the
+// keypoint SET, responses and descriptors are identical.
+#pragma once
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "feature/feature_extractor.h"
+#include "vxorb.h"
+
+namespace visionx {
+
+class CudaORBExtractor : public FeatureExtractor {
+public:
+    explicit CudaORBExtractor(int n_features = 1000, float scale_factor = 1.2f, int n_levels = 8,
+                              int device_id = 0, int max_width = 1920, int max_height = 1088);
+    ~CudaORBExtractor() override;
+    CudaORBExtractor(const CudaORBExtractor&) = delete;
+    CudaORBExtractor& operator=(const CudaORBExtractor&) = delete;
+
+    void Extract(Frame& frame) override;
+
+    // Last vxorb status / message (VXORB_OK after a successful Extract).
+    int last_status() const { return last_status_; }
+    const std::string& last_error() const { return last_error_; }
+    // The handle is shared with a CudaORBMatcher built from it so both use one device context.
+    vxorb_handle* handle() const { return handle_; }
+
+private:
+    vxorb_handle* handle_ = nullptr;
+    int kp_cap_ = 0;
+    std::vector<vxorb_keypoint> kp_;
+    int last_status_ = VXORB_OK;
+    std::string last_error_;
+};
+
+}  // namespace visionx
