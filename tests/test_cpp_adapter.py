@@ -92,7 +92,7 @@ def test_cpp_adapter_matches_oracle(tmp_path):
         gf = m_filt[i - 1]
         assert np.array_equal(np.stack([gf["q"], gf["t"], gf["d"].astype(np.int32)], 1).reshape(-1, 3), matches_as_rows(of))
     assert len(feats[3][0]) == 0 and len(m_plain[2]) == 0
-    assert "Too few matches" in log  # orb_matcher.cpp:38-40 warning kept
+    assert "Too few matches" not in log  # an empty side returns before the warning (orb_matcher.cpp:18-20)
 
 
 @pytest.mark.gpu
@@ -103,6 +103,11 @@ def test_cpp_adapter_bgr(tmp_path):
     rng = np.random.default_rng(5)
     g = synth_scene(320, 240, 9)
     bgr = np.stack([np.clip(g.astype(int) + rng.integers(-20, 20, g.shape), 0, 255).astype(np.uint8) for _ in range(3)], 2)
-    feats, _, _, _ = _run_adapter(tmp_path, bgr[None])
+    other = np.ascontiguousarray(bgr[::-1, ::-1])  # unrelated second frame: few ratio-test survivors
+    feats, m_plain, _, log = _run_adapter(tmp_path, np.stack([bgr, other]))
     okp, odesc = oracle.orb_extract(oracle.bgr2gray(bgr))
     assert len(feats[0][0]) == len(okp) and np.array_equal(feats[0][1], odesc)
+    okp2, odesc2 = oracle.orb_extract(oracle.bgr2gray(other))
+    om = oracle.match(odesc, odesc2, 0.8)
+    assert len(m_plain[0]) == len(om)
+    assert ("Too few matches" in log) == (len(om) < 50)  # orb_matcher.cpp:38-40 warning kept

@@ -167,9 +167,9 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
             lt.n_levels = l;
             break;
         }
-        lt.pitch[l] = (int)align_up((size_t)lt.w[l], kPitchAlign);
-        lt.fstride[l] = (unsigned long long)lt.pitch[l] * lt.h[l];
-        lt.off[l] = off;
+        lt.pitch[l] = plane_pitch(lt.w[l]);
+        lt.fstride[l] = plane_bytes(lt.w[l], lt.h[l]);
+        lt.off[l] = off + plane_origin(lt.w[l]);
         off += align_up((size_t)lt.fstride[l] * B, 256);
         lt.active[l] = (lt.w[l] > 2 * kEdge && lt.h[l] > 2 * kEdge && lt.quota[l] > 0) ? 1 : 0;
         const int ew = lt.w[l] - 2 * kEdge, eh = lt.h[l] - 2 * kEdge;  // emission domain
@@ -179,11 +179,12 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
         lt.fin_cap[l] = std::min(lt.cand_cap[l], h->kp_cap);
         lt.fin_off[l] = fin_off;
         fin_off += (size_t)lt.fin_cap[l] * B;
-        lt.fast_tiles_x[l] = lt.active[l] ? (ew + 63) / 64 : 0;
-        const int fty = lt.active[l] ? (eh + 31) / 32 : 0;
+        lt.fast_tiles_x[l] = lt.active[l] ? fast_tiles_x(lt.w[l], kEdge) : 0;
+        const int fty = lt.active[l] ? fast_tiles_y(lt.h[l], kEdge) : 0;
         lt.fast_tile_begin[l + 1] = lt.fast_tile_begin[l] + lt.fast_tiles_x[l] * fty;
-        lt.blur_tiles_x[l] = (lt.w[l] + 63) / 64;
-        lt.blur_tile_begin[l + 1] = lt.blur_tile_begin[l] + lt.blur_tiles_x[l] * ((lt.h[l] + 31) / 32);
+        lt.blur_tiles_x[l] = (lt.w[l] + 3) / 4;
+        lt.blur_tile_begin[l + 1] =
+            lt.blur_tile_begin[l] + (lt.blur_tiles_x[l] * ((lt.h[l] + kBlurRows - 1) / kBlurRows) + 255) / 256;
         lt.coef_off[l] = coef_off;
         if (l > 0) {
             coef.resize((size_t)coef_off + lt.w[l] + lt.h[l]);
@@ -284,7 +285,9 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
     // cand_n / fin_n are indexed [level * batch + frame] with the launch's batch
     {
         StageScope sc(h, s, VXORB_STAGE_PYRAMID);
-        sc.end(launch_pyramid(lt, d, s));
+        int n = launch_pyramid(lt, d, s);
+        n += launch_apron(lt, d, s);
+        sc.end(n);
     }
     {
         StageScope sc(h, s, VXORB_STAGE_FAST);
@@ -343,9 +346,15 @@ int upload_frames(vxorb_handle* h, Workspace& ws, const uint8_t* frames, int bat
                   size_t frame_stride) {
     const LevelTab& lt = h->lt;
     uint8_t* dst = ws.db.pyr + lt.off[0];
-    if (frame_stride == stride * (size_t)H) {
-        CK(cudaMemcpy2DAsync(dst, lt.pitch[0], frames, stride, W, (size_t)H * batch, cudaMemcpyHostToDevice,
-                             ws.stream));
+    if (stride > 0 && frame_stride % stride == 0 && frame_stride / stride >= (size_t)H) {
+        // one strided 3-D copy: frame f, row y of the source -> plane f, row y (planes carry an apron)
+        cudaMemcpy3DParms p;
+        memset(&p, 0, sizeof(p));
+        p.srcPtr = make_cudaPitchedPtr(const_cast<uint8_t*>(frames), stride, (size_t)W, frame_stride / stride);
+        p.dstPtr = make_cudaPitchedPtr(dst, (size_t)lt.pitch[0], (size_t)W, (size_t)(lt.fstride[0] / lt.pitch[0]));
+        p.extent = make_cudaExtent((size_t)W, (size_t)H, (size_t)batch);
+        p.kind = cudaMemcpyHostToDevice;
+        CK(cudaMemcpy3DAsync(&p, ws.stream));
     } else {
         for (int f = 0; f < batch; ++f)
             CK(cudaMemcpy2DAsync(dst + (size_t)f * lt.fstride[0], lt.pitch[0], frames + (size_t)f * frame_stride,
@@ -1040,16 +1049,17 @@ static int single_level_tab(vxorb_handle* h, int W, int H, int border, LevelTab*
     lt.batch = 1;
     lt.w[0] = W;
     lt.h[0] = H;
-    lt.pitch[0] = (int)align_up((size_t)W, kPitchAlign);
-    lt.fstride[0] = (unsigned long long)lt.pitch[0] * H;
+    lt.pitch[0] = plane_pitch(W);
+    lt.fstride[0] = plane_bytes(W, H);
+    lt.off[0] = plane_origin(W);
     lt.scale[0] = 1.f;
     const int ew = W - 2 * border, eh = H - 2 * border;
     lt.active[0] = (ew > 0 && eh > 0) ? 1 : 0;
     lt.cand_cap[0] = lt.active[0] ? ((ew + 1) / 2 + 1) * ((eh + 1) / 2 + 1) : 0;
-    lt.fast_tiles_x[0] = lt.active[0] ? (ew + 63) / 64 : 0;
-    lt.fast_tile_begin[1] = lt.active[0] ? lt.fast_tiles_x[0] * ((eh + 31) / 32) : 0;
-    lt.blur_tiles_x[0] = (W + 63) / 64;
-    lt.blur_tile_begin[1] = lt.blur_tiles_x[0] * ((H + 31) / 32);
+    lt.fast_tiles_x[0] = lt.active[0] ? fast_tiles_x(W, border) : 0;
+    lt.fast_tile_begin[1] = lt.active[0] ? lt.fast_tiles_x[0] * fast_tiles_y(H, border) : 0;
+    lt.blur_tiles_x[0] = (W + 3) / 4;
+    lt.blur_tile_begin[1] = (lt.blur_tiles_x[0] * ((H + kBlurRows - 1) / kBlurRows) + 255) / 256;
     for (int l = 1; l < kMaxLevels; ++l) {
         lt.fast_tile_begin[l + 1] = lt.fast_tile_begin[1];
         lt.blur_tile_begin[l + 1] = lt.blur_tile_begin[1];
@@ -1084,7 +1094,7 @@ int vxorb_debug_fast(vxorb_handle* h, const uint8_t* img, int width, int height,
     if (!lt.active[0]) return VXORB_OK;
     cudaStream_t s = h->ws[0].stream;
     CK(cudaMemsetAsync(h->s_a, 0, h->s_bytes, s));
-    CK(cudaMemcpy2DAsync(db.pyr, lt.pitch[0], img, stride, width, height, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpy2DAsync(db.pyr + lt.off[0], lt.pitch[0], img, stride, width, height, cudaMemcpyHostToDevice, s));
     h->launches += launch_fast(lt, db, threshold, border, s);
     CK(cudaGetLastError());
     int n = 0;
@@ -1119,10 +1129,11 @@ int vxorb_debug_blur(vxorb_handle* h, const uint8_t* src, int width, int height,
     int rc = single_level_tab(h, width, height, 3, &lt, &db, &ccap);
     if (rc) return rc;
     cudaStream_t s = h->ws[0].stream;
-    CK(cudaMemcpy2DAsync(db.pyr, lt.pitch[0], src, stride, width, height, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpy2DAsync(db.pyr + lt.off[0], lt.pitch[0], src, stride, width, height, cudaMemcpyHostToDevice, s));
+    h->launches += launch_apron(lt, db, s);
     h->launches += launch_blur(lt, db, s);
     CK(cudaGetLastError());
-    CK(cudaMemcpy2DAsync(dst, dstride, db.blur, lt.pitch[0], width, height, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpy2DAsync(dst, dstride, db.blur + lt.off[0], lt.pitch[0], width, height, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     return VXORB_OK;
 }

@@ -6,9 +6,19 @@
 //   row pass     acc = k0*x0;  acc = fma(x_i, k_i, acc)            i = 1..6
 //   column pass  acc = k3*r3;  acc = fma(r[3-j] + r[3+j], k[3+j], acc)   j = 1..3
 //   output       saturate(round-half-even(acc))
-// Tile: 64x32 outputs per CTA; (32+6) x (64+6) source bytes with the reflect-101 halo resolved at
-// load time; row-pass results kept as float in shared memory; four outputs per thread per store.
-// Roofline: HBM, algorithmic bytes = read + write of every level pixel (1 901 064 B per 640x480).
+//
+// Register-resident separable filter, no shared memory.  One thread owns a strip of 4 adjacent
+// columns x kBlurRows output rows and walks down the source rows:
+//   * per source row: three aligned 32-bit loads (columns x0-4 .. x0+7; the reflect-101 apron
+//     written by apron_kernel makes the border a plain read), ten byte->float conversions
+//     (PRMT into 0x4B0000bb, then subtract 2^23: exact), 4 x 7 row-pass FMAs;
+//   * the last seven row-pass rows live in registers (window rotated by unrolling x7);
+//   * per output row: 4 x 7 column-pass ops, round-half-even by adding 1.5*2^23, pack, one
+//     32-bit store.  Consecutive lanes own consecutive words, so loads and stores coalesce.
+// Strips are enumerated per level (band-major, then word) and dealt to threads linearly, so lane
+// utilisation does not depend on the level width.
+// Roofline: HBM, algorithmic bytes = read + write of every level pixel (1 901 064 B per 640x480);
+// the kernel is FP32-issue bound (~23 instructions per pixel), see DESIGN.md section 4.
 #include <math.h>
 
 #include "vxorb_internal.h"
@@ -17,83 +27,94 @@ namespace vxorb {
 
 namespace {
 
-constexpr int BW = 64, BH = 32;
-constexpr int SRC_W = BW + 6, SRC_H = BH + 6;
-constexpr int SRC_P = 72;  // padded source row
-
-__device__ __forceinline__ int reflect101(int i, int n) {
-    if (n == 1) return 0;
-    while (i < 0 || i >= n) {
-        if (i < 0) i = -i;
-        if (i >= n) i = 2 * (n - 1) - i;
-    }
-    return i;
-}
-
 struct GaussK {
     float k[7];
 };
+
+__device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t sel) {
+    // bytes [b, 0, 0, 0x4B] = 2^23 + b as a float; the subtraction is exact
+    return __fsub_rn(__uint_as_float(__byte_perm(word, 0x4B000000u, sel)), 8388608.0f);
+}
 
 }  // namespace
 
 __global__ void __launch_bounds__(256)
 blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, const GaussK gk) {
-    __shared__ uint8_t src[SRC_H][SRC_P];
-    __shared__ float rows[SRC_H][BW];
-
-    const int tid = threadIdx.x;
     int l = 0;
     while (l + 1 < lt.n_levels && (int)blockIdx.x >= lt.blur_tile_begin[l + 1]) ++l;
-    const int tl = blockIdx.x - lt.blur_tile_begin[l];
-    const int tx = tl % lt.blur_tiles_x[l], ty = tl / lt.blur_tiles_x[l];
-    const int f = blockIdx.y;
     const int w = lt.w[l], h = lt.h[l], pitch = lt.pitch[l];
-    const uint8_t* img = pyr + lt.off[l] + (size_t)f * lt.fstride[l];
-    uint8_t* out = blur + lt.off[l] + (size_t)f * lt.fstride[l];
-    const int ox = tx * BW, oy = ty * BH;
+    const int words = lt.blur_tiles_x[l];
+    const int item = ((int)blockIdx.x - lt.blur_tile_begin[l]) * 256 + (int)threadIdx.x;
+    const int band = item / words;
+    const int y0 = band * kBlurRows;
+    if (y0 >= h) return;
+    const int x0 = (item - band * words) * 4;
+    (void)w;
+    const int rows_out = min(kBlurRows, h - y0);
+    const size_t plane = lt.off[l] + (size_t)blockIdx.y * lt.fstride[l];
+    // source row r (0-based in the strip) is image row y0 - 3 + r; word c-1 starts at x0 - 4
+    const uint8_t* src = pyr + plane + (ptrdiff_t)(y0 - kApronY) * pitch + (x0 - 4);
+    uint8_t* dst = blur + plane + (size_t)y0 * pitch + x0;
+    const int last_src = rows_out + 2 * kApronY - 1;
+    const int groups = (rows_out + 2 * kApronY + 6) / 7;
 
-    for (int i = tid; i < SRC_H * SRC_W; i += 256) {
-        const int r = i / SRC_W, c = i - r * SRC_W;
-        const int gy = reflect101(oy - 3 + r, h), gx = reflect101(ox - 3 + c, w);
-        src[r][c] = __ldg(img + (size_t)gy * pitch + gx);
-    }
-    __syncthreads();
+    float win[7][4];
+#pragma unroll
+    for (int i = 0; i < 7; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) win[i][j] = 0.f;
 
-    // row pass: rows[r][x] for the 38 source rows of the tile
-    for (int i = tid; i < SRC_H * BW; i += 256) {
-        const int r = i / BW, x = i - r * BW;
-        const uint8_t* p = &src[r][x];
-        float acc = __fmul_rn(gk.k[0], (float)p[0]);
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(src);
+    const int pitch_w = pitch >> 2;  // pitch is a multiple of 32
+    int r = 0;
+    dst -= (size_t)6 * pitch;        // output row of source row r is r - 6
+    for (int g = 0; g < groups; ++g) {
 #pragma unroll
-        for (int t = 1; t < 7; ++t) acc = __fmaf_rn((float)p[t], gk.k[t], acc);
-        rows[r][x] = acc;
-    }
-    __syncthreads();
-
-    // column pass: each thread produces 4 adjacent pixels of one row, two rows per thread
-    for (int i = tid; i < BH * (BW / 4); i += 256) {
-        const int y = i / (BW / 4), x0 = (i - y * (BW / 4)) * 4;
-        const int gy = oy + y, gx0 = ox + x0;
-        if (gy >= h || gx0 >= w) continue;
-        uint32_t packed = 0;
+        for (int s = 0; s < 7; ++s, ++r) {
+            const uint32_t wa = __ldg(p), wb = __ldg(p + 1), wc = __ldg(p + 2);
+            if (r < last_src) p += pitch_w;  // never read below the apron
+            float f[10];
+            f[0] = byte_to_float(wa, 0x7541u);
+            f[1] = byte_to_float(wa, 0x7542u);
+            f[2] = byte_to_float(wa, 0x7543u);
+            f[3] = byte_to_float(wb, 0x7540u);
+            f[4] = byte_to_float(wb, 0x7541u);
+            f[5] = byte_to_float(wb, 0x7542u);
+            f[6] = byte_to_float(wb, 0x7543u);
+            f[7] = byte_to_float(wc, 0x7540u);
+            f[8] = byte_to_float(wc, 0x7541u);
+            f[9] = byte_to_float(wc, 0x7542u);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int x = x0 + k;
-            float acc = __fmul_rn(gk.k[3], rows[y + 3][x]);
+            for (int j = 0; j < 4; ++j) {
+                float acc = __fmul_rn(gk.k[0], f[j]);
 #pragma unroll
-            for (int j = 1; j <= 3; ++j)
-                acc = __fmaf_rn(__fadd_rn(rows[y + 3 - j][x], rows[y + 3 + j][x]), gk.k[3 + j], acc);
-            int v = __float2int_rn(acc);
-            v = min(max(v, 0), 255);
-            if (gx0 + k < w) packed |= (uint32_t)v << (8 * k);
+                for (int t = 1; t < 7; ++t) acc = __fmaf_rn(f[j + t], gk.k[t], acc);
+                win[s][j] = acc;
+            }
+            // rows r-6 .. r are in win[(s+1)%7] .. win[s]; the output row is r - 6
+            const int o = r - 6;
+            if (o >= 0 && o < rows_out) {
+                uint32_t t4[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float acc = __fmul_rn(gk.k[3], win[(s + 4) % 7][j]);
+                    acc = __fmaf_rn(__fadd_rn(win[(s + 3) % 7][j], win[(s + 5) % 7][j]), gk.k[4], acc);
+                    acc = __fmaf_rn(__fadd_rn(win[(s + 2) % 7][j], win[(s + 6) % 7][j]), gk.k[5], acc);
+                    acc = __fmaf_rn(__fadd_rn(win[(s + 1) % 7][j], win[s][j]), gk.k[6], acc);
+                    // 0 <= acc <= 255.001: adding 1.5 * 2^23 leaves round-half-even(acc) in the low byte
+                    t4[j] = __float_as_uint(__fadd_rn(acc, 12582912.0f));
+                }
+                const uint32_t lo = __byte_perm(t4[0], t4[1], 0x0040u), hi = __byte_perm(t4[2], t4[3], 0x0040u);
+                *reinterpret_cast<uint32_t*>(dst) = __byte_perm(lo, hi, 0x5410u);
+            }
+            dst += pitch;
         }
-        *reinterpret_cast<uint32_t*>(out + (size_t)gy * pitch + gx0) = packed;
     }
 }
 
 int launch_blur(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
-    const int tiles = lt.blur_tile_begin[lt.n_levels];
-    if (tiles == 0) return 0;
+    const int ctas = lt.blur_tile_begin[lt.n_levels];
+    if (ctas == 0) return 0;
     GaussK gk;
     {
         // cv::getGaussianKernel(7, 2, CV_32F): normalised in double, then rounded to float
@@ -105,7 +126,7 @@ int launch_blur(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
         }
         for (int i = 0; i < 7; ++i) gk.k[i] = (float)(t[i] / sum);
     }
-    dim3 grid(tiles, lt.batch);
+    dim3 grid(ctas, lt.batch);
     blur_kernel<<<grid, 256, 0, s>>>(lt, db.pyr, db.blur, gk);
     return 1;
 }

@@ -3,192 +3,214 @@
 // Replaces cv::FastFeatureDetector(20, true)::detect on every pyramid level plus
 // KeyPointsFilter::runByImageBorder(31), both inside cv::ORB::detectAndCompute
 // (orb_extractor.cpp:13).  Semantics: SURVEY.md A.2/A.3 — a pixel is a corner iff >= 9 contiguous
-// ring pixels are all > v+t or all < v-t; score = max over the 16 arcs of 9 of min|v - p| minus 1;
-// kept iff its score is strictly greater than the 8 neighbours' scores.  Integer work, bit-exact.
+// ring pixels are all > v+t or all < v-t; score = max over the 16 arcs of 9 of min|v - p| minus 1
+// (so corner <=> score >= t); kept iff its score is strictly greater than the 8 neighbours'.
+// Integer work, bit-exact.
 //
-// One CTA handles a 64x32 tile of one (level, frame); the score map never leaves shared memory.
-//   load   : (32+8) rows x 96 B of 16-byte vectors (3-px ring + 1-px NMS halo, 16 B aligned start)
-//   pass A : every pixel of the (64+2)x(32+2) score domain runs the 4 opposite-pair quick test;
-//            survivors are pushed to a shared queue (ballot + popc), so later passes stay converged
-//   pass B : full 16-pixel segment test + score for queued pixels (arc minima in packed s16x2)
-//   pass C : NMS on the shared score map, survivors staged in shared memory
-//   emit   : one global atomicAdd per CTA, coalesced write of packed corners
-// Roofline: HBM, algorithmic bytes = one read of every level pixel (950 532 B per 640x480 frame).
+// One CTA (8 warps) owns a tile whose score region is 128 x 40 px (emission region: the inner
+// 124 x 38); the level pixels it needs sit in shared memory as 32-bit words and the score map never
+// leaves shared memory.
+//   load    46 rows x 34 aligned words (3-row ring halo, one halo word left and right)
+//   stage 1 every lane tests FOUR horizontally adjacent pixels per step with byte SIMD: a corner
+//           needs, for each opposite ring pair {k, k+8}, one pixel with |p - v| > t, so
+//           (F0|F8) & (F4|F12) with F = per-byte |p - v| > t (VABSDIFF4 + carry trick) is a
+//           necessary condition; 16-byte pixel rows -> 5 LDS, 2 PRMT, 4 VABSDIFF4, ~16 logic ops
+//           per 4 px.  Survivor bits of a warp's 5 rows collect in one register per lane and are
+//           compacted to a shared queue with one warp prefix sum.
+//   stage 2 one thread scores TWO queued pixels at once in s16x2 lanes: D_k = p_k - v, sliding
+//           min-of-9 / max-of-9 over the ring with 3-input VIMNMX3 (40 + 40 ops), score =
+//           max(max_arcs min D, -min_arcs max D) - 1, written to the score map iff >= t.
+//   stage 3 strict 3x3 NMS of queued pixels on the score map, survivors staged in shared memory
+//   emit    one global atomicAdd per CTA, coalesced write of packed corners (score<<24|y<<12|x)
+// Roofline: HBM, algorithmic bytes = one read of every level pixel (950 532 B per 640x480 frame);
+// the kernel is integer-issue bound.
 #include "vxorb_internal.h"
 
 namespace vxorb {
 
 namespace {
 
-constexpr int TW = 64, TH = 32;
-constexpr int SMW = 96;           // shared row bytes (6 x uint4)
-constexpr int SMH = TH + 8;
-constexpr int SCW = TW + 2, SCH = TH + 2;
-constexpr int SCP = SCW + 2;      // padded score row
-constexpr int QCAP = SCW * SCH;
-constexpr int OCAP = (TW / 2 + 1) * (TH / 2 + 1);
+constexpr int FW = kFastScoreW, FSR = kFastScoreH;   // score region of a tile
+constexpr int TROWS = FSR + 6, TWORDS = FW / 4 + 2;  // tile rows, 32-bit words per tile row
+constexpr int TPITCH = TWORDS * 4;
+constexpr int RPW = FSR / 8;                          // score rows per warp
+constexpr int QCAP = FW * FSR;
+constexpr int OCAP = (kFastEmitW / 2 + 1) * (kFastEmitH / 2 + 1);
 
-__device__ __forceinline__ unsigned has_run9(unsigned m) {
-    m |= m << 16;
-    unsigned x = m & (m >> 1);
-    x &= x >> 2;
-    x &= x >> 4;
-    x &= m >> 8;
-    return x & 0xffffu;
+// ring offsets (dx, dy), k = 0..15, as byte offsets into the tile
+__device__ __forceinline__ constexpr int ring_off(int k) {
+    constexpr int dx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
+    constexpr int dy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+    return dy[k] * TPITCH + dx[k];
 }
 
-// class bits of ring pixel p against centre band [lo, hi]: 1 = darker, 2 = brighter
-__device__ __forceinline__ unsigned cls(int p, int lo, int hi) {
-    return (p < lo ? 1u : 0u) | (p > hi ? 2u : 0u);
+// per-byte flag (bit 7) of d > t
+template <bool HI>
+__device__ __forceinline__ uint32_t gt_flags(uint32_t d, uint32_t c) {
+    const uint32_t lo = (d & 0x7f7f7f7fu) + c;
+    return HI ? (lo & d) : (lo | d);
 }
 
 }  // namespace
 
+template <bool HI>
 __global__ void __launch_bounds__(256)
 fast_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand,
             int* __restrict__ cand_n, int threshold, int border) {
-    __shared__ __align__(16) uint8_t tile[SMH][SMW];
-    __shared__ uint8_t score[SCH][SCP];
-    __shared__ uint16_t queue[QCAP];
+    __shared__ __align__(16) uint32_t tile[TROWS][TWORDS];
+    __shared__ __align__(16) uint8_t score[FSR][FW];
+    __shared__ uint32_t queue[QCAP / 2];  // u16 entries: row * 128 + col in the score region
     __shared__ uint32_t outq[OCAP];
     __shared__ int qn, on, obase;
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int l = 0;
-    {
-        const int t = blockIdx.x;
-        while (l + 1 < lt.n_levels && t >= lt.fast_tile_begin[l + 1]) ++l;
-    }
+    while (l + 1 < lt.n_levels && (int)blockIdx.x >= lt.fast_tile_begin[l + 1]) ++l;
     const int tl = blockIdx.x - lt.fast_tile_begin[l];
     const int tx = tl % lt.fast_tiles_x[l], ty = tl / lt.fast_tiles_x[l];
     const int f = blockIdx.y;
     const int w = lt.w[l], h = lt.h[l], pitch = lt.pitch[l];
     const uint8_t* img = pyr + lt.off[l] + (size_t)f * lt.fstride[l];
 
-    const int ox = border + tx * TW, oy = border + ty * TH;  // tile origin in the emission domain
-    const int x_al = (ox - 4) & ~15;                          // 16 B aligned left edge of the load
-    const int ry0 = oy - 4;
-    const int cx0 = ox - x_al;                                // shared column of pixel ox
+    // score region origin: X is a multiple of 4 so tile words are aligned words of the plane
+    const int X = ((border - 1) & ~3) + tx * kFastEmitW;
+    const int Y = (border - 1) + ty * kFastEmitH;
 
-    for (int i = tid; i < SMH * (SMW / 16); i += 256) {
-        const int r = i / (SMW / 16), c = i % (SMW / 16);
-        const int gy = ry0 + r, gx = x_al + c * 16;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (gy >= 0 && gy < h && gx >= 0 && gx < pitch)
-            v = __ldg(reinterpret_cast<const uint4*>(img + (size_t)gy * pitch + gx));
-        *reinterpret_cast<uint4*>(&tile[r][c * 16]) = v;
-    }
-    for (int i = tid; i < SCH * SCP; i += 256) (&score[0][0])[i] = 0;
-    if (tid == 0) {
-        qn = 0;
-        on = 0;
+    {
+        const int max_word = (pitch - kApronX) / 4 - 1;  // last whole word of a plane row
+        for (int i = tid; i < TROWS * TWORDS; i += 256) {
+            const int r = i / TWORDS, c = i - r * TWORDS;
+            const int gy = min(max(Y - 3 + r, -kApronY), h + kApronY - 1);
+            const int gw = min(max(X / 4 - 1 + c, -(kApronX / 4)), max_word);
+            tile[r][c] = __ldg(reinterpret_cast<const uint32_t*>(img + (ptrdiff_t)gy * pitch) + gw);
+        }
+        for (int i = tid; i < FSR * FW / 16; i += 256) reinterpret_cast<uint4*>(&score[0][0])[i] = make_uint4(0, 0, 0, 0);
+        if (tid == 0) {
+            qn = 0;
+            on = 0;
+        }
     }
     __syncthreads();
 
     // score domain (global coordinates, inclusive)
     const int sx_min = max(3, border - 1), sx_max = min(w - 4, w - border);
     const int sy_min = max(3, border - 1), sy_max = min(h - 4, h - border);
-    const int lane = tid & 31;
 
-    // ---- pass A: quick reject on the 4 opposite pairs of compass / diagonal points ------------
-    for (int i0 = 0; i0 < QCAP; i0 += 256) {
-        const int i = i0 + tid;
-        bool pass = false;
-        int lx = 0, ly = 0;
-        if (i < QCAP) {
-            lx = i % SCW - 1;
-            ly = i / SCW - 1;
-            const int gx = ox + lx, gy = oy + ly;
-            if (gx >= sx_min && gx <= sx_max && gy >= sy_min && gy <= sy_max) {
-                const uint8_t* c = &tile[ly + 4][lx + cx0];
-                const int v = c[0], lo = v - threshold, hi = v + threshold;
-                unsigned d = cls(c[3 * SMW], lo, hi) | cls(c[-3 * SMW], lo, hi);          // 0, 8
-                if (d) {
-                    d &= cls(c[3], lo, hi) | cls(c[-3], lo, hi);                            // 4, 12
-                    if (d) {
-                        d &= cls(c[2 * SMW + 2], lo, hi) | cls(c[-2 * SMW - 2], lo, hi);   // 2, 10
-                        d &= cls(c[-2 * SMW + 2], lo, hi) | cls(c[2 * SMW - 2], lo, hi);   // 6, 14
-                        pass = d != 0;
-                    }
-                }
-            }
+    // ---- stage 1: 4-pixel-wide necessary-condition test ---------------------------------------
+    {
+        uint32_t colmask = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gx = X + 4 * lane + j;
+            if (gx >= sx_min && gx <= sx_max) colmask |= 0x80u << (8 * j);
         }
-        const unsigned m = __ballot_sync(0xffffffffu, pass);
-        if (m) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(&qn, __popc(m));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (pass) queue[base + __popc(m & ((1u << lane) - 1u))] = (uint16_t)((ly + 1) * SCW + (lx + 1));
+        const uint32_t cadd = (uint32_t)(HI ? 255 - threshold : 127 - threshold) * 0x01010101u;
+        uint32_t acc = 0;
+#pragma unroll
+        for (int i = 0; i < RPW; ++i) {
+            const int r = warp * RPW + i;
+            const int gy = Y + r;
+            uint32_t q = 0;
+            if (gy >= sy_min && gy <= sy_max) {
+                const uint32_t* row = &tile[r + 3][lane];
+                const uint32_t wl = row[0], v = row[1], wr = row[2];
+                const uint32_t up = tile[r][lane + 1], dn = tile[r + 6][lane + 1];
+                const uint32_t lf = __byte_perm(wl, v, 0x4321u), rt = __byte_perm(v, wr, 0x6543u);
+                const uint32_t f0 = gt_flags<HI>(__vabsdiffu4(dn, v), cadd);
+                const uint32_t f8 = gt_flags<HI>(__vabsdiffu4(up, v), cadd);
+                const uint32_t f4 = gt_flags<HI>(__vabsdiffu4(rt, v), cadd);
+                const uint32_t f12 = gt_flags<HI>(__vabsdiffu4(lf, v), cadd);
+                q = (f0 | f8) & (f4 | f12) & colmask;
+            }
+            // bits 7/15/23/31 -> bits 28..31 (distinct partial products, no carries)
+            acc = (acc >> 4) | ((q * 0x00204081u) & 0xF0000000u);
+        }
+        acc >>= 32 - 4 * RPW;  // row i of this warp now sits in bits 4i .. 4i+3
+        // compaction: one inclusive prefix sum per warp, one shared atomic per warp
+        const int cnt = __popc(acc);
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += n;
+        }
+        int base = 0;
+        if (lane == 31 && incl > 0) base = atomicAdd(&qn, incl);
+        base = __shfl_sync(0xffffffffu, base, 31);
+        int pos = base + incl - cnt;
+        uint16_t* q16 = reinterpret_cast<uint16_t*>(queue);
+        const int rowbase = warp * RPW * FW + 4 * lane;
+        while (acc) {
+            const int b = __ffs(acc) - 1;
+            acc &= acc - 1;
+            q16[pos++] = (uint16_t)(rowbase + (b >> 2) * FW + (b & 3));
         }
     }
     __syncthreads();
     const int nq = qn;
 
-    // ---- pass B: full segment test and score --------------------------------------------------
-    for (int q = tid; q < nq; q += 256) {
-        const int e = queue[q];
-        const int lx = e % SCW - 1, ly = e / SCW - 1;
-        const uint8_t* c = &tile[ly + 4][lx + cx0];
-        const int v = c[0];
-        int d[16];
-        d[0] = v - c[3 * SMW];
-        d[1] = v - c[3 * SMW + 1];
-        d[2] = v - c[2 * SMW + 2];
-        d[3] = v - c[SMW + 3];
-        d[4] = v - c[3];
-        d[5] = v - c[-SMW + 3];
-        d[6] = v - c[-2 * SMW + 2];
-        d[7] = v - c[-3 * SMW + 1];
-        d[8] = v - c[-3 * SMW];
-        d[9] = v - c[-3 * SMW - 1];
-        d[10] = v - c[-2 * SMW - 2];
-        d[11] = v - c[-SMW - 3];
-        d[12] = v - c[-3];
-        d[13] = v - c[SMW - 3];
-        d[14] = v - c[2 * SMW - 2];
-        d[15] = v - c[3 * SMW - 1];
-        unsigned bm = 0, dm = 0;
+    // ---- stage 2: cornerScore of two queued pixels per thread ---------------------------------
+    {
+        const uint8_t* t8 = reinterpret_cast<const uint8_t*>(&tile[0][0]) + 3 * TPITCH + 4;
+        const int pairs = (nq + 1) >> 1;
+        for (int pi = tid; pi < pairs; pi += 256) {
+            const uint32_t u = queue[pi];
+            const int ia = (int)(u & 0xffffu);
+            const int ib = (2 * pi + 1 < nq) ? (int)(u >> 16) : ia;
+            const uint8_t* ta = t8 + (ia >> 7) * TPITCH + (ia & 127);
+            const uint8_t* tb = t8 + (ib >> 7) * TPITCH + (ib & 127);
+            const uint32_t va = ta[0], vb = tb[0];
+            const uint32_t nv = ((0u - va) & 0xffffu) | ((0u - vb) << 16);
+            uint32_t d[16];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            bm |= (d[k] < -threshold ? 1u : 0u) << k;  // ring pixel brighter than v + t
-            dm |= (d[k] > threshold ? 1u : 0u) << k;   // ring pixel darker than v - t
-        }
-        if (has_run9(bm) | has_run9(dm)) {
-            // packed s16x2: low half d, high half -d; sliding minima over windows of 9
-            unsigned p[16], m2[16], m4[16];
-#pragma unroll
-            for (int k = 0; k < 16; ++k) p[k] = ((unsigned)d[k] & 0xffffu) | ((unsigned)(-d[k]) << 16);
-#pragma unroll
-            for (int k = 0; k < 16; ++k) m2[k] = __vmins2(p[k], p[(k + 1) & 15]);
-#pragma unroll
-            for (int k = 0; k < 16; ++k) m4[k] = __vmins2(m2[k], m2[(k + 2) & 15]);
-            unsigned best = 0x80008000u;
+            for (int k = 0; k < 16; ++k)
+                d[k] = __vadd2((uint32_t)ta[ring_off(k)] | ((uint32_t)tb[ring_off(k)] << 16), nv);  // p_k - v
+            uint32_t lo3[16], hi3[16];
 #pragma unroll
             for (int k = 0; k < 16; ++k) {
-                unsigned m8 = __vmins2(m4[k], m4[(k + 4) & 15]);
-                best = __vmaxs2(best, __vmins2(m8, p[(k + 8) & 15]));
+                lo3[k] = __vimin3_s16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+                hi3[k] = __vimax3_s16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
             }
-            const int a = (int)(short)(best & 0xffffu), b = (int)(short)(best >> 16);
-            score[ly + 1][lx + 1] = (uint8_t)(max(a, b) - 1);
+            uint32_t lo9[16], hi9[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                lo9[k] = __vimin3_s16x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
+                hi9[k] = __vimax3_s16x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
+            }
+            uint32_t bb = lo9[15], bd = hi9[15];
+#pragma unroll
+            for (int k = 0; k < 15; k += 3) {
+                bb = __vimax3_s16x2(bb, lo9[k], lo9[k + 1]);
+                bb = __vmaxs2(bb, lo9[k + 2]);
+                bd = __vimin3_s16x2(bd, hi9[k], hi9[k + 1]);
+                bd = __vmins2(bd, hi9[k + 2]);
+            }
+            // bright score = max_arcs min(p - v); dark score = max_arcs min(v - p) = -min_arcs max(p - v)
+            const int sa = max((int)(short)(bb & 0xffffu), -(int)(short)(bd & 0xffffu)) - 1;
+            const int sb = max((int)bb >> 16, -((int)bd >> 16)) - 1;
+            if (sa >= threshold) (&score[0][0])[ia] = (uint8_t)sa;
+            if (sb >= threshold) (&score[0][0])[ib] = (uint8_t)sb;
         }
     }
     __syncthreads();
 
-    // ---- pass C: strict 3x3 non-max suppression over the emission domain ----------------------
-    const int ex_max = w - border, ey_max = h - border;  // exclusive
-    for (int q = tid; q < nq; q += 256) {
-        const int e = queue[q];
-        const int sx = e % SCW, sy = e / SCW;  // score-map coordinates (= local + 1)
-        const int lx = sx - 1, ly = sy - 1;
-        const int s = score[sy][sx];
-        if (s == 0 || lx < 0 || lx >= TW || ly < 0 || ly >= TH) continue;
-        const int gx = ox + lx, gy = oy + ly;
-        if (gx >= ex_max || gy >= ey_max) continue;
-        const uint8_t* r = &score[sy][sx];
-        if (s > r[-SCP - 1] && s > r[-SCP] && s > r[-SCP + 1] && s > r[-1] && s > r[1] && s > r[SCP - 1] &&
-            s > r[SCP] && s > r[SCP + 1]) {
-            const int o = atomicAdd(&on, 1);
-            outq[o] = ((uint32_t)s << 24) | ((uint32_t)gy << 12) | (uint32_t)gx;
+    // ---- stage 3: strict 3x3 non-max suppression over the emission region ----------------------
+    {
+        const uint16_t* q16 = reinterpret_cast<const uint16_t*>(queue);
+        const int ex_max = w - border, ey_max = h - border;  // exclusive
+        for (int e = tid; e < nq; e += 256) {
+            const int idx = q16[e];
+            const int r = idx >> 7, c = idx & 127;
+            const int s = (&score[0][0])[idx];
+            if (s == 0 || r < 1 || r > kFastEmitH || c < 1 || c > kFastEmitW) continue;
+            const int gx = X + c, gy = Y + r;
+            if (gx < border || gy < border || gx >= ex_max || gy >= ey_max) continue;
+            const uint8_t* p = &score[r][c];
+            if (s > p[-FW - 1] && s > p[-FW] && s > p[-FW + 1] && s > p[-1] && s > p[1] && s > p[FW - 1] &&
+                s > p[FW] && s > p[FW + 1]) {
+                const int o = atomicAdd(&on, 1);
+                outq[o] = ((uint32_t)s << 24) | ((uint32_t)gy << 12) | (uint32_t)gx;
+            }
         }
     }
     __syncthreads();
@@ -207,7 +229,10 @@ int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int 
     const int tiles = lt.fast_tile_begin[lt.n_levels];
     if (tiles == 0) return 0;
     dim3 grid(tiles, lt.batch);
-    fast_kernel<<<grid, 256, 0, s>>>(lt, db.pyr, db.cand, db.cand_n, threshold, border);
+    if (threshold >= 128)
+        fast_kernel<true><<<grid, 256, 0, s>>>(lt, db.pyr, db.cand, db.cand_n, threshold, border);
+    else
+        fast_kernel<false><<<grid, 256, 0, s>>>(lt, db.pyr, db.cand, db.cand_n, threshold, border);
     return 1;
 }
 

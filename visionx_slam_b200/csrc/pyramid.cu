@@ -116,6 +116,55 @@ int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) 
     return launches;
 }
 
+// Reflect-101 apron (3 px) around every level of every frame, so the blur reads straight through
+// the image border exactly as cv::GaussianBlur(BORDER_REFLECT_101) sees it.  One thread per apron
+// pixel; items of a level: rows -3..-1 and h..h+2 over x in [-3, w+2], then columns -3..-1 and
+// w..w+2 over y in [0, h).
+__device__ __forceinline__ int reflect101(int i, int n) {
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) {
+        if (i < 0) i = -i;
+        if (i >= n) i = 2 * (n - 1) - i;
+    }
+    return i;
+}
+
+__global__ void __launch_bounds__(256) apron_kernel(const LevelTab lt, uint8_t* __restrict__ pyr) {
+    int idx = blockIdx.x * 256 + threadIdx.x;
+    const int f = blockIdx.y;
+    for (int l = 0; l < lt.n_levels; ++l) {
+        const int w = lt.w[l], h = lt.h[l];
+        const int horiz = 2 * kApronY * (w + 2 * kApronY), vert = 2 * kApronY * h;
+        if (idx < horiz + vert) {
+            int x, y;
+            if (idx < horiz) {
+                const int r = idx / (w + 2 * kApronY);
+                x = idx - r * (w + 2 * kApronY) - kApronY;
+                y = r < kApronY ? r - kApronY : h + (r - kApronY);
+            } else {
+                const int j = idx - horiz;
+                y = j / (2 * kApronY);
+                const int c = j - y * (2 * kApronY);
+                x = c < kApronY ? c - kApronY : w + (c - kApronY);
+            }
+            uint8_t* img = pyr + lt.off[l] + (size_t)f * lt.fstride[l];
+            const int pitch = lt.pitch[l];
+            img[(ptrdiff_t)y * pitch + x] = img[(ptrdiff_t)reflect101(y, h) * pitch + reflect101(x, w)];
+            return;
+        }
+        idx -= horiz + vert;
+    }
+}
+
+int launch_apron(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
+    int items = 0;
+    for (int l = 0; l < lt.n_levels; ++l) items += 2 * kApronY * (lt.w[l] + 2 * kApronY) + 2 * kApronY * lt.h[l];
+    if (items == 0) return 0;
+    dim3 grid((items + 255) / 256, lt.batch);
+    apron_kernel<<<grid, 256, 0, s>>>(lt, db.pyr);
+    return 1;
+}
+
 // Streams `bytes` of writes so the next kernel starts from a cold L2 (bench hygiene).
 __global__ void flush_kernel(uint4* p, size_t n16, uint32_t tag) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -2,8 +2,9 @@
 //
 // Data layout in HBM.  Everything is level-major so that one launch covers all
 // frames of a batch with blockIdx.{y|z} = frame:
-//   pyr / blur : for level l, frame f, row y : base + off[l] + f*fstride[l] + y*pitch[l]
-//                (u8, pitch = width rounded up to 32 B, planes 256 B aligned)
+//   pyr / blur : for level l, frame f, pixel (x, y) : base + off[l] + f*fstride[l] + y*pitch[l] + x
+//                (u8; off[l] is pixel (0,0) of frame 0, 16 B aligned; each plane has a 3-px
+//                reflect-101 apron around it, see kApron*; planes 256 B aligned)
 //   cand       : FAST corners after NMS, packed u32 = score<<24 | y<<12 | x, per (level, frame)
 //   resp       : Harris response per candidate slot (f32), written only for retained candidates
 //   fin        : final per-level keypoints (packed key, response), sorted by (y, x)
@@ -23,6 +24,31 @@ constexpr int kMaxLevels = VXORB_MAX_LEVELS;
 constexpr int kEdge = 31;        // cv::ORB edgeThreshold (only value supported)
 constexpr int kHalfPatch = 15;   // patchSize 31
 constexpr int kPitchAlign = 32;
+// Every pyramid / blurred plane carries a reflect-101 apron so stencil kernels need no border
+// logic: kApronY rows above and below, kApronX bytes left of pixel (0,0) (keeps it 16 B aligned)
+// and at least kApronRight bytes after pixel (w-1).  The apron holds 3 valid reflected pixels.
+constexpr int kApronY = 3;
+constexpr int kApronX = 16;
+constexpr int kApronRight = 8;
+constexpr int kBlurRows = 64;    // output rows per blur strip
+
+// FAST tiling (fast.cu): a CTA computes scores for kFastScoreW x kFastScoreH pixels and emits corners
+// from the inner kFastEmitW x kFastEmitH; tile origins are multiples of 4 px in x.
+constexpr int kFastScoreW = 128, kFastScoreH = 40;
+constexpr int kFastEmitW = 124, kFastEmitH = 38;
+inline int fast_tiles_x(int w, int border) {
+    const int first = ((border - 1) & ~3) + 1;  // first emission column a tile row can cover
+    const int span = (w - border) - first;
+    return span > 0 ? (span + kFastEmitW - 1) / kFastEmitW : 0;
+}
+inline int fast_tiles_y(int h, int border) {
+    const int span = h - 2 * border;
+    return span > 0 ? (span + kFastEmitH - 1) / kFastEmitH : 0;
+}
+
+inline int plane_pitch(int w) { return (kApronX + w + kApronRight + kPitchAlign - 1) / kPitchAlign * kPitchAlign; }
+inline size_t plane_bytes(int w, int h) { return (size_t)plane_pitch(w) * (size_t)(h + 2 * kApronY); }
+inline size_t plane_origin(int w) { return (size_t)kApronY * plane_pitch(w) + kApronX; }
 
 // Per-geometry tables passed to kernels by value (kernel parameters live in the constant bank).
 struct LevelTab {
@@ -40,6 +66,7 @@ struct LevelTab {
     unsigned long long fin_off[kMaxLevels];
     // tile bookkeeping: tiles of level l are [tile_begin[l], tile_begin[l+1]) in blockIdx.x
     int fast_tiles_x[kMaxLevels], fast_tile_begin[kMaxLevels + 1];
+    // blur strips: blur_tiles_x = 4-px words per row; CTAs of level l are [blur_tile_begin[l], [l+1])
     int blur_tiles_x[kMaxLevels], blur_tile_begin[kMaxLevels + 1];
     int coef_off[kMaxLevels];        // offset (in u32) of level l's resize tables: x[w_l] then y[h_l]
 };
@@ -72,6 +99,7 @@ int launch_gray_from_bgr(const uint8_t* bgr, size_t bgr_pitch, size_t bgr_fstrid
 int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh,
                          int dpitch, const uint32_t* xtab, const uint32_t* ytab, cudaStream_t s);
+int launch_apron(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s);
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_blur(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
