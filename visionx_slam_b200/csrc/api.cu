@@ -190,6 +190,7 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
             coef.resize((size_t)coef_off + lt.w[l] + lt.h[l]);
             build_resize_taps(lt.w[l - 1], lt.w[l], coef.data() + coef_off);
             build_resize_taps(lt.h[l - 1], lt.h[l], coef.data() + coef_off + lt.w[l]);
+            lt.resize_fast[l] = resize_taps_fit_fast_path(coef.data() + coef_off, lt.w[l]) ? 1 : 0;
             coef_off += lt.w[l] + lt.h[l];
         }
     }
@@ -1024,19 +1025,26 @@ int vxorb_debug_resize(vxorb_handle* h, const uint8_t* src, int sw, int sh, size
     if (!src || !dst || sw < 1 || sh < 1 || dw < 1 || dh < 1 || sw >= 65536 || sh >= 65536)
         return fail(h, VXORB_E_INVALID, "bad resize arguments");
     CK(cudaSetDevice(h->p.device_id));
-    const int sp = (int)align_up((size_t)sw, kPitchAlign), dp = (int)align_up((size_t)dw, kPitchAlign);
-    int rc = ensure_stage_scratch(h, std::max((size_t)sp * sh, (size_t)dp * dh) + (size_t)(dw + dh) * 4 + 256);
+    // source and destination live in apron planes like the pyramid levels (the kernels read whole
+    // aligned words around the taps)
+    const int sp = plane_pitch(sw), dp = plane_pitch(dw);
+    const size_t sbytes = align_up(plane_bytes(sw, sh), 256), dbytes = align_up(plane_bytes(dw, dh), 256);
+    int rc = ensure_stage_scratch(h, std::max(sbytes, dbytes) + (size_t)(dw + dh) * 4 + 256);
     if (rc) return rc;
     cudaStream_t s = h->ws[0].stream;
     std::vector<uint32_t> taps((size_t)dw + dh);
     build_resize_taps(sw, dw, taps.data());
     build_resize_taps(sh, dh, taps.data() + dw);
-    uint32_t* d_taps = reinterpret_cast<uint32_t*>(h->s_b + align_up((size_t)dp * dh, 256));
-    CK(cudaMemcpy2DAsync(h->s_a, sp, src, sstride, sw, sh, cudaMemcpyHostToDevice, s));
+    uint32_t* d_taps = reinterpret_cast<uint32_t*>(h->s_b + dbytes);
+    uint8_t* s0 = h->s_a + plane_origin(sw);
+    uint8_t* d0 = h->s_b + plane_origin(dw);
+    CK(cudaMemsetAsync(h->s_a, 0, sbytes, s));
+    CK(cudaMemcpy2DAsync(s0, sp, src, sstride, sw, sh, cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(d_taps, taps.data(), taps.size() * 4, cudaMemcpyHostToDevice, s));
-    h->launches += launch_resize_single(h->s_a, sw, sh, sp, h->s_b, dw, dh, dp, d_taps, d_taps + dw, s);
+    h->launches += launch_resize_single(s0, sw, sh, sp, d0, dw, dh, dp, d_taps, d_taps + dw,
+                                        resize_taps_fit_fast_path(taps.data(), dw), s);
     CK(cudaGetLastError());
-    CK(cudaMemcpy2DAsync(dst, dstride, h->s_b, dp, dw, dh, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpy2DAsync(dst, dstride, d0, dp, dw, dh, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     return VXORB_OK;
 }

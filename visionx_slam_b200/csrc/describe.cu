@@ -5,11 +5,19 @@
 // what ORBExtractor::Extract copies into Frame::Features() / Frame::Descriptors()
 // (orb_extractor.cpp:19-26), in canonical (octave, y, x) order.
 //
-// One warp per keypoint:
-//   orientation  lane j owns column u = j-15 of the radius-15 disc, integer moments, REDUX sum,
-//                fastAtan2 polynomial evaluated with un-fused float ops (degrees)
-//   descriptor   lane i produces byte i: 8 comparisons of blurred pixels at pattern points rotated
-//                by the angle (double cos/sin, float un-fused rotate, round-half-even)
+// One warp owns a group of G consecutive keypoints of one frame (G = 16, or 4 for tiny batches):
+//   setup        lane i looks up keypoint i of the group (level, x, y, response); every lane keeps
+//                the 16 pattern points of "its" descriptor byte as floats in registers and the
+//                disc weights of "its" patch row (u values and a 0/1 mask as s8x4 / u8x4 words)
+//   orientation  per keypoint: lane = patch row v; nine aligned 32-bit loads, a funnel shift to
+//                the patch origin, then IDP.4A does the work: m10 += dp4a(pixels, u-weights),
+//                rowsum += dp4a(pixels, mask), m01 += v*rowsum; two REDUX adds per keypoint
+//   angle        all lanes at once, lane i for keypoint i: fastAtan2 polynomial with un-fused
+//                float ops (degrees), then cos/sin in double — once per group instead of once
+//                per keypoint-warp
+//   descriptor   per keypoint: lane i produces byte i: 8 comparisons of blurred pixels at pattern
+//                points rotated by the angle (float un-fused rotate, round-half-even via the
+//                1.5*2^23 trick so the rounded coordinates feed the address IMAD directly)
 // Float rules are load-bearing: every op is an explicit *_rn intrinsic so nvcc cannot contract.
 #include <float.h>
 
@@ -59,17 +67,24 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 
 }  // namespace
 
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ int dp4a_us(uint32_t pixels, uint32_t weights_s8, int acc) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pixels), "r"(weights_s8), "r"(acc));
+    return d;
+}
+
+__global__ void __launch_bounds__(128)
 describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                 const uint32_t* __restrict__ fin_key, const float* __restrict__ fin_resp,
-                const int* __restrict__ fin_n, int kp_cap, vxorb_keypoint* __restrict__ kp_out,
+                const int* __restrict__ fin_n, int kp_cap, int group, vxorb_keypoint* __restrict__ kp_out,
                 uint8_t* __restrict__ desc_out, float* __restrict__ xy_out, int* __restrict__ kp_n,
                 int* __restrict__ kp_total, int* __restrict__ status) {
     const int f = blockIdx.y;
     const int lane = threadIdx.x & 31;
-    const int g = blockIdx.x * 8 + (threadIdx.x >> 5);  // keypoint index inside the frame
+    const int g0 = (blockIdx.x * 4 + (threadIdx.x >> 5)) * group;  // first keypoint of this warp's group
 
-    // locate (level, index in level) from the per-level counts
+    // ---- setup: locate keypoint g0 + lane from the per-level counts -----------------------------
+    const int g = g0 + lane;
     int level = -1, idx = 0, total = 0;
     for (int l = 0; l < lt.n_levels; ++l) {
         const int cnt = min(fin_n[l * lt.batch + f], lt.fin_cap[l]);
@@ -79,58 +94,91 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
         }
         total += cnt;
     }
-    if (g == 0 && lane == 0) {
+    if (g0 == 0 && lane == 0) {
         kp_n[f] = min(total, kp_cap);
         kp_total[f] = total;
         if (total > kp_cap) atomicOr(status, 4);
     }
-    if (level < 0 || g >= kp_cap) return;
-
-    const int fcap = lt.fin_cap[level];
-    const uint32_t key = fin_key[lt.fin_off[level] + (size_t)f * fcap + idx];
-    const float response = fin_resp[lt.fin_off[level] + (size_t)f * fcap + idx];
-    const int x = (int)(key & 0xfffu), y = (int)((key >> 12) & 0xfffu);
-    const int pitch = lt.pitch[level];
-    const size_t plane = lt.off[level] + (size_t)f * lt.fstride[level];
-
-    // ---- orientation: m10 = sum u*I, m01 = sum v*I over the radius-15 disc --------------------
-    const uint8_t* c = pyr + plane + (size_t)y * pitch + x;
-    const int u = lane - 15;
-    const int au = abs(u);
-    int m10 = 0, m01 = 0;
-    if (lane < 31) {
-        const int vm = umax_of(au);
-        for (int v = -vm; v <= vm; ++v) {
-            const int p = __ldg(c + (ptrdiff_t)v * pitch + u);
-            m10 += u * p;
-            m01 += v * p;
-        }
+    const int n_here = min(group, min(total, kp_cap) - g0);  // keypoints this warp processes
+    if (n_here <= 0) return;
+    const bool mine = lane < n_here;
+    int x = 0, y = 0;
+    float response = 0.f;
+    if (mine) {
+        const int fcap = lt.fin_cap[level];
+        const uint32_t key = fin_key[lt.fin_off[level] + (size_t)f * fcap + idx];
+        response = fin_resp[lt.fin_off[level] + (size_t)f * fcap + idx];
+        x = (int)(key & 0xfffu);
+        y = (int)((key >> 12) & 0xfffu);
+    } else {
+        level = 0;
     }
-    m10 = __reduce_add_sync(0xffffffffu, m10);
-    m01 = __reduce_add_sync(0xffffffffu, m01);
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-    // ---- rotated BRIEF ------------------------------------------------------------------------
-    const float ang = __fmul_rn(angle, (float)(3.141592653589793238462643383279502884 / 180.f));
-    const float ca = (float)cos((double)ang), sa = (float)sin((double)ang);
-    const uint8_t* bc = blur + plane + (size_t)y * pitch + x;
-    unsigned byte = 0;
+    // this lane's pattern points (byte `lane` of the descriptor) as floats
+    float px[16], py[16];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         const char4 pp = g_pattern.p[k][lane];
-        const float x1 = (float)pp.x, y1 = (float)pp.y, x2 = (float)pp.z, y2 = (float)pp.w;
-        const int ix1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sa)));
-        const int iy1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));
-        const int ix2 = __float2int_rn(__fsub_rn(__fmul_rn(x2, ca), __fmul_rn(y2, sa)));
-        const int iy2 = __float2int_rn(__fadd_rn(__fmul_rn(x2, sa), __fmul_rn(y2, ca)));
-        const int t0 = __ldg(bc + (ptrdiff_t)iy1 * pitch + ix1);
-        const int t1 = __ldg(bc + (ptrdiff_t)iy2 * pitch + ix2);
-        byte |= (t0 < t1 ? 1u : 0u) << k;
+        px[2 * k] = (float)pp.x;
+        py[2 * k] = (float)pp.y;
+        px[2 * k + 1] = (float)pp.z;
+        py[2 * k + 1] = (float)pp.w;
     }
-    const size_t row = (size_t)f * kp_cap + g;
-    desc_out[row * 32 + lane] = (uint8_t)byte;
-    if (lane == 0) {
+    // this lane's patch row v = lane - 15: weights for u = -15 .. 16 (8 words)
+    const int v = lane - 15;
+    const int um = lane < 31 ? umax_of(abs(v)) : -1;
+    uint32_t wu[8], wm[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        uint32_t a = 0, m = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int u = 4 * j + b - 15;
+            if (abs(u) <= um) {
+                a |= ((uint32_t)u & 0xffu) << (8 * b);
+                m |= 1u << (8 * b);
+            }
+        }
+        wu[j] = a;
+        wm[j] = m;
+    }
+
+    // ---- orientation moments, one keypoint at a time, lane = patch row --------------------------
+    int my_m10 = 0, my_m01 = 0;
+    for (int i = 0; i < n_here; ++i) {
+        const int kx = __shfl_sync(0xffffffffu, x, i), ky = __shfl_sync(0xffffffffu, y, i);
+        const int kl = __shfl_sync(0xffffffffu, level, i);
+        const int pitch = lt.pitch[kl];
+        const uint8_t* row = pyr + lt.off[kl] + (size_t)f * lt.fstride[kl] + (ptrdiff_t)(ky + min(v, 15)) * pitch + (kx - 15);
+        const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(row) & 3u) * 8u;
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(row) & ~(uintptr_t)3);
+        uint32_t wd[9];
+#pragma unroll
+        for (int j = 0; j < 9; ++j) wd[j] = __ldg(wp + j);
+        int m10 = 0;
+        uint32_t rs = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t a = __funnelshift_r(wd[j], wd[j + 1], sh);
+            m10 = dp4a_us(a, wu[j], m10);
+            rs = __dp4a(a, wm[j], rs);
+        }
+        int m01 = v * (int)rs;
+        m10 = __reduce_add_sync(0xffffffffu, m10);
+        m01 = __reduce_add_sync(0xffffffffu, m01);
+        if (lane == i) {
+            my_m10 = m10;
+            my_m01 = m01;
+        }
+    }
+
+    // ---- angle, cos/sin and the keypoint record: lane i for keypoint i --------------------------
+    const float angle = fast_atan2_deg((float)my_m01, (float)my_m10);
+    const float ang = __fmul_rn(angle, (float)(3.141592653589793238462643383279502884 / 180.f));
+    float ca = (float)cos((double)ang), sa = (float)sin((double)ang);
+    if (mine) {
         const float sc = lt.scale[level];
+        const size_t row = (size_t)f * kp_cap + g;
         vxorb_keypoint kp;
         kp.x = __fmul_rn((float)x, sc);
         kp.y = __fmul_rn((float)y, sc);
@@ -140,6 +188,33 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
         kp_out[row] = kp;
         xy_out[row * 2] = kp.x;
         xy_out[row * 2 + 1] = kp.y;
+    }
+
+    // ---- rotated BRIEF, one keypoint at a time, lane = descriptor byte ---------------------------
+    const float magic = 12582912.0f;  // 1.5 * 2^23: low mantissa bits of (t + magic) = round-half-even(t)
+    for (int i = 0; i < n_here; ++i) {
+        const int kx = __shfl_sync(0xffffffffu, x, i), ky = __shfl_sync(0xffffffffu, y, i);
+        const int kl = __shfl_sync(0xffffffffu, level, i);
+        const float c = __shfl_sync(0xffffffffu, ca, i), s = __shfl_sync(0xffffffffu, sa, i);
+        const int pitch = lt.pitch[kl];
+        // address = centre + iy*pitch + ix with iy = bits(ty) - bits(magic), ix likewise
+        const uint8_t* bc = blur + lt.off[kl] + (size_t)f * lt.fstride[kl] + (ptrdiff_t)ky * pitch + kx -
+                            (ptrdiff_t)0x4B400000 * pitch - (ptrdiff_t)0x4B400000;
+        unsigned byte = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            int t[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const float xx = px[2 * k + e], yy = py[2 * k + e];
+                const float rx = __fsub_rn(__fmul_rn(xx, c), __fmul_rn(yy, s));
+                const float ry = __fadd_rn(__fmul_rn(xx, s), __fmul_rn(yy, c));
+                const int bx = __float_as_int(__fadd_rn(rx, magic)), by = __float_as_int(__fadd_rn(ry, magic));
+                t[e] = __ldg(bc + (ptrdiff_t)by * pitch + bx);
+            }
+            byte |= (t[0] < t[1] ? 1u : 0u) << k;
+        }
+        desc_out[((size_t)f * kp_cap + g0 + i) * 32 + lane] = (uint8_t)byte;
     }
 }
 
@@ -155,8 +230,12 @@ cudaError_t init_device_tables() {
 }
 
 int launch_describe(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, cudaStream_t s) {
-    dim3 grid((kp_cap + 7) / 8, lt.batch);
-    describe_kernel<<<grid, 256, 0, s>>>(lt, db.pyr, db.blur, db.fin_key, db.fin_resp, db.fin_n, kp_cap, db.kp,
+    // 16 keypoints per warp amortise the per-group trigonometry; tiny batches use 4 so that one
+    // frame still spreads over ~80 CTAs
+    const int group = lt.batch >= 8 ? 16 : 4;
+    const int warps = (kp_cap + group - 1) / group;
+    dim3 grid((warps + 3) / 4, lt.batch);
+    describe_kernel<<<grid, 128, 0, s>>>(lt, db.pyr, db.blur, db.fin_key, db.fin_resp, db.fin_n, kp_cap, group, db.kp,
                                          db.desc, db.xy, db.kp_n, db.kp_total, db.status);
     return 1;
 }

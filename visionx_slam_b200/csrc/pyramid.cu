@@ -53,13 +53,13 @@ __global__ void __launch_bounds__(256) bgr2gray_kernel(const uint8_t* __restrict
     *reinterpret_cast<uint32_t*>(dst + (size_t)blockIdx.z * fstride + (size_t)y * pitch + x0) = out;
 }
 
-// One thread produces four horizontally adjacent output pixels (one 32-bit store).  A block of
-// 32x8 threads covers a 128x8 output strip; its source footprint (~154 B x ~10 rows at 1.2x) is
-// read through L1 with the two source rows of a thread adjacent in memory.
+// Generic path (any scale): one thread produces four horizontally adjacent output pixels with
+// scalar taps.  Used only when four consecutive output columns span more than 8 source bytes
+// (scale factor above ~2); cv::ORB's 1.2 never gets here.
 __global__ void __launch_bounds__(256)
-resize_kernel(const uint8_t* __restrict__ src, int sw, int sh, int spitch, size_t sfstride,
-              uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
-              const uint32_t* __restrict__ xtab, const uint32_t* __restrict__ ytab) {
+resize_generic_kernel(const uint8_t* __restrict__ src, int sw, int sh, int spitch, size_t sfstride,
+                      uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
+                      const uint32_t* __restrict__ xtab, const uint32_t* __restrict__ ytab) {
     const int x0 = (blockIdx.x * 32 + threadIdx.x) * 4;
     const int y = blockIdx.y * 8 + threadIdx.y;
     if (x0 >= dw || y >= dh) return;
@@ -89,6 +89,101 @@ resize_kernel(const uint8_t* __restrict__ src, int sw, int sh, int spitch, size_
     *reinterpret_cast<uint32_t*>(dst + (size_t)y * dpitch + x0) = out;
 }
 
+// Fast path: one thread owns 4 output columns and walks down kResizeRows output rows; a warp owns
+// 128 adjacent output columns of one row band, so the row schedule is warp-uniform.
+//   horizontal pass of one source row: three aligned 32-bit loads cover the <= 8 source bytes the
+//   4 columns need; a funnel shift aligns them to the first tap, two PRMTs (loop-invariant
+//   selectors) gather the (p[i0], p[i0+1]) byte pairs, and IDP.2A multiplies each pair with its
+//   16-bit weights (256-c1, c1): H = p0*c0 + p1*c1 in ONE instruction per column;
+//   the two most recent source rows' H values stay in registers (rows advance ~1.2 per output row);
+//   vertical pass: 2 IMAD per pixel, +2^15, byte 2 of each result packed into one 32-bit store.
+constexpr int kResizeRows = 16;
+
+__global__ void __launch_bounds__(256)
+resize_kernel(const uint8_t* __restrict__ src, int sh, int spitch, size_t sfstride,
+              uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
+              const uint32_t* __restrict__ xtab, const uint32_t* __restrict__ ytab, int word_groups) {
+    const int item = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int band = item / word_groups;
+    const int y0 = band * kResizeRows;
+    if (y0 >= dh) return;
+    const int x0 = ((item - band * word_groups) * 32 + (threadIdx.x & 31)) * 4;
+    if (x0 >= dw) return;
+    src += (size_t)blockIdx.y * sfstride;
+    dst += (size_t)blockIdx.y * dfstride + (size_t)y0 * dpitch + x0;
+
+    // loop-invariant column taps
+    uint32_t wgt[4];
+    int ofs[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t t = __ldg(xtab + min(x0 + k, dw - 1));
+        ofs[k] = (int)(t & 0xffffu);
+        const uint32_t c1 = t >> 16;
+        wgt[k] = (256u - c1) | (c1 << 16);
+    }
+    const uint32_t shift = (uint32_t)(ofs[0] & 3) * 8u;
+    const int e0 = 0, e1 = ofs[1] - ofs[0], e2 = ofs[2] - ofs[0], e3 = ofs[3] - ofs[0];
+    const uint32_t sel01 = (uint32_t)(e0 | ((e0 + 1) << 4) | (e1 << 8) | ((e1 + 1) << 12));
+    const uint32_t sel23 = (uint32_t)(e2 | ((e2 + 1) << 4) | (e3 << 8) | ((e3 + 1) << 12));
+    const uint32_t* sp = reinterpret_cast<const uint32_t*>(src) + (ofs[0] >> 2);
+    const int spitch_w = spitch >> 2;
+
+    uint32_t hp[4] = {0, 0, 0, 0}, hc[4] = {0, 0, 0, 0};  // H of source rows cur-1 and cur
+    int cur = -2;
+    const int rows = min(kResizeRows, dh - y0);
+    for (int i = 0; i < rows; ++i) {
+        const uint32_t ty = __ldg(ytab + y0 + i);
+        const int j0 = (int)(ty & 0xffffu);
+        const uint32_t cy1 = ty >> 16, cy0 = 256u - cy1;
+        if (cur < j0 - 1) cur = j0 - 1;  // first row of the strip (or a jump): restart the pair
+        while (cur < j0 + 1) {
+            ++cur;
+            const uint32_t* p = sp + (size_t)min(cur, sh - 1) * spitch_w;
+            const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+            const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
+            const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) hp[k] = hc[k];
+            hc[0] = __dp2a_lo(wgt[0], b01, 0u);
+            hc[1] = __dp2a_hi(wgt[1], b01, 0u);
+            hc[2] = __dp2a_lo(wgt[2], b23, 0u);
+            hc[3] = __dp2a_hi(wgt[3], b23, 0u);
+        }
+        uint32_t v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = hc[k] * cy1 + (hp[k] * cy0 + (1u << 15));  // 16.16, byte 2 = result
+        *reinterpret_cast<uint32_t*>(dst) =
+            __byte_perm(__byte_perm(v[0], v[1], 0x0062u), __byte_perm(v[2], v[3], 0x0062u), 0x5410u);
+        dst += dpitch;
+    }
+}
+
+// True when every group of 4 output columns reads at most 8 consecutive source bytes.
+bool resize_taps_fit_fast_path(const uint32_t* xtaps, int dw) {
+    for (int x0 = 0; x0 < dw; x0 += 4) {
+        const int last = x0 + 3 < dw ? x0 + 3 : dw - 1;
+        if ((int)(xtaps[last] & 0xffffu) - (int)(xtaps[x0] & 0xffffu) > 6) return false;
+    }
+    return true;
+}
+
+static void launch_resize(const uint8_t* src, int sw, int sh, int spitch, size_t sfstride, uint8_t* dst, int dw,
+                          int dh, int dpitch, size_t dfstride, const uint32_t* xtab, const uint32_t* ytab, int batch,
+                          bool fast, cudaStream_t s) {
+    if (fast) {
+        const int word_groups = ((dw + 3) / 4 + 31) / 32;
+        const int items = word_groups * ((dh + kResizeRows - 1) / kResizeRows);
+        dim3 grid((items + 7) / 8, batch);
+        resize_kernel<<<grid, 256, 0, s>>>(src, sh, spitch, sfstride, dst, dw, dh, dpitch, dfstride, xtab, ytab,
+                                           word_groups);
+    } else {
+        dim3 block(32, 8), grid((dw + 127) / 128, (dh + 7) / 8, batch);
+        resize_generic_kernel<<<grid, block, 0, s>>>(src, sw, sh, spitch, sfstride, dst, dw, dh, dpitch, dfstride, xtab,
+                                                     ytab);
+    }
+}
+
 int launch_gray_from_bgr(const uint8_t* bgr, size_t bgr_pitch, size_t bgr_fstride, uint8_t* dst, int w,
                          int h, int pitch, size_t fstride, int batch, cudaStream_t s) {
     dim3 block(32, 8), grid((w + 127) / 128, (h + 7) / 8, batch);
@@ -97,20 +192,17 @@ int launch_gray_from_bgr(const uint8_t* bgr, size_t bgr_pitch, size_t bgr_fstrid
 }
 
 int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh,
-                         int dpitch, const uint32_t* xtab, const uint32_t* ytab, cudaStream_t s) {
-    dim3 block(32, 8), grid((dw + 127) / 128, (dh + 7) / 8, 1);
-    resize_kernel<<<grid, block, 0, s>>>(src, sw, sh, spitch, 0, dst, dw, dh, dpitch, 0, xtab, ytab);
+                         int dpitch, const uint32_t* xtab, const uint32_t* ytab, bool fast, cudaStream_t s) {
+    launch_resize(src, sw, sh, spitch, 0, dst, dw, dh, dpitch, 0, xtab, ytab, 1, fast, s);
     return 1;
 }
 
 int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
     int launches = 0;
     for (int l = 1; l < lt.n_levels; ++l) {
-        dim3 block(32, 8), grid((lt.w[l] + 127) / 128, (lt.h[l] + 7) / 8, lt.batch);
-        resize_kernel<<<grid, block, 0, s>>>(db.pyr + lt.off[l - 1], lt.w[l - 1], lt.h[l - 1], lt.pitch[l - 1],
-                                             (size_t)lt.fstride[l - 1], db.pyr + lt.off[l], lt.w[l], lt.h[l],
-                                             lt.pitch[l], (size_t)lt.fstride[l], db.coef + lt.coef_off[l],
-                                             db.coef + lt.coef_off[l] + lt.w[l]);
+        launch_resize(db.pyr + lt.off[l - 1], lt.w[l - 1], lt.h[l - 1], lt.pitch[l - 1], (size_t)lt.fstride[l - 1],
+                      db.pyr + lt.off[l], lt.w[l], lt.h[l], lt.pitch[l], (size_t)lt.fstride[l],
+                      db.coef + lt.coef_off[l], db.coef + lt.coef_off[l] + lt.w[l], lt.batch, lt.resize_fast[l] != 0, s);
         ++launches;
     }
     return launches;

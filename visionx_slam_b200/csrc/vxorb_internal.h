@@ -29,7 +29,7 @@ constexpr int kPitchAlign = 32;
 // and at least kApronRight bytes after pixel (w-1).  The apron holds 3 valid reflected pixels.
 constexpr int kApronY = 3;
 constexpr int kApronX = 16;
-constexpr int kApronRight = 8;
+constexpr int kApronRight = 12;
 constexpr int kBlurRows = 64;    // output rows per blur strip
 
 // FAST tiling (fast.cu): a CTA computes scores for kFastScoreW x kFastScoreH pixels and emits corners
@@ -69,6 +69,7 @@ struct LevelTab {
     // blur strips: blur_tiles_x = 4-px words per row; CTAs of level l are [blur_tile_begin[l], [l+1])
     int blur_tiles_x[kMaxLevels], blur_tile_begin[kMaxLevels + 1];
     int coef_off[kMaxLevels];        // offset (in u32) of level l's resize tables: x[w_l] then y[h_l]
+    int resize_fast[kMaxLevels];     // level l's x taps fit the register-resident resize kernel
 };
 
 struct DeviceBuffers {
@@ -98,7 +99,8 @@ int launch_gray_from_bgr(const uint8_t* bgr, size_t bgr_pitch, size_t bgr_fstrid
                          int w, int h, int pitch, size_t fstride, int batch, cudaStream_t s);
 int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh,
-                         int dpitch, const uint32_t* xtab, const uint32_t* ytab, cudaStream_t s);
+                         int dpitch, const uint32_t* xtab, const uint32_t* ytab, bool fast, cudaStream_t s);
+bool resize_taps_fit_fast_path(const uint32_t* xtaps, int dw);
 int launch_apron(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s);
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
