@@ -38,7 +38,7 @@ __device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t sel) {
 
 }  // namespace
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, const GaussK gk) {
     int l = 0;
     while (l + 1 < lt.n_levels && (int)blockIdx.x >= lt.blur_tile_begin[l + 1]) ++l;
@@ -66,13 +66,29 @@ blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restr
 
     const uint32_t* p = reinterpret_cast<const uint32_t*>(src);
     const int pitch_w = pitch >> 2;  // pitch is a multiple of 32
+    // software pipeline: the words of source rows r+1 and r+2 are in flight while row r is filtered
+    // (the pointer stops at the last apron row, so the tail re-reads that row instead of running on)
+    uint32_t qa[2], qb[2], qc[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        qa[i] = __ldg(p);
+        qb[i] = __ldg(p + 1);
+        qc[i] = __ldg(p + 2);
+        if (i < last_src) p += pitch_w;
+    }
     int r = 0;
     dst -= (size_t)6 * pitch;        // output row of source row r is r - 6
     for (int g = 0; g < groups; ++g) {
 #pragma unroll
         for (int s = 0; s < 7; ++s, ++r) {
-            const uint32_t wa = __ldg(p), wb = __ldg(p + 1), wc = __ldg(p + 2);
-            if (r < last_src) p += pitch_w;  // never read below the apron
+            const uint32_t wa = qa[0], wb = qb[0], wc = qc[0];
+            qa[0] = qa[1];
+            qb[0] = qb[1];
+            qc[0] = qc[1];
+            qa[1] = __ldg(p);
+            qb[1] = __ldg(p + 1);
+            qc[1] = __ldg(p + 2);
+            if (r + 2 < last_src) p += pitch_w;  // never read below the apron
             float f[10];
             f[0] = byte_to_float(wa, 0x7541u);
             f[1] = byte_to_float(wa, 0x7542u);

@@ -108,7 +108,7 @@ fast_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint32_t* __rest
         uint32_t acc = 0;
 #pragma unroll
         for (int i = 0; i < RPW; ++i) {
-            const int r = warp * RPW + i;
+            const int r = i * 8 + warp;  // rows interleaved over warps: a corner cluster spreads over lanes of several warps
             const int gy = Y + r;
             uint32_t q = 0;
             if (gy >= sy_min && gy <= sy_max) {
@@ -139,11 +139,11 @@ fast_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint32_t* __rest
         base = __shfl_sync(0xffffffffu, base, 31);
         int pos = base + incl - cnt;
         uint16_t* q16 = reinterpret_cast<uint16_t*>(queue);
-        const int rowbase = warp * RPW * FW + 4 * lane;
+        const int rowbase = warp * FW + 4 * lane;
         while (acc) {
             const int b = __ffs(acc) - 1;
             acc &= acc - 1;
-            q16[pos++] = (uint16_t)(rowbase + (b >> 2) * FW + (b & 3));
+            q16[pos++] = (uint16_t)(rowbase + (b >> 2) * (8 * FW) + (b & 3));
         }
     }
     __syncthreads();

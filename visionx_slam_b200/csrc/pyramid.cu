@@ -89,7 +89,7 @@ resize_generic_kernel(const uint8_t* __restrict__ src, int sw, int sh, int spitc
     *reinterpret_cast<uint32_t*>(dst + (size_t)y * dpitch + x0) = out;
 }
 
-// Fast path: one thread owns 4 output columns and walks down kResizeRows output rows; a warp owns
+// Fast path: one thread owns 4 output columns and walks down `strip_rows` output rows; a warp owns
 // 128 adjacent output columns of one row band, so the row schedule is warp-uniform.
 //   horizontal pass of one source row: three aligned 32-bit loads cover the <= 8 source bytes the
 //   4 columns need; a funnel shift aligns them to the first tap, two PRMTs (loop-invariant
@@ -97,15 +97,18 @@ resize_generic_kernel(const uint8_t* __restrict__ src, int sw, int sh, int spitc
 //   16-bit weights (256-c1, c1): H = p0*c0 + p1*c1 in ONE instruction per column;
 //   the two most recent source rows' H values stay in registers (rows advance ~1.2 per output row);
 //   vertical pass: 2 IMAD per pixel, +2^15, byte 2 of each result packed into one 32-bit store.
-constexpr int kResizeRows = 16;
-
+//   The source words of the next two rows are always in flight (2-deep register queue), and the
+//   next row's y tap is fetched one row early, so the dependent load chain never stalls the strip.
+// Rows per strip shrink with the level size (resize_rows_for) so that small levels still spread over
+// every SM: they are latency bound, not bandwidth bound.
 __global__ void __launch_bounds__(256)
 resize_kernel(const uint8_t* __restrict__ src, int sh, int spitch, size_t sfstride,
               uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
-              const uint32_t* __restrict__ xtab, const uint32_t* __restrict__ ytab, int word_groups) {
+              const uint32_t* __restrict__ xtab, const uint32_t* __restrict__ ytab, int word_groups,
+              int strip_rows) {
     const int item = blockIdx.x * 8 + (threadIdx.x >> 5);
     const int band = item / word_groups;
-    const int y0 = band * kResizeRows;
+    const int y0 = band * strip_rows;
     if (y0 >= dh) return;
     const int x0 = ((item - band * word_groups) * 32 + (threadIdx.x & 31)) * 4;
     if (x0 >= dw) return;
@@ -128,19 +131,44 @@ resize_kernel(const uint8_t* __restrict__ src, int sh, int spitch, size_t sfstri
     const uint32_t sel23 = (uint32_t)(e2 | ((e2 + 1) << 4) | (e3 << 8) | ((e3 + 1) << 12));
     const uint32_t* sp = reinterpret_cast<const uint32_t*>(src) + (ofs[0] >> 2);
     const int spitch_w = spitch >> 2;
+    const int rows = min(strip_rows, dh - y0);
 
     uint32_t hp[4] = {0, 0, 0, 0}, hc[4] = {0, 0, 0, 0};  // H of source rows cur-1 and cur
-    int cur = -2;
-    const int rows = min(kResizeRows, dh - y0);
+    uint32_t ty = __ldg(ytab + y0);
+    int cur = (int)(ty & 0xffffu) - 1;
+    // queue: q?[0] = words of source row cur+1, q?[1] = row cur+2
+    uint32_t q0[2], q1[2], q2[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const uint32_t* p = sp + (size_t)min(cur + 1 + i, sh - 1) * spitch_w;
+        q0[i] = __ldg(p);
+        q1[i] = __ldg(p + 1);
+        q2[i] = __ldg(p + 2);
+    }
     for (int i = 0; i < rows; ++i) {
-        const uint32_t ty = __ldg(ytab + y0 + i);
         const int j0 = (int)(ty & 0xffffu);
         const uint32_t cy1 = ty >> 16, cy0 = 256u - cy1;
-        if (cur < j0 - 1) cur = j0 - 1;  // first row of the strip (or a jump): restart the pair
+        ty = __ldg(ytab + min(y0 + i + 1, dh - 1));  // next row's tap, one row early
+        if (cur < j0 - 1) {  // a jump of more than one source row (scale > 2): restart the queue
+            cur = j0 - 1;
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const uint32_t* p = sp + (size_t)min(cur + 1 + k, sh - 1) * spitch_w;
+                q0[k] = __ldg(p);
+                q1[k] = __ldg(p + 1);
+                q2[k] = __ldg(p + 2);
+            }
+        }
         while (cur < j0 + 1) {
             ++cur;
-            const uint32_t* p = sp + (size_t)min(cur, sh - 1) * spitch_w;
-            const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+            const uint32_t w0 = q0[0], w1 = q1[0], w2 = q2[0];
+            q0[0] = q0[1];
+            q1[0] = q1[1];
+            q2[0] = q2[1];
+            const uint32_t* p = sp + (size_t)min(cur + 2, sh - 1) * spitch_w;
+            q0[1] = __ldg(p);
+            q1[1] = __ldg(p + 1);
+            q2[1] = __ldg(p + 2);
             const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
             const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
 #pragma unroll
@@ -159,6 +187,19 @@ resize_kernel(const uint8_t* __restrict__ src, int sh, int spitch, size_t sfstri
     }
 }
 
+// Strip height for one level: 16 rows amortise the two start-up source rows best; halve it while the
+// launch would leave SMs without a full set of resident warps (148 SMs x 5 CTAs of 8 warps).
+static int resize_rows_for(int dw, int dh, int batch) {
+    const int word_groups = ((dw + 3) / 4 + 31) / 32;
+    int rows = 16;
+    while (rows > 4) {
+        const long long warps = (long long)word_groups * ((dh + rows - 1) / rows) * batch;
+        if (warps >= 148LL * 40) break;
+        rows >>= 1;
+    }
+    return rows;
+}
+
 // True when every group of 4 output columns reads at most 8 consecutive source bytes.
 bool resize_taps_fit_fast_path(const uint32_t* xtaps, int dw) {
     for (int x0 = 0; x0 < dw; x0 += 4) {
@@ -173,10 +214,11 @@ static void launch_resize(const uint8_t* src, int sw, int sh, int spitch, size_t
                           bool fast, cudaStream_t s) {
     if (fast) {
         const int word_groups = ((dw + 3) / 4 + 31) / 32;
-        const int items = word_groups * ((dh + kResizeRows - 1) / kResizeRows);
+        const int rows = resize_rows_for(dw, dh, batch);
+        const int items = word_groups * ((dh + rows - 1) / rows);
         dim3 grid((items + 7) / 8, batch);
         resize_kernel<<<grid, 256, 0, s>>>(src, sh, spitch, sfstride, dst, dw, dh, dpitch, dfstride, xtab, ytab,
-                                           word_groups);
+                                           word_groups, rows);
     } else {
         dim3 block(32, 8), grid((dw + 127) / 128, (dh + 7) / 8, batch);
         resize_generic_kernel<<<grid, block, 0, s>>>(src, sw, sh, spitch, sfstride, dst, dw, dh, dpitch, dfstride, xtab,

@@ -7,11 +7,13 @@
 // so the kept SET is order independent and is reproduced here with histogram / radix selection.
 //
 //   step 1  256-bin shared histogram of FAST scores -> threshold of the (2q)-th largest
-//   step 2  Harris response, one warp per retained candidate (9x9 window staged in shared memory,
-//           integer sums reduced with REDUX, float combine un-fused exactly as OpenCV's)
+//           (bin walk done by one warp: 8 bins per lane + a shuffle suffix sum)
+//   step 2  retained candidates compacted into a shared index list, then ONE THREAD per candidate
+//           computes the Harris response: 27 independent word loads, separable gradients in
+//           registers, float combine un-fused exactly as OpenCV's
 //   step 3  4-pass 8-bit radix select on the order-preserving float key -> q-th largest response
-//   step 4  survivors staged in shared memory, rank-sorted by (y, x), written to the final list
-// One CTA per (level, frame).  Working set is a few KB per CTA and L2 resident; the stage is
+//   step 4  survivors rank-sorted by (y, x) inside shared memory, written to the final list
+// One CTA per (level, frame), level-major so the long level-0 CTAs are scheduled first.  Working set is a few KB per CTA and L2 resident; the stage is
 // latency/issue bound, not HBM bound.
 #include "vxorb_internal.h"
 
@@ -20,7 +22,6 @@ namespace vxorb {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kWarps = kThreads / 32;
 constexpr int kSortCap = 2048;
 
 __device__ __forceinline__ uint32_t float_key(float v) {
@@ -29,43 +30,109 @@ __device__ __forceinline__ uint32_t float_key(float v) {
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-// Harris response of the 7x7 block around (x, y); all 32 lanes of the warp take part.
-// `patch` is this warp's 9 x 12 byte staging area.
-__device__ __forceinline__ float harris_warp(const uint8_t* __restrict__ img, int pitch, int x, int y,
-                                             uint8_t (*patch)[12], int lane) {
-    __syncwarp();
-    for (int i = lane; i < 81; i += 32) {
-        const int r = i / 9, c = i - r * 9;
-        patch[r][c] = __ldg(img + (size_t)(y - 4 + r) * pitch + (x - 4 + c));
+// Harris response of the 7x7 block around (x, y), computed by ONE thread: 9 rows x 3 aligned words
+// are loaded up front (27 independent loads in flight), then the separable form is evaluated in
+// registers: d[r][x] = p[x+1] - p[x-1], s[r][x] = p[x-1] + 2 p[x] + p[x+1] per row,
+// Ix = d[y-1] + 2 d[y] + d[y+1], Iy = s[y+1] - s[y-1].  Integer sums are exact, so the grouping does
+// not matter; the float combine is un-fused in OpenCV's association.
+__device__ __forceinline__ float harris_thread(const uint8_t* __restrict__ img, int pitch, int x, int y) {
+    const uint8_t* base = img + (ptrdiff_t)(y - 4) * pitch + (x - 4);
+    const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(base) & 3u) * 8u;
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(base) & ~(uintptr_t)3);
+    const int pw = pitch >> 2;
+    uint32_t w[9][3];
+#pragma unroll
+    for (int r = 0; r < 9; ++r) {
+        w[r][0] = __ldg(wp + r * pw);
+        w[r][1] = __ldg(wp + r * pw + 1);
+        w[r][2] = __ldg(wp + r * pw + 2);
     }
-    __syncwarp();
+    int d[3][7], s[3][7];  // rolling window of rows r-2, r-1, r (index r % 3)
     int a = 0, b = 0, c = 0;
 #pragma unroll
-    for (int rnd = 0; rnd < 2; ++rnd) {
-        const int k = lane + rnd * 32;
-        if (k < 49) {
-            const int by = k / 7, bx = k - by * 7;  // block pixel, patch coords (bx+1, by+1)
-            const uint8_t* p = &patch[by + 1][bx + 1];
-            const int p00 = p[-12 - 1], p01 = p[-12], p02 = p[-12 + 1];
-            const int p10 = p[-1], p12 = p[1];
-            const int p20 = p[12 - 1], p21 = p[12], p22 = p[12 + 1];
-            const int ix = (p12 - p10) * 2 + (p02 - p00) + (p22 - p20);
-            const int iy = (p21 - p01) * 2 + (p20 - p00) + (p22 - p02);
-            a += ix * ix;
-            b += iy * iy;
-            c += ix * iy;
+    for (int r = 0; r < 9; ++r) {
+        const uint32_t lo = __funnelshift_r(w[r][0], w[r][1], sh), mid = __funnelshift_r(w[r][1], w[r][2], sh);
+        const uint32_t hi = w[r][2] >> sh;
+        int p[9];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            p[k] = (int)((lo >> (8 * k)) & 0xffu);
+            p[4 + k] = (int)((mid >> (8 * k)) & 0xffu);
+        }
+        p[8] = (int)(hi & 0xffu);
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            d[r % 3][k] = p[k + 2] - p[k];
+            s[r % 3][k] = p[k] + 2 * p[k + 1] + p[k + 2];
+        }
+        if (r >= 2) {
+            // block row centred on patch row r-1
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {
+                const int ix = d[(r - 2) % 3][k] + 2 * d[(r - 1) % 3][k] + d[r % 3][k];
+                const int iy = s[r % 3][k] - s[(r - 2) % 3][k];
+                a += ix * ix;
+                b += iy * iy;
+                c += ix * iy;
+            }
         }
     }
-    a = __reduce_add_sync(0xffffffffu, a);
-    b = __reduce_add_sync(0xffffffffu, b);
-    c = __reduce_add_sync(0xffffffffu, c);
     const float scale = 1.0f / (4 * 7 * 255.0f);
     const float s4 = __fmul_rn(__fmul_rn(__fmul_rn(scale, scale), scale), scale);
     const float fa = (float)a, fb = (float)b, fc = (float)c;
     const float det = __fsub_rn(__fmul_rn(fa, fb), __fmul_rn(fc, fc));
     const float tr = __fadd_rn(fa, fb);
-    const float r = __fsub_rn(det, __fmul_rn(__fmul_rn(0.04f, tr), tr));
-    return __fmul_rn(r, s4);
+    const float rr = __fsub_rn(det, __fmul_rn(__fmul_rn(0.04f, tr), tr));
+    return __fmul_rn(rr, s4);
+}
+
+// Warp-parallel replacement of the serial "walk the 256-bin histogram from the top until k entries
+// are covered" loop.  Called by all 32 lanes of ONE warp.  Returns (via out params, valid in every
+// lane) the largest bin d >= 1 with sum_{b >= d} hist[b] >= k, and above = sum_{b > d} hist[b]; if
+// no such bin exists d = 0 and above = sum_{b >= 1} hist[b] (what the serial loop leaves behind).
+__device__ __forceinline__ void top_bin_scan(const int* hist, int k, int lane, int& d_out, int& above_out) {
+    int hb[8], tot = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        hb[j] = hist[8 * lane + j];
+        tot += hb[j];
+    }
+    int suf = tot;  // becomes sum over lanes >= lane
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_down_sync(0xffffffffu, suf, o);
+        if (lane + o < 32) suf += n;
+    }
+    int cum = suf - tot;  // bins of higher lanes
+    const bool has = cum < k && suf >= k;
+    int d = 0, above = 0;
+    if (has) {
+        d = -1;
+#pragma unroll
+        for (int j = 7; j >= 0; --j) {
+            if (d < 0) {
+                if (cum + hb[j] >= k) {
+                    d = 8 * lane + j;
+                    above = cum;
+                } else {
+                    cum += hb[j];
+                }
+            }
+        }
+        if (d == 0) {  // the serial loop never stops on bin 0
+            above = cum;
+        }
+    }
+    const unsigned who = __ballot_sync(0xffffffffu, has);
+    if (who == 0) {
+        const int all = __shfl_sync(0xffffffffu, suf, 0);
+        d_out = 0;
+        above_out = all - hist[0];
+        return;
+    }
+    const int src = __ffs(who) - 1;
+    d_out = __shfl_sync(0xffffffffu, d, src);
+    above_out = __shfl_sync(0xffffffffu, above, src);
 }
 
 }  // namespace
@@ -75,14 +142,14 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
               const int* __restrict__ cand_n, float* __restrict__ resp, uint32_t* __restrict__ fin_key,
               float* __restrict__ fin_resp, int* __restrict__ fin_n, int* __restrict__ status) {
     __shared__ int hist[256];
-    __shared__ uint8_t patch[kWarps][9][12];
-    __shared__ uint32_t skey[kSortCap];
+    __shared__ uint32_t skey[kSortCap];   // phase A: index of a retained candidate; phase B: (y, x) key
     __shared__ float sresp[kSortCap];
-    __shared__ int s_thr1, s_ns, s_nf;
+    __shared__ int s_thr1, s_ns, s_nf, s_nr;
     __shared__ uint32_t s_prefix;
     __shared__ int s_k;
 
-    const int l = blockIdx.x, f = blockIdx.y;
+    // heavy levels first: blockIdx.y = level, so all level-0 CTAs are scheduled before level 1 ...
+    const int l = blockIdx.y, f = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int* out_n = fin_n + l * lt.batch + f;
     if (!lt.active[l]) {
@@ -107,31 +174,47 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
         s_thr1 = 0;
         s_ns = n;
         s_nf = 0;
+        s_nr = 0;
     }
     __syncthreads();
     if (n > 2 * q) {
         for (int i = tid; i < n; i += kThreads) atomicAdd(&hist[c[i] >> 24], 1);
         __syncthreads();
-        if (tid == 0) {
-            int cum = 0, s = 255;
-            for (; s > 0; --s) {
-                cum += hist[s];
-                if (cum >= 2 * q) break;
+        if (warp == 0) {
+            int d, above;
+            top_bin_scan(hist, 2 * q, lane, d, above);
+            if (lane == 0) {
+                s_thr1 = d;
+                s_ns = above + hist[d];  // d >= 20 here: n > 2q and every score is >= the threshold
             }
-            s_thr1 = s;
-            s_ns = cum;
         }
         __syncthreads();
     }
     const uint32_t thr1 = (uint32_t)s_thr1;
     const int ns = s_ns;
+    const bool listed = ns <= kSortCap;  // retained candidates fit the shared index list
 
-    // ---- step 2: Harris response of every retained candidate ----------------------------------
-    for (int i = warp; i < n; i += kWarps) {
-        const uint32_t k = c[i];
-        if ((k >> 24) >= thr1) {
-            const float r = harris_warp(img, pitch, (int)(k & 0xfffu), (int)((k >> 12) & 0xfffu), patch[warp], lane);
-            if (lane == 0) rs[i] = r;
+    // ---- step 2: Harris response of every retained candidate, one thread per candidate --------
+    if (listed) {
+        for (int i0 = 0; i0 < n; i0 += kThreads) {
+            const int i = i0 + tid;
+            const bool keep = i < n && (c[i] >> 24) >= thr1;
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            int base = 0;
+            if (lane == 0 && m) base = atomicAdd(&s_nr, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (keep) skey[base + __popc(m & ((1u << lane) - 1u))] = (uint32_t)i;
+        }
+        __syncthreads();
+        for (int j = tid; j < ns; j += kThreads) {
+            const uint32_t i = skey[j];
+            const uint32_t k = c[i];
+            sresp[j] = harris_thread(img, pitch, (int)(k & 0xfffu), (int)((k >> 12) & 0xfffu));
+        }
+    } else {
+        for (int i = tid; i < n; i += kThreads) {
+            const uint32_t k = c[i];
+            if ((k >> 24) >= thr1) rs[i] = harris_thread(img, pitch, (int)(k & 0xfffu), (int)((k >> 12) & 0xfffu));
         }
     }
     __syncthreads();
@@ -148,21 +231,28 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
             hist[tid] = 0;
             __syncthreads();
             const uint32_t prefix = s_prefix;
-            for (int i = tid; i < n; i += kThreads) {
-                if ((c[i] >> 24) >= thr1) {
-                    const uint32_t u = float_key(rs[i]);
+            if (listed) {
+                for (int j = tid; j < ns; j += kThreads) {
+                    const uint32_t u = float_key(sresp[j]);
                     if ((u & mask) == prefix) atomicAdd(&hist[(u >> (8 * pass)) & 255u], 1);
+                }
+            } else {
+                for (int i = tid; i < n; i += kThreads) {
+                    if ((c[i] >> 24) >= thr1) {
+                        const uint32_t u = float_key(rs[i]);
+                        if ((u & mask) == prefix) atomicAdd(&hist[(u >> (8 * pass)) & 255u], 1);
+                    }
                 }
             }
             __syncthreads();
-            if (tid == 0) {
-                int k = s_k, cum = 0, d = 255;
-                for (; d > 0; --d) {
-                    if (cum + hist[d] >= k) break;
-                    cum += hist[d];
+            if (warp == 0) {
+                int d, above;
+                top_bin_scan(hist, s_k, lane, d, above);
+                __syncwarp();
+                if (lane == 0) {
+                    s_k -= above;
+                    s_prefix = prefix | ((uint32_t)d << (8 * pass));
                 }
-                s_k = k - cum;
-                s_prefix = prefix | ((uint32_t)d << (8 * pass));
             }
             mask |= 255u << (8 * pass);
             __syncthreads();
@@ -170,42 +260,54 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
         thr2 = s_prefix;
     }
 
-    // ---- step 4: gather survivors, order by (y, x), write the final list ----------------------
-    for (int i = tid; i < n; i += kThreads) {
-        const uint32_t k = c[i];
-        if ((k >> 24) >= thr1) {
-            const float r = rs[i];
-            if (float_key(r) >= thr2) {
-                const int o = atomicAdd(&s_nf, 1);
-                if (o < kSortCap) {
-                    skey[o] = k & 0xffffffu;
-                    sresp[o] = r;
-                }
-            }
-        }
-    }
-    __syncthreads();
-    const int nf = s_nf;
+    // ---- step 4: survivors in (y, x) order -> final list ----------------------------------------
     const int fcap = lt.fin_cap[l];
     uint32_t* ok = fin_key + lt.fin_off[l] + (size_t)f * fcap;
     float* orr = fin_resp + lt.fin_off[l] + (size_t)f * fcap;
-    if (nf <= kSortCap) {
-        for (int i = tid; i < nf; i += kThreads) {
-            const uint32_t k = skey[i];
-            int rank = 0;
-            for (int j = 0; j < nf; ++j) rank += skey[j] < k ? 1 : 0;
-            if (rank < fcap) {
-                ok[rank] = k;
-                orr[rank] = sresp[i];
+    if (listed) {
+        // rank sort inside the shared list: non-survivors get the sentinel key and never count
+        uint32_t mykey[kSortCap / kThreads];
+        int cnt = 0;
+#pragma unroll
+        for (int t = 0; t < kSortCap / kThreads; ++t) {
+            const int j = tid + t * kThreads;
+            mykey[t] = 0xffffffffu;
+            if (j < ns && float_key(sresp[j]) >= thr2) {
+                mykey[t] = c[skey[j]] & 0xffffffu;
+                ++cnt;
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int t = 0; t < kSortCap / kThreads; ++t) {
+            const int j = tid + t * kThreads;
+            if (j < ns) skey[j] = mykey[t];
+        }
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (lane == 0 && cnt) atomicAdd(&s_nf, cnt);
+        __syncthreads();
+#pragma unroll
+        for (int t = 0; t < kSortCap / kThreads; ++t) {
+            const int j = tid + t * kThreads;
+            const uint32_t k = mykey[t];
+            if (k != 0xffffffffu) {
+                int rank = 0;
+                for (int jj = 0; jj < ns; ++jj) rank += skey[jj] < k ? 1 : 0;
+                if (rank < fcap) {
+                    ok[rank] = k;
+                    orr[rank] = sresp[j];
+                }
             }
         }
     } else {
         // Degenerate images (massive ties): rank against the candidate list in global memory.
+        int cnt = 0;
         for (int i = tid; i < n; i += kThreads) {
             const uint32_t k = c[i];
             if ((k >> 24) < thr1) continue;
             const float r = rs[i];
             if (float_key(r) < thr2) continue;
+            ++cnt;
             const uint32_t key = k & 0xffffffu;
             int rank = 0;
             for (int j = 0; j < n; ++j) {
@@ -217,15 +319,18 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
                 orr[rank] = r;
             }
         }
+        if (cnt) atomicAdd(&s_nf, cnt);
     }
+    __syncthreads();
     if (tid == 0) {
+        const int nf = s_nf;
         *out_n = nf;  // true count; consumers clamp to fin_cap
         if (nf > fcap) atomicOr(status, 2);
     }
 }
 
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
-    dim3 grid(lt.n_levels, lt.batch);
+    dim3 grid(lt.batch, lt.n_levels);
     select_kernel<<<grid, kThreads, 0, s>>>(lt, db.pyr, db.cand, db.cand_n, db.resp, db.fin_key, db.fin_resp,
                                            db.fin_n, db.status);
     return 1;
