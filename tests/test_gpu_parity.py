@@ -210,6 +210,37 @@ def test_match_windowed_kat(h, golden_kat):
     assert np.array_equal(matches_as_rows(m), g["dup_matches_win64"])
 
 
+@pytest.mark.parametrize("nq,nt,radius,kind", [
+    (1000, 1000, 32.0, "image"), (1000, 1000, 16.0, "image"), (997, 1003, 100.0, "image"),
+    (300, 2500, 32.0, "cluster"), (2000, 2000, 24.0, "lattice"), (500, 700, 32.0, "far"),
+    (64, 1, 32.0, "image"), (40, 6000, 32.0, "image"),
+])
+def test_match_windowed_vs_oracle(h, nq, nt, radius, kind):
+    """Cell-binned windowed 2-NN (few distinct descriptors -> heavy distance ties) against the
+    oracle's masked knn: positions on a lattice put many pairs exactly on the window edge."""
+    rng = np.random.default_rng(nq * 7 + nt)
+    base = rng.integers(0, 256, (24, 32), dtype=np.uint8)
+    t = base[rng.integers(0, 24, nt)].copy()
+    q = base[rng.integers(0, 24, nq)].copy()
+    t[::3, rng.integers(0, 32)] ^= 0x5a
+    q[::5, rng.integers(0, 32)] ^= 0x0f
+    if kind == "image":
+        txy = rng.random((nt, 2), np.float32) * np.float32([640, 480])
+        qxy = rng.random((nq, 2), np.float32) * np.float32([640, 480])
+    elif kind == "cluster":
+        txy = (rng.normal(0, 20, (nt, 2)) + [300, 200]).astype(np.float32)
+        qxy = (rng.normal(0, 40, (nq, 2)) + [300, 200]).astype(np.float32)
+    elif kind == "lattice":
+        txy = (rng.integers(0, 40, (nt, 2)) * 8).astype(np.float32)      # |dx| == radius happens often
+        qxy = (rng.integers(0, 40, (nq, 2)) * 8).astype(np.float32)
+    else:  # negative and large coordinates, queries partly outside the train bounding box
+        txy = (rng.random((nt, 2), np.float32) * 2000 - 1000).astype(np.float32) + np.float32(1.0e5)
+        qxy = (rng.random((nq, 2), np.float32) * 2400 - 1200).astype(np.float32) + np.float32(1.0e5)
+    assert _knn_equal(h.knn2(q, t, qxy, txy, radius), oracle.knn2(q, t, qxy, txy, radius))
+    assert np.array_equal(matches_as_rows(h.match(q, t, 0.8, qxy, txy, radius)),
+                          matches_as_rows(oracle.match(q, t, 0.8, qxy, txy, radius)))
+
+
 def test_match_empty_sides(h):
     z = np.zeros((0, 32), np.uint8)
     q = np.zeros((5, 32), np.uint8)

@@ -330,6 +330,7 @@ int enqueue_track_match(vxorb_handle* h, Workspace& ws, int batch, float radius)
     a.t_n = d.kp_n + 1;
     a.q_pair_stride = a.t_pair_stride = h->kp_cap;
     a.max_q = h->kp_cap;
+    a.max_t = h->kp_cap;
     a.pairs = batch;
     a.radius = radius;
     a.knn = d.knn;
@@ -416,14 +417,14 @@ int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, co
     a.q_xy = win ? h->m_qxy : nullptr; a.t_xy = win ? h->m_txy : nullptr;
     a.q_n = h->m_n; a.t_n = h->m_n + 1;
     a.q_pair_stride = a.t_pair_stride = 0;
-    a.max_q = nq; a.pairs = 1; a.radius = win ? radius : 0.f;
+    a.max_q = nq; a.max_t = nt; a.pairs = 1; a.radius = win ? radius : 0.f;
     a.knn = h->m_knn; a.knn_stride = 0;
     int launches = launch_knn2(a, s);
     if (reverse_too) {
         MatchArgs b = a;
         b.q_desc = h->m_t; b.t_desc = h->m_q;
         b.q_n = h->m_n + 1; b.t_n = h->m_n;
-        b.max_q = nt; b.knn = h->m_back;
+        b.max_q = nt; b.max_t = nq; b.knn = h->m_back;
         launches += launch_knn2(b, s);
     }
     sc.end(launches);
@@ -551,6 +552,7 @@ int vxorb_create(const vxorb_params* p, vxorb_handle** out) {
     if ((e = cudaEventCreate(&h->t_begin)) != cudaSuccess) return bail(e, "event");
     if ((e = cudaEventCreate(&h->t_end)) != cudaSuccess) return bail(e, "event");
     if ((e = init_device_tables()) != cudaSuccess) return bail(e, "pattern upload");
+    if ((e = init_match_kernels()) != cudaSuccess) return bail(e, "match kernel attributes");
     *out = h;
     return VXORB_OK;
 }

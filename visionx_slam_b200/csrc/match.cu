@@ -102,6 +102,168 @@ knn2_kernel(const MatchArgs a) {
     }
 }
 
+// ---- windowed 2-NN over a uniform cell grid ------------------------------------------------------
+// The brute-force kernel above tests every (query, train) pair against the window.  With a square
+// window of radius r only ~(2r)^2 / (W*H) of the train rows can pass (1.3 % at r = 32 on 640x480),
+// so this kernel first bins the train keypoints of the pair into a kCellGrid x kCellGrid grid of
+// cells at least r wide (counting sort in shared memory: histogram, block scan, scatter of
+// descriptor + position + original index in cell order), and every query thread then visits only
+// the cells its window touches: <= 3 x 3 cells, each cell row one contiguous range of the sorted
+// list.  The exact window test (same float expression as the brute-force kernel) is still applied
+// per candidate, and the packed key (distance << 20 | original train index) keeps OpenCV's
+// tie-break (lowest train index) whatever the visiting order.  Cell lookup is conservative: the
+// cell range is computed from a slightly widened radius with the same monotonic float expression
+// that bins the train points, so no in-window row can be missed.
+constexpr int kCellGrid = 32;
+constexpr int kCells = kCellGrid * kCellGrid;
+constexpr int kWinThreads = 256;
+
+__device__ __forceinline__ int cell_of(float v, float org, float inv) {
+    const float c = floorf(__fmul_rn(__fsub_rn(v, org), inv));
+    return (int)fminf(fmaxf(c, 0.0f), (float)(kCellGrid - 1));
+}
+
+static size_t window_smem_bytes(int max_t) {
+    return (size_t)max_t * (32 + 8 + 4) + (size_t)(2 * kCells + 1) * 4 + 64;
+}
+
+__global__ void __launch_bounds__(kWinThreads)
+knn2_window_kernel(const MatchArgs a, int max_t) {
+    extern __shared__ __align__(16) uint8_t wsm[];
+    uint4* tdesc = reinterpret_cast<uint4*>(wsm);                                  // [max_t][2]
+    float2* txy = reinterpret_cast<float2*>(wsm + (size_t)max_t * 32);             // [max_t]
+    int* tidx = reinterpret_cast<int*>(wsm + (size_t)max_t * 40);                  // [max_t]
+    int* cell_start = tidx + max_t;                                                // [kCells + 1]
+    int* cursor = cell_start + kCells + 1;                                         // [kCells]
+    float* bounds = reinterpret_cast<float*>(cursor + kCells);                     // minx, miny, maxx, maxy
+    __shared__ int warp_tot[kWinThreads / 32];
+
+    const int pair = blockIdx.y;
+    const int nq = a.q_n[pair], nt = min(a.t_n[pair], max_t);
+    if ((int)blockIdx.x * kWinThreads >= nq) return;  // whole CTA idle
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint8_t* qbase = a.q_desc + (size_t)pair * a.q_pair_stride * 32;
+    const uint8_t* tbase = a.t_desc + (size_t)pair * a.t_pair_stride * 32;
+    const float2* txy_g = reinterpret_cast<const float2*>(a.t_xy + (size_t)pair * a.t_pair_stride * 2);
+    const float r = a.radius;
+
+    // ---- 1. bounding box of the train positions -> grid geometry ------------------------------
+    {
+        float mnx = 3.0e38f, mny = 3.0e38f, mxx = -3.0e38f, mxy = -3.0e38f;
+        for (int i = tid; i < nt; i += kWinThreads) {
+            const float2 p = __ldg(txy_g + i);
+            mnx = fminf(mnx, p.x); mxx = fmaxf(mxx, p.x);
+            mny = fminf(mny, p.y); mxy = fmaxf(mxy, p.y);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mnx = fminf(mnx, __shfl_xor_sync(0xffffffffu, mnx, o));
+            mny = fminf(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+            mxx = fmaxf(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
+            mxy = fmaxf(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+        }
+        float* wb = reinterpret_cast<float*>(cursor);  // scratch: 8 warps x 4 floats
+        if (lane == 0) {
+            wb[warp * 4 + 0] = mnx; wb[warp * 4 + 1] = mny; wb[warp * 4 + 2] = mxx; wb[warp * 4 + 3] = mxy;
+        }
+        for (int i = tid; i < kCells + 1; i += kWinThreads) cell_start[i] = 0;
+        __syncthreads();
+        if (tid == 0) {
+            for (int wv = 1; wv < kWinThreads / 32; ++wv) {
+                mnx = fminf(mnx, wb[wv * 4 + 0]); mny = fminf(mny, wb[wv * 4 + 1]);
+                mxx = fmaxf(mxx, wb[wv * 4 + 2]); mxy = fmaxf(mxy, wb[wv * 4 + 3]);
+            }
+            bounds[0] = mnx; bounds[1] = mny; bounds[2] = mxx; bounds[3] = mxy;
+        }
+        __syncthreads();
+    }
+    const float orgx = bounds[0], orgy = bounds[1];
+    // cells at least r wide, and wide enough that kCellGrid of them cover the bounding box
+    const float csx = fmaxf(r, (bounds[2] - orgx) * (1.0f / kCellGrid) * 1.0001f);
+    const float csy = fmaxf(r, (bounds[3] - orgy) * (1.0f / kCellGrid) * 1.0001f);
+    const float invx = 1.0f / csx, invy = 1.0f / csy;
+
+    // ---- 2. counting sort of the train rows by cell --------------------------------------------
+    for (int i = tid; i < nt; i += kWinThreads) {
+        const float2 p = __ldg(txy_g + i);
+        atomicAdd(&cell_start[cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx)], 1);
+    }
+    __syncthreads();
+    {
+        // exclusive scan of kCells counts: 4 per thread, warp scan, then warp totals
+        constexpr int per = kCells / kWinThreads;
+        int c[per], sum = 0;
+#pragma unroll
+        for (int k = 0; k < per; ++k) {
+            c[k] = cell_start[tid * per + k];
+            sum += c[k];
+        }
+        int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += n;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        int base = incl - sum;
+        for (int wv = 0; wv < warp; ++wv) base += warp_tot[wv];
+#pragma unroll
+        for (int k = 0; k < per; ++k) {
+            cell_start[tid * per + k] = base;
+            cursor[tid * per + k] = base;
+            base += c[k];
+        }
+        if (tid == kWinThreads - 1) cell_start[kCells] = base;
+    }
+    __syncthreads();
+    for (int i = tid; i < nt; i += kWinThreads) {
+        const float2 p = __ldg(txy_g + i);
+        const int cell = cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx);
+        const int pos = atomicAdd(&cursor[cell], 1);
+        txy[pos] = p;
+        tidx[pos] = i;
+        tdesc[2 * pos] = __ldg(reinterpret_cast<const uint4*>(tbase + (size_t)i * 32));
+        tdesc[2 * pos + 1] = __ldg(reinterpret_cast<const uint4*>(tbase + (size_t)i * 32 + 16));
+    }
+    __syncthreads();
+
+    // ---- 3. one thread per query: visit the cells under its window ------------------------------
+    const int qi = blockIdx.x * kWinThreads + tid;
+    if (qi >= nq) return;
+    uint32_t q[8];
+    {
+        const uint4 lo = __ldg(reinterpret_cast<const uint4*>(qbase + (size_t)qi * 32));
+        const uint4 hi = __ldg(reinterpret_cast<const uint4*>(qbase + (size_t)qi * 32 + 16));
+        q[0] = lo.x; q[1] = lo.y; q[2] = lo.z; q[3] = lo.w;
+        q[4] = hi.x; q[5] = hi.y; q[6] = hi.z; q[7] = hi.w;
+    }
+    const float2 qp = __ldg(reinterpret_cast<const float2*>(a.q_xy + ((size_t)pair * a.q_pair_stride + qi) * 2));
+    const float qx = qp.x, qy = qp.y;
+    // widened radius for the cell range only (covers the rounding of qx - tx and of qx +- r)
+    const float rw = r + r * 1.0e-4f + fmaxf(fabsf(qx), fabsf(qy)) * 1.0e-6f;
+    const int cx0 = cell_of(qx - rw, orgx, invx), cx1 = cell_of(qx + rw, orgx, invx);
+    const int cy0 = cell_of(qy - rw, orgy, invy), cy1 = cell_of(qy + rw, orgy, invy);
+    uint32_t k0 = kNoKey, k1 = kNoKey;
+    for (int cy = cy0; cy <= cy1; ++cy) {
+        const int j0 = cell_start[cy * kCellGrid + cx0], j1 = cell_start[cy * kCellGrid + cx1 + 1];
+        for (int j = j0; j < j1; ++j) {
+            const float2 p = txy[j];
+            if (fabsf(__fsub_rn(qx, p.x)) <= r && fabsf(__fsub_rn(qy, p.y)) <= r) {
+                const uint4 lo = tdesc[2 * j], hi = tdesc[2 * j + 1];
+                const int d = __popc(q[0] ^ lo.x) + __popc(q[1] ^ lo.y) + __popc(q[2] ^ lo.z) + __popc(q[3] ^ lo.w) +
+                              __popc(q[4] ^ hi.x) + __popc(q[5] ^ hi.y) + __popc(q[6] ^ hi.z) + __popc(q[7] ^ hi.w);
+                const uint32_t key = ((uint32_t)d << 20) | (uint32_t)tidx[j];
+                k1 = min(k1, max(k0, key));
+                k0 = min(k0, key);
+            }
+        }
+    }
+    reinterpret_cast<int4*>(a.knn + (size_t)pair * a.knn_stride)[qi] =
+        make_int4(k0 == kNoKey ? -1 : (int)(k0 & 0xfffffu), k1 == kNoKey ? -1 : (int)(k1 & 0xfffffu),
+                  k0 == kNoKey ? 0 : (int)(k0 >> 20), k1 == kNoKey ? 0 : (int)(k1 >> 20));
+}
+
 // One CTA per pair.  Walks the queries in ascending order in chunks of blockDim and appends the
 // accepted ones with an ordered block scan, so matches come out sorted by query index exactly as
 // the reference's loop over knn_matches (orb_matcher.cpp:27-36) produces them.
@@ -201,8 +363,20 @@ int launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t s) {
     return 1;
 }
 
+// Opts the windowed kernel into large dynamic shared memory on the current device (vxorb_create).
+cudaError_t init_match_kernels() {
+    return cudaFuncSetAttribute(knn2_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+}
+
 int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     if (a.pairs <= 0 || a.max_q <= 0) return 0;
+    const bool windowed = a.radius > 0.0f && a.q_xy != nullptr && a.t_xy != nullptr;
+    if (windowed && a.max_t > 0 && window_smem_bytes(a.max_t) <= 200 * 1024) {
+        // cell-binned path: the whole train set of a pair sits in shared memory in cell order
+        dim3 grid((a.max_q + kWinThreads - 1) / kWinThreads, a.pairs);
+        knn2_window_kernel<<<grid, kWinThreads, window_smem_bytes(a.max_t), s>>>(a, a.max_t);
+        return 1;
+    }
     dim3 grid((a.max_q + kQPerBlock - 1) / kQPerBlock, a.pairs);
     knn2_kernel<<<grid, kQPerBlock, 0, s>>>(a);
     return 1;

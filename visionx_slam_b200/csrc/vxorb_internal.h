@@ -114,6 +114,7 @@ struct MatchArgs {
     const int* q_n; const int* t_n;                 // [pair] row counts (device)
     long long q_pair_stride, t_pair_stride;         // rows between consecutive pairs
     int max_q;                                      // upper bound of q_n (grid sizing)
+    int max_t = 0;                                  // upper bound of t_n (shared-memory sizing of the windowed path)
     int pairs;
     float radius;                                   // <= 0: brute force
     vxorb_knn2_t* knn;                              // [pair][knn_stride]
@@ -128,6 +129,7 @@ int launch_flush(uint8_t* buf, size_t bytes, cudaStream_t s);
 int launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t s);
 
 cudaError_t init_device_tables();
+cudaError_t init_match_kernels();
 void build_resize_taps(int ssize, int dsize, uint32_t* taps);
 
 }  // namespace vxorb
