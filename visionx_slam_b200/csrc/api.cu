@@ -292,7 +292,9 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
     }
     {
         StageScope sc(h, s, VXORB_STAGE_FAST);
-        sc.end(launch_fast(lt, d, h->p.fast_threshold, kEdge, s));
+        const int n = launch_fast(lt, d, h->p.fast_threshold, kEdge, s);
+        if (n < 0) return fail(h, VXORB_E_CUDA, "cuTensorMapEncodeTiled failed for the FAST tile maps");
+        sc.end(n);
     }
     {
         StageScope sc(h, s, VXORB_STAGE_SELECT);
@@ -1105,7 +1107,11 @@ int vxorb_debug_fast(vxorb_handle* h, const uint8_t* img, int width, int height,
     cudaStream_t s = h->ws[0].stream;
     CK(cudaMemsetAsync(h->s_a, 0, h->s_bytes, s));
     CK(cudaMemcpy2DAsync(db.pyr + lt.off[0], lt.pitch[0], img, stride, width, height, cudaMemcpyHostToDevice, s));
-    h->launches += launch_fast(lt, db, threshold, border, s);
+    {
+        const int nl = launch_fast(lt, db, threshold, border, s);
+        if (nl < 0) return fail(h, VXORB_E_CUDA, "cuTensorMapEncodeTiled failed for the FAST tile maps");
+        h->launches += nl;
+    }
     CK(cudaGetLastError());
     int n = 0;
     CK(cudaMemcpyAsync(&n, db.cand_n, sizeof(int), cudaMemcpyDeviceToHost, s));

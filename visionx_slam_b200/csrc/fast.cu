@@ -7,10 +7,14 @@
 // (so corner <=> score >= t); kept iff its score is strictly greater than the 8 neighbours'.
 // Integer work, bit-exact.
 //
-// One CTA (8 warps) owns a tile whose score region is 128 x 40 px (emission region: the inner
-// 124 x 38); the level pixels it needs sit in shared memory as 32-bit words and the score map never
-// leaves shared memory.
-//   load    46 rows x 34 aligned words (3-row ring halo, one halo word left and right)
+// Persistent CTAs (8 warps) walk over tiles whose score region is 128 x 40 px (emission region: the
+// inner 124 x 38); the level pixels a tile needs sit in shared memory as 32-bit words and the score
+// map never leaves shared memory.
+//   load    one TMA box per tile (cp.async.bulk.tensor.3d over a per-level {pitch, rows, frame}
+//           tensor map: 46 rows x 160 B = 3-row ring halo, halo words left and right, 16 B aligned start), issued
+//           by thread 0 for the NEXT tile into the other buffer while the CTA works on this one and
+//           completed through an mbarrier; pixels outside the plane are zero-filled by the TMA unit
+//           and are never part of a valid ring
 //   stage 1 every lane tests FOUR horizontally adjacent pixels per step with byte SIMD: a corner
 //           needs, for each opposite ring pair {k, k+8}, one pixel with |p - v| > t, so
 //           (F0|F8) & (F4|F12) with F = per-byte |p - v| > t (VABSDIFF4 + carry trick) is a
@@ -24,6 +28,8 @@
 //   emit    one global atomicAdd per CTA, coalesced write of packed corners (score<<24|y<<12|x)
 // Roofline: HBM, algorithmic bytes = one read of every level pixel (950 532 B per 640x480 frame);
 // the kernel is integer-issue bound.
+#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
+
 #include "vxorb_internal.h"
 
 namespace vxorb {
@@ -31,7 +37,9 @@ namespace vxorb {
 namespace {
 
 constexpr int FW = kFastScoreW, FSR = kFastScoreH;   // score region of a tile
-constexpr int TROWS = FSR + 6, TWORDS = FW / 4 + 2;  // tile rows, 32-bit words per tile row
+constexpr int TROWS = FSR + 6, TWORDS = FW / 4 + 8;  // tile rows, 32-bit words per tile row: 160 B, because a TMA box must
+                                                     // START on a 16 B boundary of the plane row, so up to 12 B of slack precede the tile
+constexpr uint32_t kTileBytes = TROWS * TWORDS * 4;
 constexpr int TPITCH = TWORDS * 4;
 constexpr int RPW = FSR / 8;                          // score rows per warp
 constexpr int QCAP = FW * FSR;
@@ -51,46 +59,102 @@ __device__ __forceinline__ uint32_t gt_flags(uint32_t d, uint32_t c) {
     return HI ? (lo & d) : (lo | d);
 }
 
+struct FastMaps {
+    CUtensorMap m[kMaxLevels];
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, int c0, int c1, int c2,
+                                            unsigned long long* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+            smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+        : "memory");
+}
+
 }  // namespace
 
 template <bool HI>
-__global__ void __launch_bounds__(256)
-fast_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint32_t* __restrict__ cand,
-            int* __restrict__ cand_n, int threshold, int border) {
-    __shared__ __align__(16) uint32_t tile[TROWS][TWORDS];
+__global__ void __launch_bounds__(256, 5)
+fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* __restrict__ cand,
+            int* __restrict__ cand_n, int threshold, int border, int tiles_per_frame, int total_tiles) {
+    struct __align__(128) TileBuf {
+        uint32_t w[TROWS][TWORDS];  // TMA destinations must be 128 B aligned: the struct alignment pads buffer 1
+    };
+    __shared__ TileBuf tiles[2];
     __shared__ __align__(16) uint8_t score[FSR][FW];
     __shared__ uint32_t queue[QCAP / 2];  // u16 entries: row * 128 + col in the score region
     __shared__ uint32_t outq[OCAP];
+    __shared__ __align__(8) unsigned long long mbar[2];
+    __shared__ int4 info[2];              // tile descriptor: level, X, Y, frame
     __shared__ int qn, on, obase;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int l = 0;
-    while (l + 1 < lt.n_levels && (int)blockIdx.x >= lt.fast_tile_begin[l + 1]) ++l;
-    const int tl = blockIdx.x - lt.fast_tile_begin[l];
-    const int tx = tl % lt.fast_tiles_x[l], ty = tl / lt.fast_tiles_x[l];
-    const int f = blockIdx.y;
-    const int w = lt.w[l], h = lt.h[l], pitch = lt.pitch[l];
-    const uint8_t* img = pyr + lt.off[l] + (size_t)f * lt.fstride[l];
 
-    // score region origin: X is a multiple of 4 so tile words are aligned words of the plane
-    const int X = ((border - 1) & ~3) + tx * kFastEmitW;
-    const int Y = (border - 1) + ty * kFastEmitH;
+    // thread 0: decode tile t, publish its descriptor and start its TMA load into buffer b
+    auto issue = [&](int t, int b) {
+        const int f = t / tiles_per_frame;
+        int tl = t - f * tiles_per_frame;
+        int l = 0;
+        while (l + 1 < lt.n_levels && tl >= lt.fast_tile_begin[l + 1]) ++l;
+        tl -= lt.fast_tile_begin[l];
+        const int ty = tl / lt.fast_tiles_x[l], tx = tl - ty * lt.fast_tiles_x[l];
+        // score region origin: X is a multiple of 4 so tile words are aligned words of the plane
+        const int X = ((border - 1) & ~3) + tx * kFastEmitW;
+        const int Y = (border - 1) + ty * kFastEmitH;
+        info[b] = make_int4(l, X, Y, f);
+        mbar_expect_tx(&mbar[b], kTileBytes);
+        // tensor map coordinates count from the plane allocation: kApronX bytes / kApronY rows before
+        // pixel (0, 0).  The box starts at the 16 B boundary at or below the tile's first byte (X - 4).
+        tma_load_3d(&tiles[b].w[0][0], &maps.m[l], (X - 4 + kApronX) & ~15, Y - 3 + kApronY, f, &mbar[b]);
+    };
 
-    {
-        const int max_word = (pitch - kApronX) / 4 - 1;  // last whole word of a plane row
-        for (int i = tid; i < TROWS * TWORDS; i += 256) {
-            const int r = i / TWORDS, c = i - r * TWORDS;
-            const int gy = min(max(Y - 3 + r, -kApronY), h + kApronY - 1);
-            const int gw = min(max(X / 4 - 1 + c, -(kApronX / 4)), max_word);
-            tile[r][c] = __ldg(reinterpret_cast<const uint32_t*>(img + (ptrdiff_t)gy * pitch) + gw);
-        }
-        for (int i = tid; i < FSR * FW / 16; i += 256) reinterpret_cast<uint4*>(&score[0][0])[i] = make_uint4(0, 0, 0, 0);
-        if (tid == 0) {
-            qn = 0;
-            on = 0;
-        }
+    if (tid == 0) {
+        mbar_init(&mbar[0], 1);
+        mbar_init(&mbar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        if ((int)blockIdx.x < total_tiles) issue(blockIdx.x, 0);
     }
+
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+    const int buf = it & 1;
+    uint32_t (*tile)[TWORDS] = tiles[buf].w;
+    if (tid == 0) {
+        const int tn = t + (int)gridDim.x;
+        if (tn < total_tiles) issue(tn, buf ^ 1);  // buffer buf^1 was released by the barrier ending the previous tile
+        qn = 0;
+        on = 0;
+    }
+    for (int i = tid; i < FSR * FW / 16; i += 256) reinterpret_cast<uint4*>(&score[0][0])[i] = make_uint4(0, 0, 0, 0);
     __syncthreads();
+    const int4 ti = info[buf];
+    const int l = ti.x, X = ti.y, Y = ti.z, f = ti.w;
+    const int w = lt.w[l], h = lt.h[l];
+    const int wo = ((X - 4 + kApronX) & 15) >> 2;  // words of slack before the tile's first word in a buffer row
+    mbar_wait(&mbar[buf], (uint32_t)(it >> 1) & 1u);
 
     // score domain (global coordinates, inclusive)
     const int sx_min = max(3, border - 1), sx_max = min(w - 4, w - border);
@@ -112,9 +176,9 @@ fast_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint32_t* __rest
             const int gy = Y + r;
             uint32_t q = 0;
             if (gy >= sy_min && gy <= sy_max) {
-                const uint32_t* row = &tile[r + 3][lane];
+                const uint32_t* row = &tile[r + 3][lane + wo];
                 const uint32_t wl = row[0], v = row[1], wr = row[2];
-                const uint32_t up = tile[r][lane + 1], dn = tile[r + 6][lane + 1];
+                const uint32_t up = tile[r][lane + 1 + wo], dn = tile[r + 6][lane + 1 + wo];
                 const uint32_t lf = __byte_perm(wl, v, 0x4321u), rt = __byte_perm(v, wr, 0x6543u);
                 const uint32_t f0 = gt_flags<HI>(__vabsdiffu4(dn, v), cadd);
                 const uint32_t f8 = gt_flags<HI>(__vabsdiffu4(up, v), cadd);
@@ -151,7 +215,7 @@ fast_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint32_t* __rest
 
     // ---- stage 2: cornerScore of two queued pixels per thread ---------------------------------
     {
-        const uint8_t* t8 = reinterpret_cast<const uint8_t*>(&tile[0][0]) + 3 * TPITCH + 4;
+        const uint8_t* t8 = reinterpret_cast<const uint8_t*>(&tile[0][0]) + 3 * TPITCH + 4 + 4 * wo;
         const int pairs = (nq + 1) >> 1;
         for (int pi = tid; pi < pairs; pi += 256) {
             const uint32_t u = queue[pi];
@@ -215,24 +279,62 @@ fast_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint32_t* __rest
     }
     __syncthreads();
     const int no = on;
-    if (no == 0) return;
-    const int cap = lt.cand_cap[l];
-    int* cn = cand_n + l * lt.batch + f;
-    if (tid == 0) obase = atomicAdd(cn, no);
-    __syncthreads();
-    uint32_t* out = cand + lt.cand_off[l] + (size_t)f * cap;
-    for (int i = tid; i < no; i += 256)
-        if (obase + i < cap) out[obase + i] = outq[i];
+    if (no > 0) {  // uniform over the CTA
+        const int cap = lt.cand_cap[l];
+        if (tid == 0) obase = atomicAdd(cand_n + l * lt.batch + f, no);
+        __syncthreads();
+        uint32_t* out = cand + lt.cand_off[l] + (size_t)f * cap;
+        for (int i = tid; i < no; i += 256)
+            if (obase + i < cap) out[obase + i] = outq[i];
+    }
+    __syncthreads();  // tile buffer, score map and queues are free for the next tile
+    }
+}
+
+// Per-level tensor maps over the pyramid planes: dims {pitch bytes, rows incl. apron, frames}, u8,
+// box {160, 46, 1}, no swizzle, zero fill outside.  The encoder is a driver entry point fetched
+// through the runtime, so the library still links against cudart only.
+static bool build_fast_maps(const LevelTab& lt, const uint8_t* pyr, FastMaps* out) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn)
+            return false;
+        encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    memset(out, 0, sizeof(*out));
+    for (int l = 0; l < lt.n_levels; ++l) {
+        if (!lt.active[l]) continue;
+        const size_t origin = plane_origin(lt.w[l]);
+        void* base = const_cast<uint8_t*>(pyr) + lt.off[l] - origin;
+        const cuuint64_t dims[3] = {(cuuint64_t)lt.pitch[l], (cuuint64_t)(lt.h[l] + 2 * kApronY),
+                                    (cuuint64_t)(lt.batch > 0 ? lt.batch : 1)};
+        const cuuint64_t strides[2] = {(cuuint64_t)lt.pitch[l], (cuuint64_t)lt.fstride[l]};
+        const cuuint32_t box[3] = {(cuuint32_t)(TWORDS * 4), (cuuint32_t)TROWS, 1u};
+        const cuuint32_t estr[3] = {1u, 1u, 1u};
+        if (encode(&out->m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return false;
+    }
+    return true;
 }
 
 int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s) {
     const int tiles = lt.fast_tile_begin[lt.n_levels];
-    if (tiles == 0) return 0;
-    dim3 grid(tiles, lt.batch);
+    if (tiles == 0 || lt.batch <= 0) return 0;
+    FastMaps maps;
+    if (!build_fast_maps(lt, db.pyr, &maps)) return -1;
+    const int total = tiles * lt.batch;
+    const int grid = total < 148 * 5 ? total : 148 * 5;  // persistent: 5 CTAs of 8 warps per SM
     if (threshold >= 128)
-        fast_kernel<true><<<grid, 256, 0, s>>>(lt, db.pyr, db.cand, db.cand_n, threshold, border);
+        fast_kernel<true><<<grid, 256, 0, s>>>(lt, maps, db.cand, db.cand_n, threshold, border, tiles, total);
     else
-        fast_kernel<false><<<grid, 256, 0, s>>>(lt, db.pyr, db.cand, db.cand_n, threshold, border);
+        fast_kernel<false><<<grid, 256, 0, s>>>(lt, maps, db.cand, db.cand_n, threshold, border, tiles, total);
     return 1;
 }
 
