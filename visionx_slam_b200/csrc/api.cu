@@ -162,6 +162,7 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
     int coef_off = 0;
     std::vector<uint32_t> coef;
     lt.fast_tile_begin[0] = lt.blur_tile_begin[0] = 0;
+    lt.resize_band = 1;
     for (int l = 0; l < p.n_levels; ++l) {
         if (lt.w[l] < 1 || lt.h[l] < 1) {  // pyramid bottoms out: drop the remaining levels
             lt.n_levels = l;
@@ -191,7 +192,17 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
             build_resize_taps(lt.w[l - 1], lt.w[l], coef.data() + coef_off);
             build_resize_taps(lt.h[l - 1], lt.h[l], coef.data() + coef_off + lt.w[l]);
             lt.resize_fast[l] = resize_taps_fit_fast_path(coef.data() + coef_off, lt.w[l]) ? 1 : 0;
+            const bool banded = lt.resize_fast[l] && lt.w[l] >= 8 &&
+                                plan_resize_bands(coef.data() + coef_off + lt.w[l], lt.h[l], lt.h[l - 1], lt.pitch[l - 1],
+                                                  &lt.band_rows[l], &lt.n_bands[l], &lt.band_smem[l]);
+            if (!banded) lt.resize_band = 0;
             coef_off += lt.w[l] + lt.h[l];
+            coef_off = (coef_off + 3) & ~3;  // uint4 alignment of the per-word table
+            const int words = (lt.w[l] + 3) / 4;
+            lt.xw_off[l] = coef_off;
+            coef.resize((size_t)coef_off + (size_t)words * 6);
+            build_resize_words(coef.data() + lt.coef_off[l], lt.w[l], coef.data() + coef_off);
+            coef_off += words * 6;
         }
     }
     for (int l = lt.n_levels; l < kMaxLevels; ++l) {
@@ -286,9 +297,7 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
     // cand_n / fin_n are indexed [level * batch + frame] with the launch's batch
     {
         StageScope sc(h, s, VXORB_STAGE_PYRAMID);
-        int n = launch_pyramid(lt, d, s);
-        n += launch_apron(lt, d, s);
-        sc.end(n);
+        sc.end(launch_pyramid(lt, d, s));
     }
     {
         StageScope sc(h, s, VXORB_STAGE_FAST);
@@ -555,6 +564,7 @@ int vxorb_create(const vxorb_params* p, vxorb_handle** out) {
     if ((e = cudaEventCreate(&h->t_end)) != cudaSuccess) return bail(e, "event");
     if ((e = init_device_tables()) != cudaSuccess) return bail(e, "pattern upload");
     if ((e = init_match_kernels()) != cudaSuccess) return bail(e, "match kernel attributes");
+    if ((e = init_pyramid_kernels()) != cudaSuccess) return bail(e, "pyramid kernel attributes");
     *out = h;
     return VXORB_OK;
 }
@@ -1146,7 +1156,7 @@ int vxorb_debug_blur(vxorb_handle* h, const uint8_t* src, int width, int height,
     if (rc) return rc;
     cudaStream_t s = h->ws[0].stream;
     CK(cudaMemcpy2DAsync(db.pyr + lt.off[0], lt.pitch[0], src, stride, width, height, cudaMemcpyHostToDevice, s));
-    h->launches += launch_apron(lt, db, s);
+    h->launches += launch_apron(lt, db, lt.n_levels, s);
     h->launches += launch_blur(lt, db, s);
     CK(cudaGetLastError());
     CK(cudaMemcpy2DAsync(dst, dstride, db.blur + lt.off[0], lt.pitch[0], width, height, cudaMemcpyDeviceToHost, s));

@@ -10,6 +10,8 @@
 // l = 1..7 (1 569 878 B at 640x480).  One launch per level covers the whole batch (grid.z = frame).
 #include <math.h>
 
+#include <algorithm>
+
 #include "vxorb_internal.h"
 
 namespace vxorb {
@@ -209,6 +211,149 @@ bool resize_taps_fit_fast_path(const uint32_t* xtaps, int dw) {
     return true;
 }
 
+// ---- band kernel: the production path of the pyramid -----------------------------------------------
+// One CTA produces a band of output rows of one frame.  The source rows the band needs are ONE
+// contiguous chunk of the previous level's plane (rows are pitch-strided and a band takes whole
+// rows), so thread 0 fetches them with a single bulk async copy (cp.async.bulk, completion on an
+// mbarrier) into shared memory; 6-8 CTAs are resident per SM, so other bands compute while this
+// one's copy is in flight.  Every (output row, output word) item is then independent: two source
+// rows x (3 LDS, funnel shift to the first tap, 2 PRMT, 4 IDP.2A) for the horizontal pass and
+// 2 IMAD per pixel for the vertical pass.  The per-word tap state (weights, PRMT selectors, word
+// index, shift) comes precomputed from the host (6 words per output word, build_resize_words).
+// Warp w of the CTA takes rows w, w+8, ... of the band; lanes take consecutive output words.
+// The band's CTA also writes the reflect-101 apron of its rows (and of the plane's top / bottom for
+// the first / last band), which the blur reads; the last band absorbs the remainder rows so that it
+// always holds the rows the bottom apron mirrors.
+void build_resize_words(const uint32_t* xtaps, int dw, uint32_t* out) {
+    const int words = (dw + 3) / 4;
+    for (int k = 0; k < words; ++k) {
+        int ofs[4];
+        uint32_t wgt[4];
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t t = xtaps[std::min(4 * k + j, dw - 1)];
+            ofs[j] = (int)(t & 0xffffu);
+            const uint32_t c1 = t >> 16;
+            wgt[j] = (256u - c1) | (c1 << 16);
+        }
+        const int e1 = ofs[1] - ofs[0], e2 = ofs[2] - ofs[0], e3 = ofs[3] - ofs[0];
+        const uint32_t sel01 = (uint32_t)(0 | (1 << 4) | (e1 << 8) | ((e1 + 1) << 12));
+        const uint32_t sel23 = (uint32_t)(e2 | ((e2 + 1) << 4) | (e3 << 8) | ((e3 + 1) << 12));
+        uint32_t* o = out + (size_t)k * 4;
+        o[0] = wgt[0]; o[1] = wgt[1]; o[2] = wgt[2]; o[3] = wgt[3];
+        uint32_t* o2 = out + (size_t)words * 4 + (size_t)k * 2;
+        o2[0] = sel01 | (sel23 << 16);
+        o2[1] = (uint32_t)(kApronX / 4 + (ofs[0] >> 2)) | ((uint32_t)(ofs[0] & 3) * 8u) << 16;
+    }
+}
+
+namespace {
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+}  // namespace
+
+__global__ void __launch_bounds__(256)
+resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, size_t sfstride,
+                   uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
+                   const uint32_t* __restrict__ ytab, const uint4* __restrict__ xw4, const uint2* __restrict__ xw2,
+                   int words, int band_rows, int n_bands) {
+    extern __shared__ __align__(128) uint8_t rows_sm[];
+    __shared__ __align__(8) unsigned long long bar;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.x;
+    const int y_begin = b * band_rows, y_end = (b == n_bands - 1) ? dh : y_begin + band_rows;
+    const int jlo = (int)(__ldg(ytab + y_begin) & 0xffffu);
+    const int jhi = min((int)(__ldg(ytab + y_end - 1) & 0xffffu) + 1, sh - 1);
+    dst += (size_t)blockIdx.y * dfstride;
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(&bar)), "r"(1) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const uint32_t bytes = (uint32_t)(jhi - jlo + 1) * (uint32_t)spitch;
+        const uint8_t* g = src_plane + (size_t)blockIdx.y * sfstride + (size_t)(jlo + kApronY) * spitch;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&bar)), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         smem_addr(rows_sm)),
+                     "l"(g), "r"(bytes), "r"(smem_addr(&bar))
+                     : "memory");
+    }
+    __syncthreads();  // barrier initialised before anyone polls it
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "RW_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra RD_%=;\n"
+        "bra RW_%=;\n"
+        "RD_%=:\n"
+        "}\n" ::"r"(smem_addr(&bar)),
+        "r"(0)
+        : "memory");
+
+    const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(rows_sm);
+    const int spitch_w = spitch >> 2;
+    for (int k0 = 0; k0 < words; k0 += 32) {
+        const int k = k0 + lane;
+        const bool active = k < words;
+        const int kk = active ? k : words - 1;
+        const uint4 wg = __ldg(xw4 + kk);
+        const uint2 sx = __ldg(xw2 + kk);
+        const uint32_t sel01 = sx.x & 0xffffu, sel23 = sx.x >> 16;
+        const int wofs = (int)(sx.y & 0xffffu);
+        const uint32_t shift = sx.y >> 16;
+        for (int y = y_begin + warp; y < y_end; y += 8) {
+            const uint32_t ty = __ldg(ytab + y);
+            const int j0 = (int)(ty & 0xffffu);
+            const uint32_t cy1 = ty >> 16, cy0 = 256u - cy1;
+            const int j1 = min(j0 + 1, sh - 1);
+            const uint32_t* p0 = sm_w + (j0 - jlo) * spitch_w + wofs;
+            const uint32_t* p1 = sm_w + (j1 - jlo) * spitch_w + wofs;
+            uint32_t h0[4], h1[4];
+            {
+                const uint32_t w0 = p0[0], w1 = p0[1], w2 = p0[2];
+                const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
+                const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
+                h0[0] = __dp2a_lo(wg.x, b01, 0u);
+                h0[1] = __dp2a_hi(wg.y, b01, 0u);
+                h0[2] = __dp2a_lo(wg.z, b23, 0u);
+                h0[3] = __dp2a_hi(wg.w, b23, 0u);
+            }
+            {
+                const uint32_t w0 = p1[0], w1 = p1[1], w2 = p1[2];
+                const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
+                const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
+                h1[0] = __dp2a_lo(wg.x, b01, 0u);
+                h1[1] = __dp2a_hi(wg.y, b01, 0u);
+                h1[2] = __dp2a_lo(wg.z, b23, 0u);
+                h1[3] = __dp2a_hi(wg.w, b23, 0u);
+            }
+            uint32_t v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = h1[j] * cy1 + (h0[j] * cy0 + (1u << 15));  // 16.16, byte 2 = result
+            if (active)
+                *reinterpret_cast<uint32_t*>(dst + (size_t)y * dpitch + 4 * k) =
+                    __byte_perm(__byte_perm(v[0], v[1], 0x0062u), __byte_perm(v[2], v[3], 0x0062u), 0x5410u);
+        }
+    }
+    __syncthreads();  // the band's pixels are visible to this CTA
+
+    // reflect-101 apron, left / right: x = -1,-2,-3 <- 1,2,3 ; x = w,w+1,w+2 <- w-2,w-3,w-4
+    const int nrows = y_end - y_begin;
+    for (int i = tid; i < nrows * 6; i += 256) {
+        const int r = i / 6, c = i - r * 6;
+        uint8_t* row = dst + (size_t)(y_begin + r) * dpitch;
+        if (c < 3) row[-1 - c] = row[1 + c];
+        else row[dw + (c - 3)] = row[dw - 2 - (c - 3)];
+    }
+    if (b != 0 && b != n_bands - 1) return;
+    __syncthreads();
+    // top: rows -1,-2,-3 <- 1,2,3 ; bottom: rows h,h+1,h+2 <- h-2,h-3,h-4 (x from -3 to w+2)
+    const int span = dw + 2 * kApronY;
+    for (int i = tid; i < 3 * span; i += 256) {
+        const int r = i / span, x = i - r * span - kApronY;
+        if (b == 0) dst[(ptrdiff_t)(-1 - r) * dpitch + x] = dst[(ptrdiff_t)(1 + r) * dpitch + x];
+        if (b == n_bands - 1) dst[(ptrdiff_t)(dh + r) * dpitch + x] = dst[(ptrdiff_t)(dh - 2 - r) * dpitch + x];
+    }
+}
+
 static void launch_resize(const uint8_t* src, int sw, int sh, int spitch, size_t sfstride, uint8_t* dst, int dw,
                           int dh, int dpitch, size_t dfstride, const uint32_t* xtab, const uint32_t* ytab, int batch,
                           bool fast, cudaStream_t s) {
@@ -239,14 +384,59 @@ int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t
     return 1;
 }
 
+// Picks the band height of one level: the largest of 16 / 8 / 4 rows whose biggest source chunk
+// (the last band takes the remainder rows, so it is the largest) stays under 40 KB of shared memory.
+bool plan_resize_bands(const uint32_t* ytaps, int dh, int sh, int spitch, int* band_rows, int* n_bands, int* smem) {
+    if (dh < 8) return false;
+    for (int rows = 16; rows >= 4; rows >>= 1) {
+        const int nb = std::max(1, dh / rows);
+        int worst = 0;
+        for (int b = 0; b < nb; ++b) {
+            const int y0 = b * rows, y1 = (b == nb - 1) ? dh : y0 + rows;
+            const int jlo = (int)(ytaps[y0] & 0xffffu), jhi = std::min((int)(ytaps[y1 - 1] & 0xffffu) + 1, sh - 1);
+            worst = std::max(worst, jhi - jlo + 1);
+        }
+        const long long bytes = (long long)worst * spitch;
+        if (bytes <= 40 * 1024 || (rows == 4 && bytes <= 200 * 1024)) {
+            *band_rows = rows;
+            *n_bands = nb;
+            *smem = (int)bytes;
+            return true;
+        }
+    }
+    return false;
+}
+
+cudaError_t init_pyramid_kernels() {
+    return cudaFuncSetAttribute(resize_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+}
+
+// Builds levels 1.. of every frame and the reflect-101 apron of every level.  Returns launches.
 int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
     int launches = 0;
+    if (lt.resize_band) {
+        launches += launch_apron(lt, db, 1, s);  // level 0 comes from the upload; the bands write their own apron
+        for (int l = 1; l < lt.n_levels; ++l) {
+            const int words = (lt.w[l] + 3) / 4;
+            const uint32_t* tab = db.coef + lt.coef_off[l];
+            const uint4* xw4 = reinterpret_cast<const uint4*>(db.coef + lt.xw_off[l]);
+            const uint2* xw2 = reinterpret_cast<const uint2*>(db.coef + lt.xw_off[l] + 4 * words);
+            const uint8_t* src_plane = db.pyr + lt.off[l - 1] - plane_origin(lt.w[l - 1]);
+            dim3 grid(lt.n_bands[l], lt.batch);
+            resize_band_kernel<<<grid, 256, lt.band_smem[l], s>>>(
+                src_plane, lt.h[l - 1], lt.pitch[l - 1], (size_t)lt.fstride[l - 1], db.pyr + lt.off[l], lt.w[l], lt.h[l],
+                lt.pitch[l], (size_t)lt.fstride[l], tab + lt.w[l], xw4, xw2, words, lt.band_rows[l], lt.n_bands[l]);
+            ++launches;
+        }
+        return launches;
+    }
     for (int l = 1; l < lt.n_levels; ++l) {
         launch_resize(db.pyr + lt.off[l - 1], lt.w[l - 1], lt.h[l - 1], lt.pitch[l - 1], (size_t)lt.fstride[l - 1],
                       db.pyr + lt.off[l], lt.w[l], lt.h[l], lt.pitch[l], (size_t)lt.fstride[l],
                       db.coef + lt.coef_off[l], db.coef + lt.coef_off[l] + lt.w[l], lt.batch, lt.resize_fast[l] != 0, s);
         ++launches;
     }
+    launches += launch_apron(lt, db, lt.n_levels, s);
     return launches;
 }
 
@@ -263,10 +453,10 @@ __device__ __forceinline__ int reflect101(int i, int n) {
     return i;
 }
 
-__global__ void __launch_bounds__(256) apron_kernel(const LevelTab lt, uint8_t* __restrict__ pyr) {
+__global__ void __launch_bounds__(256) apron_kernel(const LevelTab lt, uint8_t* __restrict__ pyr, int levels) {
     int idx = blockIdx.x * 256 + threadIdx.x;
     const int f = blockIdx.y;
-    for (int l = 0; l < lt.n_levels; ++l) {
+    for (int l = 0; l < levels; ++l) {
         const int w = lt.w[l], h = lt.h[l];
         const int horiz = 2 * kApronY * (w + 2 * kApronY), vert = 2 * kApronY * h;
         if (idx < horiz + vert) {
@@ -290,12 +480,13 @@ __global__ void __launch_bounds__(256) apron_kernel(const LevelTab lt, uint8_t* 
     }
 }
 
-int launch_apron(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
+int launch_apron(const LevelTab& lt, const DeviceBuffers& db, int levels, cudaStream_t s) {
     int items = 0;
-    for (int l = 0; l < lt.n_levels; ++l) items += 2 * kApronY * (lt.w[l] + 2 * kApronY) + 2 * kApronY * lt.h[l];
+    levels = std::min(levels, lt.n_levels);
+    for (int l = 0; l < levels; ++l) items += 2 * kApronY * (lt.w[l] + 2 * kApronY) + 2 * kApronY * lt.h[l];
     if (items == 0) return 0;
     dim3 grid((items + 255) / 256, lt.batch);
-    apron_kernel<<<grid, 256, 0, s>>>(lt, db.pyr);
+    apron_kernel<<<grid, 256, 0, s>>>(lt, db.pyr, levels);
     return 1;
 }
 

@@ -70,6 +70,10 @@ struct LevelTab {
     int blur_tiles_x[kMaxLevels], blur_tile_begin[kMaxLevels + 1];
     int coef_off[kMaxLevels];        // offset (in u32) of level l's resize tables: x[w_l] then y[h_l]
     int resize_fast[kMaxLevels];     // level l's x taps fit the register-resident resize kernel
+    // band kernel (pyramid.cu): per-word tap table at coef + xw_off[l] (uint4[words] then uint2[words]),
+    // rows per band, band count and the shared-memory bytes of the largest band's source chunk
+    int xw_off[kMaxLevels], band_rows[kMaxLevels], n_bands[kMaxLevels], band_smem[kMaxLevels];
+    int resize_band;                 // every level above 0 can use the band kernel
 };
 
 struct DeviceBuffers {
@@ -101,7 +105,10 @@ int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh,
                          int dpitch, const uint32_t* xtab, const uint32_t* ytab, bool fast, cudaStream_t s);
 bool resize_taps_fit_fast_path(const uint32_t* xtaps, int dw);
-int launch_apron(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
+int launch_apron(const LevelTab& lt, const DeviceBuffers& db, int levels, cudaStream_t s);
+void build_resize_words(const uint32_t* xtaps, int dw, uint32_t* out);  // 6 words per output word
+bool plan_resize_bands(const uint32_t* ytaps, int dh, int sh, int spitch, int* band_rows, int* n_bands, int* smem);
+cudaError_t init_pyramid_kernels();
 int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s);
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_blur(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
