@@ -280,7 +280,7 @@ def run_ours(args, rank, world, local_rank):
 
     # -------- e2e: pinned host frames in, keypoints + descriptors + matches out ------------------
     slots = h.track_slots()
-    chunks = max(1, min(slots, 2))  # chunks in flight
+    chunks = max(1, min(slots, 3))  # chunks in flight: with 3 the H2D of chunk i+2 hides behind the kernels of chunk i
     pin_in = [vx.PinnedArray((B, H, W), np.uint8) for _ in range(chunks)]
     for p in pin_in:
         p.array[:] = seq

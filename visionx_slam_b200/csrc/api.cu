@@ -321,7 +321,9 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
         o.xy = d.xy + (size_t)h->kp_cap * 2;
         o.kp_n = d.kp_n + 1;
         o.kp_total = d.kp_total + 1;
-        sc.end(launch_describe(lt, o, h->kp_cap, s));
+        const int n = launch_describe(lt, o, h->kp_cap, s);
+        if (n < 0) return fail(h, VXORB_E_CUDA, "cuTensorMapEncodeTiled failed for the descriptor window maps");
+        sc.end(n);
     }
     CK(cudaGetLastError());
     return VXORB_OK;

@@ -5,20 +5,24 @@
 // what ORBExtractor::Extract copies into Frame::Features() / Frame::Descriptors()
 // (orb_extractor.cpp:19-26), in canonical (octave, y, x) order.
 //
-// One warp owns a group of G consecutive keypoints of one frame (G = 16, or 4 for tiny batches):
-//   setup        lane i looks up keypoint i of the group (level, x, y, response); every lane keeps
-//                the 16 pattern points of "its" descriptor byte as floats in registers and the
-//                disc weights of "its" patch row (u values and a 0/1 mask as s8x4 / u8x4 words)
-//   orientation  per keypoint: lane = patch row v; nine aligned 32-bit loads, a funnel shift to
-//                the patch origin, then IDP.4A does the work: m10 += dp4a(pixels, u-weights),
-//                rowsum += dp4a(pixels, mask), m01 += v*rowsum; two REDUX adds per keypoint
+// One warp owns a group of G consecutive keypoints of one frame (G = 16, or 4 for tiny batches).
+// Both per-keypoint windows are brought into shared memory by the TMA unit, one instruction each
+// (cp.async.bulk.tensor.3d over the per-level plane tensor maps, box start rounded down to 16 B),
+// double buffered per warp with an mbarrier per buffer, so the window of keypoint i+1 is in flight
+// while keypoint i is processed and no lane computes a global address:
+//   orientation  31 rows x 48 B of the un-blurred level.  lane = patch row v; nine LDS words, a
+//                funnel shift to the patch origin, then IDP.4A does the work:
+//                m10 += dp4a(pixels, u-weights), rowsum += dp4a(pixels, mask), m01 += v*rowsum;
+//                two REDUX adds per keypoint
 //   angle        all lanes at once, lane i for keypoint i: fastAtan2 polynomial with un-fused
-//                float ops (degrees), then cos/sin in double — once per group instead of once
-//                per keypoint-warp
-//   descriptor   per keypoint: lane i produces byte i: 8 comparisons of blurred pixels at pattern
-//                points rotated by the angle (float un-fused rotate, round-half-even via the
-//                1.5*2^23 trick so the rounded coordinates feed the address IMAD directly)
+//                float ops (degrees), then cos/sin in double — once per group
+//   descriptor   37 rows x 64 B of the blurred level (pattern radius 18.4 -> |offset| <= 18).
+//                lane i produces byte i: 8 comparisons of blurred pixels at pattern points rotated
+//                by the angle (float un-fused rotate, round-half-even via the 1.5*2^23 trick so the
+//                rounded coordinates feed the shared-memory address IMAD directly); the 16 byte
+//                gathers per lane are LDS.U8 instead of scattered global loads
 // Float rules are load-bearing: every op is an explicit *_rn intrinsic so nvcc cannot contract.
+#include <cuda.h>
 #include <float.h>
 
 #include "vxorb_internal.h"
@@ -73,14 +77,73 @@ __device__ __forceinline__ int dp4a_us(uint32_t pixels, uint32_t weights_s8, int
     return d;
 }
 
+namespace {
+
+constexpr int kPaW = 48, kPaH = 31, kPaBytes = kPaW * kPaH, kPaStride = 1536;  // orientation window (un-blurred)
+constexpr int kPbW = 64, kPbH = 37, kPbBytes = kPbW * kPbH, kPbStride = 2432;  // descriptor window (blurred)
+constexpr int kDescWarps = 4;
+
+struct DescMaps {
+    CUtensorMap pyr[kMaxLevels];
+    CUtensorMap blur[kMaxLevels];
+};
+
+__device__ __forceinline__ uint32_t s_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bar_init(uint32_t bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "DW_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DD_%=;\n"
+        "bra DW_%=;\n"
+        "DD_%=:\n"
+        "}\n" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+// one lane: arm the barrier with the box size and start the box load
+__device__ __forceinline__ void box_load(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar,
+                                         uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+}  // namespace
+
 __global__ void __launch_bounds__(128)
-describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
-                const uint32_t* __restrict__ fin_key, const float* __restrict__ fin_resp,
+describe_kernel(const LevelTab lt, const __grid_constant__ DescMaps maps, const uint32_t* __restrict__ fin_key, const float* __restrict__ fin_resp,
                 const int* __restrict__ fin_n, int kp_cap, int group, vxorb_keypoint* __restrict__ kp_out,
                 uint8_t* __restrict__ desc_out, float* __restrict__ xy_out, int* __restrict__ kp_n,
                 int* __restrict__ kp_total, int* __restrict__ status) {
+    __shared__ __align__(128) uint8_t win_a[kDescWarps][2][kPaStride];
+    __shared__ __align__(128) uint8_t win_b[kDescWarps][2][kPbStride];
+    __shared__ __align__(8) unsigned long long bars[kDescWarps][4];  // [0,1]: orientation buffers, [2,3]: descriptor buffers
     const int f = blockIdx.y;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) bar_init(s_addr(&bars[wid][i]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
     const int g0 = (blockIdx.x * 4 + (threadIdx.x >> 5)) * group;  // first keypoint of this warp's group
 
     // ---- setup: locate keypoint g0 + lane from the per-level counts -----------------------------
@@ -143,18 +206,39 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
         wm[j] = m;
     }
 
-    // ---- orientation moments, one keypoint at a time, lane = patch row --------------------------
-    int my_m10 = 0, my_m01 = 0;
-    for (int i = 0; i < n_here; ++i) {
+    const uint32_t bar0 = s_addr(&bars[wid][0]);
+    const uint32_t wa0 = s_addr(&win_a[wid][0][0]), wb0 = s_addr(&win_b[wid][0][0]);
+    // window loads of keypoint i (lane 0 only): box start = 16 B boundary at or below the first byte
+    auto load_a = [&](int i) {
         const int kx = __shfl_sync(0xffffffffu, x, i), ky = __shfl_sync(0xffffffffu, y, i);
         const int kl = __shfl_sync(0xffffffffu, level, i);
-        const int pitch = lt.pitch[kl];
-        const uint8_t* row = pyr + lt.off[kl] + (size_t)f * lt.fstride[kl] + (ptrdiff_t)(ky + min(v, 15)) * pitch + (kx - 15);
-        const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(row) & 3u) * 8u;
-        const uint32_t* wp = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(row) & ~(uintptr_t)3);
+        if (lane == 0)
+            box_load(wa0 + (i & 1) * kPaStride, &maps.pyr[kl], (kx - 15 + kApronX) & ~15, ky - 15 + kApronY, f,
+                     bar0 + (i & 1) * 8, kPaBytes);
+    };
+    auto load_b = [&](int i) {
+        const int kx = __shfl_sync(0xffffffffu, x, i), ky = __shfl_sync(0xffffffffu, y, i);
+        const int kl = __shfl_sync(0xffffffffu, level, i);
+        if (lane == 0)
+            box_load(wb0 + (i & 1) * kPbStride, &maps.blur[kl], (kx - 18 + kApronX) & ~15, ky - 18 + kApronY, f,
+                     bar0 + 16 + (i & 1) * 8, kPbBytes);
+    };
+
+    // ---- orientation moments, one keypoint at a time, lane = patch row --------------------------
+    load_a(0);
+    int my_m10 = 0, my_m01 = 0;
+    const uint32_t my_row = (uint32_t)min(lane, kPaH - 1) * kPaW;
+    for (int i = 0; i < n_here; ++i) {
+        if (i + 1 < n_here) load_a(i + 1);  // the other buffer was drained by the __syncwarp ending keypoint i-1
+        else load_b(0);                     // last orientation window: start the first descriptor window
+        const int kx = __shfl_sync(0xffffffffu, x, i);
+        const uint32_t off = (uint32_t)(kx - 15 + kApronX) & 15u;
+        const uint32_t sh = (off & 3u) * 8u;
+        const uint32_t rw = wa0 + (i & 1) * kPaStride + my_row + (off & ~3u);
+        bar_wait(bar0 + (i & 1) * 8, (uint32_t)(i >> 1) & 1u);
         uint32_t wd[9];
 #pragma unroll
-        for (int j = 0; j < 9; ++j) wd[j] = __ldg(wp + j);
+        for (int j = 0; j < 9; ++j) wd[j] = lds_u32(rw + 4 * j);
         int m10 = 0;
         uint32_t rs = 0;
 #pragma unroll
@@ -170,6 +254,7 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
             my_m10 = m10;
             my_m01 = m01;
         }
+        __syncwarp();  // every lane is done with this window before lane 0 refills its buffer
     }
 
     // ---- angle, cos/sin and the keypoint record: lane i for keypoint i --------------------------
@@ -193,28 +278,29 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
     // ---- rotated BRIEF, one keypoint at a time, lane = descriptor byte ---------------------------
     const float magic = 12582912.0f;  // 1.5 * 2^23: low mantissa bits of (t + magic) = round-half-even(t)
     for (int i = 0; i < n_here; ++i) {
-        const int kx = __shfl_sync(0xffffffffu, x, i), ky = __shfl_sync(0xffffffffu, y, i);
-        const int kl = __shfl_sync(0xffffffffu, level, i);
+        if (i + 1 < n_here) load_b(i + 1);
+        const int kx = __shfl_sync(0xffffffffu, x, i);
         const float c = __shfl_sync(0xffffffffu, ca, i), s = __shfl_sync(0xffffffffu, sa, i);
-        const int pitch = lt.pitch[kl];
-        // address = centre + iy*pitch + ix with iy = bits(ty) - bits(magic), ix likewise
-        const uint8_t* bc = blur + lt.off[kl] + (size_t)f * lt.fstride[kl] + (ptrdiff_t)ky * pitch + kx -
-                            (ptrdiff_t)0x4B400000 * pitch - (ptrdiff_t)0x4B400000;
+        const uint32_t off = (uint32_t)(kx - 18 + kApronX) & 15u;
+        // address = window centre + iy*64 + ix with iy = bits(ty) - bits(magic), ix likewise (mod 2^32)
+        const uint32_t bc = wb0 + (i & 1) * kPbStride + 18u * kPbW + 18u + off - 0x4B400000u * (uint32_t)kPbW - 0x4B400000u;
+        bar_wait(bar0 + 16 + (i & 1) * 8, (uint32_t)(i >> 1) & 1u);
         unsigned byte = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            int t[2];
+            uint32_t t[2];
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const float xx = px[2 * k + e], yy = py[2 * k + e];
                 const float rx = __fsub_rn(__fmul_rn(xx, c), __fmul_rn(yy, s));
                 const float ry = __fadd_rn(__fmul_rn(xx, s), __fmul_rn(yy, c));
-                const int bx = __float_as_int(__fadd_rn(rx, magic)), by = __float_as_int(__fadd_rn(ry, magic));
-                t[e] = __ldg(bc + (ptrdiff_t)by * pitch + bx);
+                const uint32_t bx = __float_as_uint(__fadd_rn(rx, magic)), by = __float_as_uint(__fadd_rn(ry, magic));
+                t[e] = lds_u8(bc + by * (uint32_t)kPbW + bx);
             }
             byte |= (t[0] < t[1] ? 1u : 0u) << k;
         }
         desc_out[((size_t)f * kp_cap + g0 + i) * 32 + lane] = (uint8_t)byte;
+        __syncwarp();  // every lane is done with this window before lane 0 refills its buffer
     }
 }
 
@@ -234,9 +320,13 @@ int launch_describe(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, cud
     // frame still spreads over ~80 CTAs
     const int group = lt.batch >= 8 ? 16 : 4;
     const int warps = (kp_cap + group - 1) / group;
-    dim3 grid((warps + 3) / 4, lt.batch);
-    describe_kernel<<<grid, 128, 0, s>>>(lt, db.pyr, db.blur, db.fin_key, db.fin_resp, db.fin_n, kp_cap, group, db.kp,
-                                         db.desc, db.xy, db.kp_n, db.kp_total, db.status);
+    DescMaps maps;
+    if (!build_plane_maps(lt, db.pyr, kPaW, kPaH, false, maps.pyr) ||
+        !build_plane_maps(lt, db.blur, kPbW, kPbH, false, maps.blur))
+        return -1;
+    dim3 grid((warps + kDescWarps - 1) / kDescWarps, lt.batch);
+    describe_kernel<<<grid, 32 * kDescWarps, 0, s>>>(lt, maps, db.fin_key, db.fin_resp, db.fin_n, kp_cap, group, db.kp,
+                                                     db.desc, db.xy, db.kp_n, db.kp_total, db.status);
     return 1;
 }
 

@@ -291,10 +291,11 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
     }
 }
 
-// Per-level tensor maps over the pyramid planes: dims {pitch bytes, rows incl. apron, frames}, u8,
-// box {160, 46, 1}, no swizzle, zero fill outside.  The encoder is a driver entry point fetched
-// through the runtime, so the library still links against cudart only.
-static bool build_fast_maps(const LevelTab& lt, const uint8_t* pyr, FastMaps* out) {
+// Per-level tensor maps over pyramid-shaped planes (pyr or blur): dims {pitch bytes, rows incl. apron,
+// frames}, u8, box {box_w, box_h, 1}, no swizzle, zero fill outside.  `out` is CUtensorMap[kMaxLevels].
+// The encoder is a driver entry point fetched through the runtime, so the library still links
+// against cudart only.
+bool build_plane_maps(const LevelTab& lt, const uint8_t* planes, int box_w, int box_h, bool active_only, void* out_maps) {
     typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -306,17 +307,18 @@ static bool build_fast_maps(const LevelTab& lt, const uint8_t* pyr, FastMaps* ou
             return false;
         encode = reinterpret_cast<EncodeFn>(fn);
     }
-    memset(out, 0, sizeof(*out));
+    CUtensorMap* out = static_cast<CUtensorMap*>(out_maps);
+    memset(out, 0, sizeof(CUtensorMap) * kMaxLevels);
     for (int l = 0; l < lt.n_levels; ++l) {
-        if (!lt.active[l]) continue;
+        if (active_only && !lt.active[l]) continue;
         const size_t origin = plane_origin(lt.w[l]);
-        void* base = const_cast<uint8_t*>(pyr) + lt.off[l] - origin;
+        void* base = const_cast<uint8_t*>(planes) + lt.off[l] - origin;
         const cuuint64_t dims[3] = {(cuuint64_t)lt.pitch[l], (cuuint64_t)(lt.h[l] + 2 * kApronY),
                                     (cuuint64_t)(lt.batch > 0 ? lt.batch : 1)};
         const cuuint64_t strides[2] = {(cuuint64_t)lt.pitch[l], (cuuint64_t)lt.fstride[l]};
-        const cuuint32_t box[3] = {(cuuint32_t)(TWORDS * 4), (cuuint32_t)TROWS, 1u};
+        const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1u};
         const cuuint32_t estr[3] = {1u, 1u, 1u};
-        if (encode(&out->m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr,
+        if (encode(&out[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
             return false;
@@ -328,7 +330,7 @@ int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int 
     const int tiles = lt.fast_tile_begin[lt.n_levels];
     if (tiles == 0 || lt.batch <= 0) return 0;
     FastMaps maps;
-    if (!build_fast_maps(lt, db.pyr, &maps)) return -1;
+    if (!build_plane_maps(lt, db.pyr, TWORDS * 4, TROWS, true, maps.m)) return -1;
     const int total = tiles * lt.batch;
     const int grid = total < 148 * 5 ? total : 148 * 5;  // persistent: 5 CTAs of 8 warps per SM
     if (threshold >= 128)

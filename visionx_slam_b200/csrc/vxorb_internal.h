@@ -135,6 +135,8 @@ int launch_match_compact(const vxorb_knn2_t* knn, const vxorb_knn2_t* back, int 
 int launch_flush(uint8_t* buf, size_t bytes, cudaStream_t s);
 int launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t s);
 
+// CUtensorMap[kMaxLevels] over pyramid-shaped planes, box {box_w (multiple of 16), box_h, 1 frame}; fast.cu
+bool build_plane_maps(const LevelTab& lt, const uint8_t* planes, int box_w, int box_h, bool active_only, void* out_maps);
 cudaError_t init_device_tables();
 cudaError_t init_match_kernels();
 void build_resize_taps(int ssize, int dsize, uint32_t* taps);
