@@ -6,10 +6,11 @@
 // (orb_extractor.cpp:19-26), in canonical (octave, y, x) order.
 //
 // One warp owns a group of G consecutive keypoints of one frame (G = 16, or 4 for tiny batches).
-// Both per-keypoint windows are brought into shared memory by the TMA unit, one instruction each
-// (cp.async.bulk.tensor.3d over the per-level plane tensor maps, box start rounded down to 16 B),
-// double buffered per warp with an mbarrier per buffer, so the window of keypoint i+1 is in flight
-// while keypoint i is processed and no lane computes a global address:
+// Both per-keypoint windows are staged in shared memory: every lane copies 16-byte chunks of the
+// window rows (row starts rounded down to 16 B) with cp.async, one commit group per keypoint,
+// 4 (orientation) / 3 (descriptor) windows deep per warp, so the windows of the next keypoints are
+// in flight while keypoint i is processed.  (TMA boxes were measured first: at 31-37 rows of 48-64 B
+// per box the TMA unit's per-row rate, ~5 cycles/row/SM, became the limiter.)
 //   orientation  31 rows x 48 B of the un-blurred level.  lane = patch row v; nine LDS words, a
 //                funnel shift to the patch origin, then IDP.4A does the work:
 //                m10 += dp4a(pixels, u-weights), rowsum += dp4a(pixels, mask), m01 += v*rowsum;
@@ -22,7 +23,6 @@
 //                rounded coordinates feed the shared-memory address IMAD directly); the 16 byte
 //                gathers per lane are LDS.U8 instead of scattered global loads
 // Float rules are load-bearing: every op is an explicit *_rn intrinsic so nvcc cannot contract.
-#include <cuda.h>
 #include <float.h>
 
 #include "vxorb_internal.h"
@@ -82,37 +82,18 @@ namespace {
 constexpr int kPaW = 48, kPaH = 31, kPaBytes = kPaW * kPaH, kPaStride = 1536;  // orientation window (un-blurred)
 constexpr int kPbW = 64, kPbH = 37, kPbBytes = kPbW * kPbH, kPbStride = 2432;  // descriptor window (blurred)
 constexpr int kDescWarps = 4;
-
-struct DescMaps {
-    CUtensorMap pyr[kMaxLevels];
-    CUtensorMap blur[kMaxLevels];
-};
+constexpr int kDepthA = 4, kDepthB = 3;            // windows in flight per warp
+constexpr int kWinBytes = kDepthB * kPbStride;     // per-warp window memory, shared by both phases
+static_assert(kDepthA * kPaStride <= kWinBytes, "orientation windows must fit the per-warp region");
 
 __device__ __forceinline__ uint32_t s_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void bar_init(uint32_t bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
-__device__ __forceinline__ void bar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "DW_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DD_%=;\n"
-        "bra DW_%=;\n"
-        "DD_%=:\n"
-        "}\n" ::"r"(bar),
-        "r"(parity)
-        : "memory");
-}
-// one lane: arm the barrier with the box size and start the box load
-__device__ __forceinline__ void box_load(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar,
-                                         uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
-        "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
-        : "memory");
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
     uint32_t v;
@@ -128,22 +109,14 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
 }  // namespace
 
 __global__ void __launch_bounds__(128)
-describe_kernel(const LevelTab lt, const __grid_constant__ DescMaps maps, const uint32_t* __restrict__ fin_key, const float* __restrict__ fin_resp,
+describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
+                const uint32_t* __restrict__ fin_key, const float* __restrict__ fin_resp,
                 const int* __restrict__ fin_n, int kp_cap, int group, vxorb_keypoint* __restrict__ kp_out,
                 uint8_t* __restrict__ desc_out, float* __restrict__ xy_out, int* __restrict__ kp_n,
                 int* __restrict__ kp_total, int* __restrict__ status) {
-    __shared__ __align__(128) uint8_t win_a[kDescWarps][2][kPaStride];
-    __shared__ __align__(128) uint8_t win_b[kDescWarps][2][kPbStride];
-    __shared__ __align__(8) unsigned long long bars[kDescWarps][4];  // [0,1]: orientation buffers, [2,3]: descriptor buffers
+    __shared__ __align__(128) uint8_t win[kDescWarps][kWinBytes];
     const int f = blockIdx.y;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (lane == 0) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) bar_init(s_addr(&bars[wid][i]), 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    __syncwarp();
     const int g0 = (blockIdx.x * 4 + (threadIdx.x >> 5)) * group;  // first keypoint of this warp's group
 
     // ---- setup: locate keypoint g0 + lane from the per-level counts -----------------------------
@@ -206,36 +179,54 @@ describe_kernel(const LevelTab lt, const __grid_constant__ DescMaps maps, const 
         wm[j] = m;
     }
 
-    const uint32_t bar0 = s_addr(&bars[wid][0]);
-    const uint32_t wa0 = s_addr(&win_a[wid][0][0]), wb0 = s_addr(&win_b[wid][0][0]);
-    // window loads of keypoint i (lane 0 only): box start = 16 B boundary at or below the first byte
+    const uint32_t win0 = s_addr(&win[wid][0]);
+    // Window loads of keypoint i: every lane copies its 16-byte chunks (3 per orientation row, 4 per
+    // descriptor row; rows start at the 16 B boundary at or below the window's first byte) with
+    // cp.async, one commit group per keypoint.  Orientation windows cycle through kDepthA slots,
+    // descriptor windows through kDepthB slots of the same per-warp region (the descriptor phase
+    // starts after the last orientation window has been read).
     auto load_a = [&](int i) {
         const int kx = __shfl_sync(0xffffffffu, x, i), ky = __shfl_sync(0xffffffffu, y, i);
         const int kl = __shfl_sync(0xffffffffu, level, i);
-        if (lane == 0)
-            box_load(wa0 + (i & 1) * kPaStride, &maps.pyr[kl], (kx - 15 + kApronX) & ~15, ky - 15 + kApronY, f,
-                     bar0 + (i & 1) * 8, kPaBytes);
+        const int pitch = lt.pitch[kl];
+        const uint8_t* g = pyr + lt.off[kl] + (size_t)f * lt.fstride[kl] + (ptrdiff_t)(ky - 15) * pitch + ((kx - 15) & ~15);
+        const uint32_t d = win0 + (i % kDepthA) * kPaStride;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int idx = lane + 32 * k;  // chunk index: row = idx / 3, 16-byte column = idx % 3
+            const int row = idx / 3, ch = idx - row * 3;
+            if (idx < kPaH * 3) cp_async16(d + idx * 16, g + (ptrdiff_t)row * pitch + ch * 16);
+        }
     };
     auto load_b = [&](int i) {
         const int kx = __shfl_sync(0xffffffffu, x, i), ky = __shfl_sync(0xffffffffu, y, i);
         const int kl = __shfl_sync(0xffffffffu, level, i);
-        if (lane == 0)
-            box_load(wb0 + (i & 1) * kPbStride, &maps.blur[kl], (kx - 18 + kApronX) & ~15, ky - 18 + kApronY, f,
-                     bar0 + 16 + (i & 1) * 8, kPbBytes);
+        const int pitch = lt.pitch[kl];
+        const uint8_t* g = blur + lt.off[kl] + (size_t)f * lt.fstride[kl] + (ptrdiff_t)(ky - 18) * pitch + ((kx - 18) & ~15);
+        const uint32_t d = win0 + (i % kDepthB) * kPbStride;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const int idx = lane + 32 * k;  // row = idx / 4, 16-byte column = idx % 4
+            if (idx < kPbH * 4) cp_async16(d + idx * 16, g + (ptrdiff_t)(idx >> 2) * pitch + (idx & 3) * 16);
+        }
     };
 
     // ---- orientation moments, one keypoint at a time, lane = patch row --------------------------
-    load_a(0);
+#pragma unroll
+    for (int i = 0; i < kDepthA; ++i) {
+        if (i < n_here) load_a(i);
+        cp_async_commit();
+    }
     int my_m10 = 0, my_m01 = 0;
     const uint32_t my_row = (uint32_t)min(lane, kPaH - 1) * kPaW;
     for (int i = 0; i < n_here; ++i) {
-        if (i + 1 < n_here) load_a(i + 1);  // the other buffer was drained by the __syncwarp ending keypoint i-1
-        else load_b(0);                     // last orientation window: start the first descriptor window
+        const int slot = i % kDepthA;
         const int kx = __shfl_sync(0xffffffffu, x, i);
-        const uint32_t off = (uint32_t)(kx - 15 + kApronX) & 15u;
+        const uint32_t off = (uint32_t)(kx - 15) & 15u;
         const uint32_t sh = (off & 3u) * 8u;
-        const uint32_t rw = wa0 + (i & 1) * kPaStride + my_row + (off & ~3u);
-        bar_wait(bar0 + (i & 1) * 8, (uint32_t)(i >> 1) & 1u);
+        const uint32_t rw = win0 + slot * kPaStride + my_row + (off & ~3u);
+        cp_async_wait<kDepthA - 1>();  // this lane's chunks of keypoint i have landed ...
+        __syncwarp();                  // ... and so have everyone else's
         uint32_t wd[9];
 #pragma unroll
         for (int j = 0; j < 9; ++j) wd[j] = lds_u32(rw + 4 * j);
@@ -254,7 +245,15 @@ describe_kernel(const LevelTab lt, const __grid_constant__ DescMaps maps, const 
             my_m10 = m10;
             my_m01 = m01;
         }
-        __syncwarp();  // every lane is done with this window before lane 0 refills its buffer
+        __syncwarp();  // every lane is done with this slot before it is refilled
+        if (i + kDepthA < n_here) load_a(i + kDepthA);
+        cp_async_commit();  // one group per iteration (possibly empty) keeps the wait distance fixed
+    }
+    // the region is free: start the first descriptor windows, the angle math below hides their latency
+#pragma unroll
+    for (int i = 0; i < kDepthB; ++i) {
+        if (i < n_here) load_b(i);
+        cp_async_commit();
     }
 
     // ---- angle, cos/sin and the keypoint record: lane i for keypoint i --------------------------
@@ -278,13 +277,14 @@ describe_kernel(const LevelTab lt, const __grid_constant__ DescMaps maps, const 
     // ---- rotated BRIEF, one keypoint at a time, lane = descriptor byte ---------------------------
     const float magic = 12582912.0f;  // 1.5 * 2^23: low mantissa bits of (t + magic) = round-half-even(t)
     for (int i = 0; i < n_here; ++i) {
-        if (i + 1 < n_here) load_b(i + 1);
+        const int slot = i % kDepthB;
         const int kx = __shfl_sync(0xffffffffu, x, i);
         const float c = __shfl_sync(0xffffffffu, ca, i), s = __shfl_sync(0xffffffffu, sa, i);
-        const uint32_t off = (uint32_t)(kx - 18 + kApronX) & 15u;
+        const uint32_t off = (uint32_t)(kx - 18) & 15u;
         // address = window centre + iy*64 + ix with iy = bits(ty) - bits(magic), ix likewise (mod 2^32)
-        const uint32_t bc = wb0 + (i & 1) * kPbStride + 18u * kPbW + 18u + off - 0x4B400000u * (uint32_t)kPbW - 0x4B400000u;
-        bar_wait(bar0 + 16 + (i & 1) * 8, (uint32_t)(i >> 1) & 1u);
+        const uint32_t bc = win0 + slot * kPbStride + 18u * kPbW + 18u + off - 0x4B400000u * (uint32_t)kPbW - 0x4B400000u;
+        cp_async_wait<kDepthB - 1>();
+        __syncwarp();
         unsigned byte = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -300,7 +300,9 @@ describe_kernel(const LevelTab lt, const __grid_constant__ DescMaps maps, const 
             byte |= (t[0] < t[1] ? 1u : 0u) << k;
         }
         desc_out[((size_t)f * kp_cap + g0 + i) * 32 + lane] = (uint8_t)byte;
-        __syncwarp();  // every lane is done with this window before lane 0 refills its buffer
+        __syncwarp();  // every lane is done with this slot before it is refilled
+        if (i + kDepthB < n_here) load_b(i + kDepthB);
+        cp_async_commit();
     }
 }
 
@@ -320,12 +322,8 @@ int launch_describe(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, cud
     // frame still spreads over ~80 CTAs
     const int group = lt.batch >= 8 ? 16 : 4;
     const int warps = (kp_cap + group - 1) / group;
-    DescMaps maps;
-    if (!build_plane_maps(lt, db.pyr, kPaW, kPaH, false, maps.pyr) ||
-        !build_plane_maps(lt, db.blur, kPbW, kPbH, false, maps.blur))
-        return -1;
     dim3 grid((warps + kDescWarps - 1) / kDescWarps, lt.batch);
-    describe_kernel<<<grid, 32 * kDescWarps, 0, s>>>(lt, maps, db.fin_key, db.fin_resp, db.fin_n, kp_cap, group, db.kp,
+    describe_kernel<<<grid, 32 * kDescWarps, 0, s>>>(lt, db.pyr, db.blur, db.fin_key, db.fin_resp, db.fin_n, kp_cap, group, db.kp,
                                                      db.desc, db.xy, db.kp_n, db.kp_total, db.status);
     return 1;
 }
