@@ -9,23 +9,27 @@
 //
 // Persistent CTAs (8 warps) walk over tiles whose score region is 128 x 40 px (emission region: the
 // inner 124 x 38); the level pixels a tile needs sit in shared memory as 32-bit words and the score
-// map never leaves shared memory.
+// map never leaves shared memory.  Warp w owns score rows w, w + 8, ... of the tile from the first
+// test to the emission, so a tile costs ONE CTA barrier (between scoring and NMS, which reads the
+// neighbouring rows other warps scored); score maps and tile buffers are double buffered.
 //   load    one TMA box per tile (cp.async.bulk.tensor.3d over a per-level {pitch, rows, frame}
-//           tensor map: 46 rows x 160 B = 3-row ring halo, halo words left and right, 16 B aligned start), issued
-//           by thread 0 for the NEXT tile into the other buffer while the CTA works on this one and
-//           completed through an mbarrier; pixels outside the plane are zero-filled by the TMA unit
-//           and are never part of a valid ring
+//           tensor map: 46 rows x 160 B = 3-row ring halo, halo words left and right, 16 B aligned start),
+//           issued two tiles ahead right after the barrier that frees the buffer and completed
+//           through an mbarrier; pixels outside the plane are zero-filled by the TMA unit and are
+//           never part of a valid ring
 //   stage 1 every lane tests FOUR horizontally adjacent pixels per step with byte SIMD: a corner
 //           needs, for each opposite ring pair {k, k+8}, one pixel with |p - v| > t, so
 //           (F0|F8) & (F4|F12) with F = per-byte |p - v| > t (VABSDIFF4 + carry trick) is a
 //           necessary condition; 16-byte pixel rows -> 5 LDS, 2 PRMT, 4 VABSDIFF4, ~16 logic ops
-//           per 4 px.  Survivor bits of a warp's 5 rows collect in one register per lane and are
-//           compacted to a shared queue with one warp prefix sum.
-//   stage 2 one thread scores TWO queued pixels at once in s16x2 lanes: D_k = p_k - v, sliding
-//           min-of-9 / max-of-9 over the ring with 3-input VIMNMX3 (40 + 40 ops), score =
-//           max(max_arcs min D, -min_arcs max D) - 1, written to the score map iff >= t.
-//   stage 3 strict 3x3 NMS of queued pixels on the score map, survivors staged in shared memory
-//   emit    one global atomicAdd per CTA, coalesced write of packed corners (score<<24|y<<12|x)
+//           per 4 px.  Survivor bits of the warp's 5 rows collect in one register per lane and are
+//           compacted into the warp's own list with one warp prefix sum (no atomics).
+//   stage 2 one lane scores one listed pixel, both polarities at once in s16x2 halves:
+//           D_k = (p_k - v + 256) | (v - p_k + 256) << 16 is ONE IMAD per ring pixel, min over 9
+//           contiguous ring pixels = two rounds of 3-input VIMNMX3 (32 ops), max over the 16 arcs
+//           (8 ops); score = max(lo, hi) - 257, written to the score map iff >= t.  Corners are
+//           re-compacted to the front of the same list by ballot.
+//   stage 3 strict 3x3 NMS of the warp's corners on the score map, survivors compacted by ballot,
+//   emit    one global atomicAdd per warp and tile, packed corners (score<<24|y<<12|x) written directly
 // Roofline: HBM, algorithmic bytes = one read of every level pixel (950 532 B per 640x480 frame);
 // the kernel is integer-issue bound.
 #include <cuda.h>  // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
@@ -42,8 +46,8 @@ constexpr int TROWS = FSR + 6, TWORDS = FW / 4 + 8;  // tile rows, 32-bit words 
 constexpr uint32_t kTileBytes = TROWS * TWORDS * 4;
 constexpr int TPITCH = TWORDS * 4;
 constexpr int RPW = FSR / 8;                          // score rows per warp
-constexpr int QCAP = FW * FSR;
-constexpr int OCAP = (kFastEmitW / 2 + 1) * (kFastEmitH / 2 + 1);
+constexpr int kFastCtasPerSm = 6;                      // 35.4 KB of shared memory and 32 registers per thread
+constexpr int WQCAP = RPW * FW;                       // pixels one warp tests per tile
 
 // ring offsets (dx, dy), k = 0..15, as byte offsets into the tile
 __device__ __forceinline__ constexpr int ring_off(int k) {
@@ -96,24 +100,24 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, i
 }  // namespace
 
 template <bool HI>
-__global__ void __launch_bounds__(256, 5)
+__global__ void __launch_bounds__(256, kFastCtasPerSm)
 fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* __restrict__ cand,
             int* __restrict__ cand_n, int threshold, int border, int tiles_per_frame, int total_tiles) {
     struct __align__(128) TileBuf {
         uint32_t w[TROWS][TWORDS];  // TMA destinations must be 128 B aligned: the struct alignment pads buffer 1
     };
     __shared__ TileBuf tiles[2];
-    __shared__ __align__(16) uint8_t score[FSR][FW];
-    __shared__ uint32_t queue[QCAP / 2];  // u16 entries: row * 128 + col in the score region
-    __shared__ uint32_t outq[OCAP];
+    __shared__ __align__(16) uint8_t score[2][FSR][FW];  // tile t uses map t & 1; a warp writes only its own rows
+    __shared__ uint16_t wq[8][WQCAP];       // per-warp list: stage-1 survivors, then corners, then NMS survivors
     __shared__ __align__(8) unsigned long long mbar[2];
-    __shared__ int4 info[2];              // tile descriptor: level, X, Y, frame
-    __shared__ int qn, on, obase;
+    __shared__ int4 info[4];                // tile descriptors (level, X, Y, frame), ring over 4 tiles
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int grid = (int)gridDim.x;
+    const uint32_t lt_mask = (1u << lane) - 1u;
 
-    // thread 0: decode tile t, publish its descriptor and start its TMA load into buffer b
-    auto issue = [&](int t, int b) {
+    // one thread: decode tile t, publish its descriptor and start its TMA load into buffer b
+    auto issue = [&](int t, int b, int slot) {
         const int f = t / tiles_per_frame;
         int tl = t - f * tiles_per_frame;
         int l = 0;
@@ -123,7 +127,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
         // score region origin: X is a multiple of 4 so tile words are aligned words of the plane
         const int X = ((border - 1) & ~3) + tx * kFastEmitW;
         const int Y = (border - 1) + ty * kFastEmitH;
-        info[b] = make_int4(l, X, Y, f);
+        info[slot] = make_int4(l, X, Y, f);
         mbar_expect_tx(&mbar[b], kTileBytes);
         // tensor map coordinates count from the plane allocation: kApronX bytes / kApronY rows before
         // pixel (0, 0).  The box starts at the 16 B boundary at or below the tile's first byte (X - 4).
@@ -135,159 +139,172 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
         mbar_init(&mbar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        if ((int)blockIdx.x < total_tiles) issue(blockIdx.x, 0);
+        if ((int)blockIdx.x < total_tiles) issue(blockIdx.x, 0, 0);
+        if ((int)blockIdx.x + grid < total_tiles) issue(blockIdx.x + grid, 1, 1);
     }
-
-    int it = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-    const int buf = it & 1;
-    uint32_t (*tile)[TWORDS] = tiles[buf].w;
-    if (tid == 0) {
-        const int tn = t + (int)gridDim.x;
-        if (tn < total_tiles) issue(tn, buf ^ 1);  // buffer buf^1 was released by the barrier ending the previous tile
-        qn = 0;
-        on = 0;
-    }
-    for (int i = tid; i < FSR * FW / 16; i += 256) reinterpret_cast<uint4*>(&score[0][0])[i] = make_uint4(0, 0, 0, 0);
     __syncthreads();
-    const int4 ti = info[buf];
-    const int l = ti.x, X = ti.y, Y = ti.z, f = ti.w;
-    const int w = lt.w[l], h = lt.h[l];
-    const int wo = ((X - 4 + kApronX) & 15) >> 2;  // words of slack before the tile's first word in a buffer row
-    mbar_wait(&mbar[buf], (uint32_t)(it >> 1) & 1u);
 
-    // score domain (global coordinates, inclusive)
-    const int sx_min = max(3, border - 1), sx_max = min(w - 4, w - border);
-    const int sy_min = max(3, border - 1), sy_max = min(h - 4, h - border);
+    uint16_t* q16 = wq[warp];
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += grid, ++it) {
+        const int buf = it & 1;
+        uint32_t (*tile)[TWORDS] = tiles[buf].w;
+        uint8_t* sc = &score[buf][0][0];
+        const int4 ti = info[it & 3];
+        const int l = ti.x, X = ti.y, Y = ti.z, f = ti.w;
+        const int w = lt.w[l], h = lt.h[l];
+        const int wo = ((X - 4 + kApronX) & 15) >> 2;  // words of slack before the tile's first word in a buffer row
 
-    // ---- stage 1: 4-pixel-wide necessary-condition test ---------------------------------------
-    {
+        // this warp's rows of the score map (last read by the NMS of tile t - 2, two barriers ago)
+#pragma unroll
+        for (int i = 0; i < RPW; ++i) reinterpret_cast<uint32_t*>(sc + (i * 8 + warp) * FW)[lane] = 0u;
+
+        // score domain (global coordinates, inclusive)
+        const int sx_min = max(3, border - 1), sx_max = min(w - 4, w - border);
+        const int sy_min = max(3, border - 1), sy_max = min(h - 4, h - border);
         uint32_t colmask = 0;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int gx = X + 4 * lane + j;
             if (gx >= sx_min && gx <= sx_max) colmask |= 0x80u << (8 * j);
         }
-        const uint32_t cadd = (uint32_t)(HI ? 255 - threshold : 127 - threshold) * 0x01010101u;
-        uint32_t acc = 0;
-#pragma unroll
-        for (int i = 0; i < RPW; ++i) {
-            const int r = i * 8 + warp;  // rows interleaved over warps: a corner cluster spreads over lanes of several warps
-            const int gy = Y + r;
-            uint32_t q = 0;
-            if (gy >= sy_min && gy <= sy_max) {
-                const uint32_t* row = &tile[r + 3][lane + wo];
-                const uint32_t wl = row[0], v = row[1], wr = row[2];
-                const uint32_t up = tile[r][lane + 1 + wo], dn = tile[r + 6][lane + 1 + wo];
-                const uint32_t lf = __byte_perm(wl, v, 0x4321u), rt = __byte_perm(v, wr, 0x6543u);
-                const uint32_t f0 = gt_flags<HI>(__vabsdiffu4(dn, v), cadd);
-                const uint32_t f8 = gt_flags<HI>(__vabsdiffu4(up, v), cadd);
-                const uint32_t f4 = gt_flags<HI>(__vabsdiffu4(rt, v), cadd);
-                const uint32_t f12 = gt_flags<HI>(__vabsdiffu4(lf, v), cadd);
-                q = (f0 | f8) & (f4 | f12) & colmask;
-            }
-            // bits 7/15/23/31 -> bits 28..31 (distinct partial products, no carries)
-            acc = (acc >> 4) | ((q * 0x00204081u) & 0xF0000000u);
-        }
-        acc >>= 32 - 4 * RPW;  // row i of this warp now sits in bits 4i .. 4i+3
-        // compaction: one inclusive prefix sum per warp, one shared atomic per warp
-        const int cnt = __popc(acc);
-        int incl = cnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int n = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += n;
-        }
-        int base = 0;
-        if (lane == 31 && incl > 0) base = atomicAdd(&qn, incl);
-        base = __shfl_sync(0xffffffffu, base, 31);
-        int pos = base + incl - cnt;
-        uint16_t* q16 = reinterpret_cast<uint16_t*>(queue);
-        const int rowbase = warp * FW + 4 * lane;
-        while (acc) {
-            const int b = __ffs(acc) - 1;
-            acc &= acc - 1;
-            q16[pos++] = (uint16_t)(rowbase + (b >> 2) * (8 * FW) + (b & 3));
-        }
-    }
-    __syncthreads();
-    const int nq = qn;
+        mbar_wait(&mbar[buf], (uint32_t)(it >> 1) & 1u);
 
-    // ---- stage 2: cornerScore of two queued pixels per thread ---------------------------------
-    {
-        const uint8_t* t8 = reinterpret_cast<const uint8_t*>(&tile[0][0]) + 3 * TPITCH + 4 + 4 * wo;
-        const int pairs = (nq + 1) >> 1;
-        for (int pi = tid; pi < pairs; pi += 256) {
-            const uint32_t u = queue[pi];
-            const int ia = (int)(u & 0xffffu);
-            const int ib = (2 * pi + 1 < nq) ? (int)(u >> 16) : ia;
-            const uint8_t* ta = t8 + (ia >> 7) * TPITCH + (ia & 127);
-            const uint8_t* tb = t8 + (ib >> 7) * TPITCH + (ib & 127);
-            const uint32_t va = ta[0], vb = tb[0];
-            const uint32_t nv = ((0u - va) & 0xffffu) | ((0u - vb) << 16);
-            uint32_t d[16];
+        // ---- stage 1: 4-pixel-wide necessary-condition test -----------------------------------
+        int nq;
+        {
+            const uint32_t cadd = (uint32_t)(HI ? 255 - threshold : 127 - threshold) * 0x01010101u;
+            uint32_t acc = 0;
 #pragma unroll
-            for (int k = 0; k < 16; ++k)
-                d[k] = __vadd2((uint32_t)ta[ring_off(k)] | ((uint32_t)tb[ring_off(k)] << 16), nv);  // p_k - v
-            uint32_t lo3[16], hi3[16];
-#pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                lo3[k] = __vimin3_s16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-                hi3[k] = __vimax3_s16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+            for (int i = 0; i < RPW; ++i) {
+                const int r = i * 8 + warp;  // rows interleaved over warps: a corner cluster spreads over several warps
+                const int gy = Y + r;
+                uint32_t q = 0;
+                if (gy >= sy_min && gy <= sy_max) {
+                    const uint32_t* row = &tile[r + 3][lane + wo];
+                    const uint32_t wl = row[0], v = row[1], wr = row[2];
+                    const uint32_t up = tile[r][lane + 1 + wo], dn = tile[r + 6][lane + 1 + wo];
+                    const uint32_t lf = __byte_perm(wl, v, 0x4321u), rt = __byte_perm(v, wr, 0x6543u);
+                    const uint32_t f0 = gt_flags<HI>(__vabsdiffu4(dn, v), cadd);
+                    const uint32_t f8 = gt_flags<HI>(__vabsdiffu4(up, v), cadd);
+                    const uint32_t f4 = gt_flags<HI>(__vabsdiffu4(rt, v), cadd);
+                    const uint32_t f12 = gt_flags<HI>(__vabsdiffu4(lf, v), cadd);
+                    q = (f0 | f8) & (f4 | f12) & colmask;
+                }
+                // bits 7/15/23/31 -> bits 28..31 (distinct partial products, no carries)
+                acc = (acc >> 4) | ((q * 0x00204081u) & 0xF0000000u);
             }
-            uint32_t lo9[16], hi9[16];
+            acc >>= 32 - 4 * RPW;  // row i of this warp now sits in bits 4i .. 4i+3
+            // compaction into the warp's own list: one inclusive prefix sum, no atomics
+            const int cnt = __popc(acc);
+            int incl = cnt;
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                lo9[k] = __vimin3_s16x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);
-                hi9[k] = __vimax3_s16x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
+            for (int d = 1; d < 32; d <<= 1) {
+                const int n = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += n;
             }
-            uint32_t bb = lo9[15], bd = hi9[15];
-#pragma unroll
-            for (int k = 0; k < 15; k += 3) {
-                bb = __vimax3_s16x2(bb, lo9[k], lo9[k + 1]);
-                bb = __vmaxs2(bb, lo9[k + 2]);
-                bd = __vimin3_s16x2(bd, hi9[k], hi9[k + 1]);
-                bd = __vmins2(bd, hi9[k + 2]);
+            nq = __shfl_sync(0xffffffffu, incl, 31);
+            int pos = incl - cnt;
+            const int rowbase = warp * FW + 4 * lane;
+            while (acc) {
+                const int b = __ffs(acc) - 1;
+                acc &= acc - 1;
+                q16[pos++] = (uint16_t)(rowbase + (b >> 2) * (8 * FW) + (b & 3));
             }
-            // bright score = max_arcs min(p - v); dark score = max_arcs min(v - p) = -min_arcs max(p - v)
-            const int sa = max((int)(short)(bb & 0xffffu), -(int)(short)(bd & 0xffffu)) - 1;
-            const int sb = max((int)bb >> 16, -((int)bd >> 16)) - 1;
-            if (sa >= threshold) (&score[0][0])[ia] = (uint8_t)sa;
-            if (sb >= threshold) (&score[0][0])[ib] = (uint8_t)sb;
         }
-    }
-    __syncthreads();
+        __syncwarp();
 
-    // ---- stage 3: strict 3x3 non-max suppression over the emission region ----------------------
-    {
-        const uint16_t* q16 = reinterpret_cast<const uint16_t*>(queue);
-        const int ex_max = w - border, ey_max = h - border;  // exclusive
-        for (int e = tid; e < nq; e += 256) {
-            const int idx = q16[e];
-            const int r = idx >> 7, c = idx & 127;
-            const int s = (&score[0][0])[idx];
-            if (s == 0 || r < 1 || r > kFastEmitH || c < 1 || c > kFastEmitW) continue;
-            const int gx = X + c, gy = Y + r;
-            if (gx < border || gy < border || gx >= ex_max || gy >= ey_max) continue;
-            const uint8_t* p = &score[r][c];
-            if (s > p[-FW - 1] && s > p[-FW] && s > p[-FW + 1] && s > p[-1] && s > p[1] && s > p[FW - 1] &&
-                s > p[FW] && s > p[FW + 1]) {
-                const int o = atomicAdd(&on, 1);
-                outq[o] = ((uint32_t)s << 24) | ((uint32_t)gy << 12) | (uint32_t)gx;
+        // ---- stage 2: cornerScore, one listed pixel per lane ----------------------------------
+        // Both polarities ride in one s16x2 register: lo = p_k - v + 256, hi = v - p_k + 256 (one IMAD
+        // per ring pixel: p_k * (1 - 2^16) + C; both fields stay in 1..511, so no carry crosses).
+        // min over 9 contiguous ring pixels by two rounds of 3-input minima, max over the 16 arcs:
+        // lo -> 256 + max_arcs min(p - v) (bright), hi -> 256 + max_arcs min(v - p) (dark).
+        int nc = 0;
+        {
+            const uint8_t* t8 = reinterpret_cast<const uint8_t*>(&tile[0][0]) + 3 * TPITCH + 4 + 4 * wo;
+            for (int e0 = 0; e0 < nq; e0 += 32) {
+                const int e = e0 + lane;
+                bool corner = false;
+                int idx = 0;
+                if (e < nq) {
+                    idx = q16[e];
+                    const uint8_t* tp = t8 + (idx >> 7) * TPITCH + (idx & 127);
+                    const uint32_t v = tp[0];
+                    const uint32_t c0 = v * 0xFFFFu + 0x01000100u;  // (256 - v) | (256 + v) << 16
+                    uint32_t d[16];
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) d[k] = (uint32_t)tp[ring_off(k)] * 0xFFFF0001u + c0;
+                    uint32_t m3[16];
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) m3[k] = __vimin3_s16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+                    uint32_t m9[16];
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) m9[k] = __vimin3_s16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+                    uint32_t best = m9[15];
+#pragma unroll
+                    for (int k = 0; k < 15; k += 3) {
+                        best = __vimax3_s16x2(best, m9[k], m9[k + 1]);
+                        best = __vmaxs2(best, m9[k + 2]);
+                    }
+                    const int s = max((int)(best & 0xffffu), (int)(best >> 16)) - 257;
+                    if (s >= threshold) {
+                        sc[idx] = (uint8_t)s;
+                        corner = true;
+                    }
+                }
+                __syncwarp();  // every lane has read its entry before the front of the list is overwritten
+                const uint32_t m = __ballot_sync(0xffffffffu, corner);
+                if (corner) q16[nc + __popc(m & lt_mask)] = (uint16_t)idx;
+                nc += __popc(m);
             }
         }
-    }
-    __syncthreads();
-    const int no = on;
-    if (no > 0) {  // uniform over the CTA
-        const int cap = lt.cand_cap[l];
-        if (tid == 0) obase = atomicAdd(cand_n + l * lt.batch + f, no);
-        __syncthreads();
-        uint32_t* out = cand + lt.cand_off[l] + (size_t)f * cap;
-        for (int i = tid; i < no; i += 256)
-            if (obase + i < cap) out[obase + i] = outq[i];
-    }
-    __syncthreads();  // tile buffer, score map and queues are free for the next tile
+        __syncthreads();  // the one CTA barrier per tile: all rows of the score map are final, tile buffer is free
+        if (tid == ((it & 7) << 5)) {
+            const int tn = t + 2 * grid;
+            if (tn < total_tiles) issue(tn, buf, (it + 2) & 3);
+        }
+
+        // ---- stage 3: strict 3x3 non-max suppression of this warp's corners, emission ----------
+        {
+            const int ex_max = w - border, ey_max = h - border;  // exclusive
+            int nk = 0;
+            for (int e0 = 0; e0 < nc; e0 += 32) {
+                const int e = e0 + lane;
+                bool keep = false;
+                int idx = 0;
+                if (e < nc) {
+                    idx = q16[e];
+                    const int r = idx >> 7, c = idx & 127;
+                    const int gx = X + c, gy = Y + r;
+                    if (r >= 1 && r <= kFastEmitH && c >= 1 && c <= kFastEmitW && gx >= border && gy >= border &&
+                        gx < ex_max && gy < ey_max) {
+                        const uint8_t* p = sc + idx;
+                        const int s = p[0];
+                        keep = s > p[-FW - 1] && s > p[-FW] && s > p[-FW + 1] && s > p[-1] && s > p[1] &&
+                               s > p[FW - 1] && s > p[FW] && s > p[FW + 1];
+                    }
+                }
+                __syncwarp();
+                const uint32_t m = __ballot_sync(0xffffffffu, keep);
+                if (keep) q16[nk + __popc(m & lt_mask)] = (uint16_t)idx;
+                nk += __popc(m);
+            }
+            if (nk > 0) {  // warp-uniform
+                __syncwarp();
+                const int cap = lt.cand_cap[l];
+                int obase = 0;
+                if (lane == 0) obase = atomicAdd(cand_n + l * lt.batch + f, nk);
+                obase = __shfl_sync(0xffffffffu, obase, 0);
+                uint32_t* out = cand + lt.cand_off[l] + (size_t)f * cap;
+                for (int e = lane; e < nk; e += 32) {
+                    const int idx = q16[e];
+                    const uint32_t s = sc[idx];
+                    if (obase + e < cap)
+                        out[obase + e] = (s << 24) | ((uint32_t)(Y + (idx >> 7)) << 12) | (uint32_t)(X + (idx & 127));
+                }
+                __syncwarp();  // the list is reused by the next tile
+            }
+        }
     }
 }
 
@@ -332,7 +349,7 @@ int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int 
     FastMaps maps;
     if (!build_plane_maps(lt, db.pyr, TWORDS * 4, TROWS, true, maps.m)) return -1;
     const int total = tiles * lt.batch;
-    const int grid = total < 148 * 5 ? total : 148 * 5;  // persistent: 5 CTAs of 8 warps per SM
+    const int grid = total < 148 * kFastCtasPerSm ? total : 148 * kFastCtasPerSm;  // persistent CTAs of 8 warps
     if (threshold >= 128)
         fast_kernel<true><<<grid, 256, 0, s>>>(lt, maps, db.cand, db.cand_n, threshold, border, tiles, total);
     else
