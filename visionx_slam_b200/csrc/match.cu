@@ -116,19 +116,19 @@ knn2_kernel(const MatchArgs a) {
 // that bins the train points, so no in-window row can be missed.
 constexpr int kCellGrid = 32;
 constexpr int kCells = kCellGrid * kCellGrid;
-constexpr int kWinThreads = 256;
+constexpr int kWinThreads = 1024;
 
 __device__ __forceinline__ int cell_of(float v, float org, float inv) {
     const float c = floorf(__fmul_rn(__fsub_rn(v, org), inv));
     return (int)fminf(fmaxf(c, 0.0f), (float)(kCellGrid - 1));
 }
 
-static size_t window_smem_bytes(int max_t) {
-    return (size_t)max_t * (32 + 8 + 4) + (size_t)(2 * kCells + 1) * 4 + 64;
+static size_t window_smem_bytes(int max_t, int max_q) {
+    return (size_t)max_t * (32 + 8 + 4) + (size_t)(2 * kCells + 1) * 4 + 64 + (size_t)((max_q + 1) & ~1) * 2;
 }
 
 __global__ void __launch_bounds__(kWinThreads)
-knn2_window_kernel(const MatchArgs a, int max_t) {
+knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
     extern __shared__ __align__(16) uint8_t wsm[];
     uint4* tdesc = reinterpret_cast<uint4*>(wsm);                                  // [max_t][2]
     float2* txy = reinterpret_cast<float2*>(wsm + (size_t)max_t * 32);             // [max_t]
@@ -136,11 +136,12 @@ knn2_window_kernel(const MatchArgs a, int max_t) {
     int* cell_start = tidx + max_t;                                                // [kCells + 1]
     int* cursor = cell_start + kCells + 1;                                         // [kCells]
     float* bounds = reinterpret_cast<float*>(cursor + kCells);                     // minx, miny, maxx, maxy
+    uint16_t* qorder = reinterpret_cast<uint16_t*>(bounds + 16);                   // [max_q] query rows in cell order
     __shared__ int warp_tot[kWinThreads / 32];
 
-    const int pair = blockIdx.y;
-    const int nq = a.q_n[pair], nt = min(a.t_n[pair], max_t);
-    if ((int)blockIdx.x * kWinThreads >= nq) return;  // whole CTA idle
+    const int pair = blockIdx.x;
+    const int nq = min(a.q_n[pair], max_q), nt = min(a.t_n[pair], max_t);
+    if (nq <= 0) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint8_t* qbase = a.q_desc + (size_t)pair * a.q_pair_stride * 32;
     const uint8_t* tbase = a.t_desc + (size_t)pair * a.t_pair_stride * 32;
@@ -189,16 +190,12 @@ knn2_window_kernel(const MatchArgs a, int max_t) {
         atomicAdd(&cell_start[cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx)], 1);
     }
     __syncthreads();
-    {
-        // exclusive scan of kCells counts: 4 per thread, warp scan, then warp totals
-        constexpr int per = kCells / kWinThreads;
-        int c[per], sum = 0;
-#pragma unroll
-        for (int k = 0; k < per; ++k) {
-            c[k] = cell_start[tid * per + k];
-            sum += c[k];
-        }
-        int incl = sum;
+    // exclusive scan of the kCells counts in cell_start (one per thread: warp scan, then warp totals);
+    // leaves the running offsets in cursor as well
+    auto scan_cells = [&]() {
+        static_assert(kCells == kWinThreads, "one cell per thread");
+        const int c = cell_start[tid];
+        int incl = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int n = __shfl_up_sync(0xffffffffu, incl, o);
@@ -206,17 +203,14 @@ knn2_window_kernel(const MatchArgs a, int max_t) {
         }
         if (lane == 31) warp_tot[warp] = incl;
         __syncthreads();
-        int base = incl - sum;
+        int base = incl - c;
         for (int wv = 0; wv < warp; ++wv) base += warp_tot[wv];
-#pragma unroll
-        for (int k = 0; k < per; ++k) {
-            cell_start[tid * per + k] = base;
-            cursor[tid * per + k] = base;
-            base += c[k];
-        }
-        if (tid == kWinThreads - 1) cell_start[kCells] = base;
-    }
-    __syncthreads();
+        cell_start[tid] = base;
+        cursor[tid] = base;
+        if (tid == kWinThreads - 1) cell_start[kCells] = base + c;
+        __syncthreads();
+    };
+    scan_cells();
     for (int i = tid; i < nt; i += kWinThreads) {
         const float2 p = __ldg(txy_g + i);
         const int cell = cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx);
@@ -228,40 +222,66 @@ knn2_window_kernel(const MatchArgs a, int max_t) {
     }
     __syncthreads();
 
-    // ---- 3. one thread per query: visit the cells under its window ------------------------------
-    const int qi = blockIdx.x * kWinThreads + tid;
-    if (qi >= nq) return;
-    uint32_t q[8];
-    {
-        const uint4 lo = __ldg(reinterpret_cast<const uint4*>(qbase + (size_t)qi * 32));
-        const uint4 hi = __ldg(reinterpret_cast<const uint4*>(qbase + (size_t)qi * 32 + 16));
-        q[0] = lo.x; q[1] = lo.y; q[2] = lo.z; q[3] = lo.w;
-        q[4] = hi.x; q[5] = hi.y; q[6] = hi.z; q[7] = hi.w;
+    // ---- 3. queries in cell order ----------------------------------------------------------------
+    // The lanes of a warp then look at the same or adjacent cells: equal trip counts (the warp runs
+    // max-over-lanes iterations) and broadcast reads of the sorted train rows.  Counting sort of the
+    // query rows by the cell of their position in the train grid; cell_start is saved first.
+    const float2* qxy_g = reinterpret_cast<const float2*>(a.q_xy + (size_t)pair * a.q_pair_stride * 2);
+    int my_start[2];
+    my_start[0] = cell_start[tid];
+    my_start[1] = tid == 0 ? cell_start[kCells] : 0;
+    __syncthreads();
+    cell_start[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < nq; i += kWinThreads) {
+        const float2 p = __ldg(qxy_g + i);
+        atomicAdd(&cell_start[cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx)], 1);
     }
-    const float2 qp = __ldg(reinterpret_cast<const float2*>(a.q_xy + ((size_t)pair * a.q_pair_stride + qi) * 2));
-    const float qx = qp.x, qy = qp.y;
-    // widened radius for the cell range only (covers the rounding of qx - tx and of qx +- r)
-    const float rw = r + r * 1.0e-4f + fmaxf(fabsf(qx), fabsf(qy)) * 1.0e-6f;
-    const int cx0 = cell_of(qx - rw, orgx, invx), cx1 = cell_of(qx + rw, orgx, invx);
-    const int cy0 = cell_of(qy - rw, orgy, invy), cy1 = cell_of(qy + rw, orgy, invy);
-    uint32_t k0 = kNoKey, k1 = kNoKey;
-    for (int cy = cy0; cy <= cy1; ++cy) {
-        const int j0 = cell_start[cy * kCellGrid + cx0], j1 = cell_start[cy * kCellGrid + cx1 + 1];
-        for (int j = j0; j < j1; ++j) {
-            const float2 p = txy[j];
-            if (fabsf(__fsub_rn(qx, p.x)) <= r && fabsf(__fsub_rn(qy, p.y)) <= r) {
-                const uint4 lo = tdesc[2 * j], hi = tdesc[2 * j + 1];
-                const int d = __popc(q[0] ^ lo.x) + __popc(q[1] ^ lo.y) + __popc(q[2] ^ lo.z) + __popc(q[3] ^ lo.w) +
-                              __popc(q[4] ^ hi.x) + __popc(q[5] ^ hi.y) + __popc(q[6] ^ hi.z) + __popc(q[7] ^ hi.w);
-                const uint32_t key = ((uint32_t)d << 20) | (uint32_t)tidx[j];
-                k1 = min(k1, max(k0, key));
-                k0 = min(k0, key);
+    __syncthreads();
+    scan_cells();
+    for (int i = tid; i < nq; i += kWinThreads) {
+        const float2 p = __ldg(qxy_g + i);
+        qorder[atomicAdd(&cursor[cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx)], 1)] = (uint16_t)i;
+    }
+    __syncthreads();
+    cell_start[tid] = my_start[0];  // back to the train offsets
+    if (tid == 0) cell_start[kCells] = my_start[1];
+    __syncthreads();
+
+    for (int rank = tid; rank < nq; rank += kWinThreads) {
+        const int qi = qorder[rank];
+        uint32_t q[8];
+        {
+            const uint4 lo = __ldg(reinterpret_cast<const uint4*>(qbase + (size_t)qi * 32));
+            const uint4 hi = __ldg(reinterpret_cast<const uint4*>(qbase + (size_t)qi * 32 + 16));
+            q[0] = lo.x; q[1] = lo.y; q[2] = lo.z; q[3] = lo.w;
+            q[4] = hi.x; q[5] = hi.y; q[6] = hi.z; q[7] = hi.w;
+        }
+        const float2 qp = __ldg(qxy_g + qi);
+        const float qx = qp.x, qy = qp.y;
+        // widened radius for the cell range only (covers the rounding of qx - tx and of qx +- r)
+        const float rw = r + r * 1.0e-4f + fmaxf(fabsf(qx), fabsf(qy)) * 1.0e-6f;
+        const int cx0 = cell_of(qx - rw, orgx, invx), cx1 = cell_of(qx + rw, orgx, invx);
+        const int cy0 = cell_of(qy - rw, orgy, invy), cy1 = cell_of(qy + rw, orgy, invy);
+        uint32_t k0 = kNoKey, k1 = kNoKey;
+        for (int cy = cy0; cy <= cy1; ++cy) {
+            const int j0 = cell_start[cy * kCellGrid + cx0], j1 = cell_start[cy * kCellGrid + cx1 + 1];
+            for (int j = j0; j < j1; ++j) {
+                const float2 p = txy[j];
+                if (fabsf(__fsub_rn(qx, p.x)) <= r && fabsf(__fsub_rn(qy, p.y)) <= r) {
+                    const uint4 lo = tdesc[2 * j], hi = tdesc[2 * j + 1];
+                    const int d = __popc(q[0] ^ lo.x) + __popc(q[1] ^ lo.y) + __popc(q[2] ^ lo.z) + __popc(q[3] ^ lo.w) +
+                                  __popc(q[4] ^ hi.x) + __popc(q[5] ^ hi.y) + __popc(q[6] ^ hi.z) + __popc(q[7] ^ hi.w);
+                    const uint32_t key = ((uint32_t)d << 20) | (uint32_t)tidx[j];
+                    k1 = min(k1, max(k0, key));
+                    k0 = min(k0, key);
+                }
             }
         }
+        reinterpret_cast<int4*>(a.knn + (size_t)pair * a.knn_stride)[qi] =
+            make_int4(k0 == kNoKey ? -1 : (int)(k0 & 0xfffffu), k1 == kNoKey ? -1 : (int)(k1 & 0xfffffu),
+                      k0 == kNoKey ? 0 : (int)(k0 >> 20), k1 == kNoKey ? 0 : (int)(k1 >> 20));
     }
-    reinterpret_cast<int4*>(a.knn + (size_t)pair * a.knn_stride)[qi] =
-        make_int4(k0 == kNoKey ? -1 : (int)(k0 & 0xfffffu), k1 == kNoKey ? -1 : (int)(k1 & 0xfffffu),
-                  k0 == kNoKey ? 0 : (int)(k0 >> 20), k1 == kNoKey ? 0 : (int)(k1 >> 20));
 }
 
 // One CTA per pair.  Walks the queries in ascending order in chunks of blockDim and appends the
@@ -371,10 +391,9 @@ cudaError_t init_match_kernels() {
 int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     if (a.pairs <= 0 || a.max_q <= 0) return 0;
     const bool windowed = a.radius > 0.0f && a.q_xy != nullptr && a.t_xy != nullptr;
-    if (windowed && a.max_t > 0 && window_smem_bytes(a.max_t) <= 200 * 1024) {
-        // cell-binned path: the whole train set of a pair sits in shared memory in cell order
-        dim3 grid((a.max_q + kWinThreads - 1) / kWinThreads, a.pairs);
-        knn2_window_kernel<<<grid, kWinThreads, window_smem_bytes(a.max_t), s>>>(a, a.max_t);
+    if (windowed && a.max_t > 0 && a.max_q <= 65536 && window_smem_bytes(a.max_t, a.max_q) <= 200 * 1024) {
+        // cell-binned path: one CTA per pair, the whole train set sits in shared memory in cell order
+        knn2_window_kernel<<<a.pairs, kWinThreads, window_smem_bytes(a.max_t, a.max_q), s>>>(a, a.max_t, a.max_q);
         return 1;
     }
     dim3 grid((a.max_q + kQPerBlock - 1) / kQPerBlock, a.pairs);
