@@ -352,7 +352,7 @@ def run_ours(args, rank, world, local_rank):
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": table[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
         "frac": table[dom]["achieved_gbs"] / peak,
-        "traffic": TRAFFIC.get(dom),
+        "traffic": TRAFFIC.get(dom) if B == 128 else None,  # the ncu capture was taken at batch 128
         "peak_source": peak_src,
         "bytes_per_launch": ab[dom] * B / max(1.0, dom_launches / args.steps),
         "avg_launch_ms": dom_ms / max(1, dom_launches),
@@ -386,7 +386,10 @@ def run_ours(args, rank, world, local_rank):
                        "l2_policy": f"inputs larger than L2: {B} frames x ~2.3 MB working set per step"},
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e_max / args.steps, "ms_device_events": ms_e2e_dev / args.steps,
-                    "ms_wall": ms_e2e_wall / args.steps, "chunks_in_flight": chunks, "keypoints_per_frame": e2e_nkp},
+                    "ms_wall": ms_e2e_wall / args.steps, "chunks_in_flight": chunks, "keypoints_per_frame": e2e_nkp,
+                    # host->device link rate the streaming path sustained (this rank); a PCIe Gen5 x16 link tops
+                    # out near 52-55 GB/s with the D2H running beside it (scratch/h2d_test.cu), which caps e2e
+                    "h2d_gbs": h2d / (ms_e2e / args.steps * 1e-3) / 1e9},
             "gpu_launches": int(launches_timed),
             "roofline": roofline, "stages": table, "cpu_baseline": cpu, "clocks": clocks,
         }
@@ -396,9 +399,18 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
-# dram bytes per launch of the dominant kernels from the ncu --set full capture (profiles/); filled
-# in by hand after each capture, None until one exists for that kernel.
-TRAFFIC = {}
+def _load_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of every stage's kernels, from the committed
+    `ncu --set full` capture of this command at batch 128 (profiles/traffic.json, written by profiles/traffic.py)."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return {}
+    with open(p) as f:
+        t = json.load(f)
+    return {k: v["dram_bytes_per_launch"] for k, v in t.items() if not k.startswith("_")}
+
+
+TRAFFIC = _load_traffic()
 
 
 def main():
