@@ -14,6 +14,10 @@
  *   core/feature/orb_matcher.cpp:22-25       cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, knn, 2)
  *   core/feature/orb_matcher.cpp:27-36       ratio test  m1.distance < nn_ratio * m2.distance
  *   core/frontend/tracking.cpp:211-222       caller's post-filter  d <= max(2*min_dist, 30)
+ *   core/frontend/tracking.cpp:93-118        CheckFeatureDistribution (5x5 grid occupancy)
+ *   core/frontend/tracking.cpp:120-139       CheckImageQuality (cv::meanStdDev of the gray frame)
+ *   core/frontend/tracking.cpp:505-514       matched point pairs pts_last / pts_curr
+ *   core/frontend/tracking.cpp:548-560       ComputeParallax (mean distance of matched points)
  *
  * Output order is canonical: keypoints (and descriptor rows) are sorted by
  * (octave asc, y asc, x asc) in level coordinates; matches by ascending query index.
@@ -85,6 +89,19 @@ typedef struct vxorb_corner {
     int x, y, score;
 } vxorb_corner;
 
+/* Per-frame quantities the tracking front end derives from the extractor / matcher outputs
+ * (tracking.cpp:93-139, 548-560), computed on the device next to the data. */
+typedef struct vxorb_frame_info {
+    double mean;       /* cv::meanStdDev(gray)[0]: S * (1/N)                                    */
+    double stddev;     /* cv::meanStdDev(gray)[1]: sqrt(max(Q * (1/N) - mean^2, 0)), population */
+    double parallax;   /* mean |p_last - p_curr| over the accepted matches (previous frame ->
+                          this frame) in level-0 pixels; 0 when there are none                  */
+    int grid_occupied; /* cells of the 5x5 grid holding at least one keypoint                   */
+    unsigned grid_mask; /* bit (col * 5 + row), col = (int)((x / width) * 5) clamped, row alike  */
+    int n_keypoints;   /* keypoints written for the frame (<= capacity)                          */
+    int n_matches;     /* accepted matches of the pair (previous frame -> this frame)            */
+} vxorb_frame_info;
+
 typedef struct vxorb_handle vxorb_handle;
 
 void vxorb_default_params(vxorb_params* p);
@@ -113,6 +130,13 @@ int vxorb_extract(vxorb_handle* h, const uint8_t* gray, int width, int height, s
  * (R*9798 + G*19235 + B*3735 + 2^14) >> 15 is fused into the level-0 load. */
 int vxorb_extract_bgr(vxorb_handle* h, const uint8_t* bgr, int width, int height, size_t stride,
                       int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out);
+
+/* vxorb_extract plus the frame's image statistics and grid coverage (CheckImageQuality and
+ * CheckFeatureDistribution of tracking.cpp:93-139 evaluated on the device); parallax and n_matches
+ * are 0.  channels = 1 (gray) or 3 (BGR, converted as vxorb_extract_bgr does). */
+int vxorb_extract_info(vxorb_handle* h, const uint8_t* img, int channels, int width, int height,
+                       size_t stride, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out,
+                       vxorb_frame_info* info_out);
 
 /* `batch` independent gray frames of identical size.  frames[i] points at frame i.  Outputs are
  * frame-major: kp_out[i*kp_cap + k], desc_out[(i*kp_cap + k)*32], n_out[i]. */
@@ -174,6 +198,14 @@ int vxorb_track_submit(vxorb_handle* h, const uint8_t* frames, int batch, int wi
                        size_t stride, size_t frame_stride, float radius, int kp_cap,
                        vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_kp_out, int match_cap,
                        vxorb_match_t* match_out, int* n_match_out, int* slot_out);
+/* vxorb_track_submit plus, per frame, vxorb_frame_info (info_out[batch]) and, per accepted match,
+ * the matched positions pts_out[(i*match_cap + k)*4 .. +3] = (x_last, y_last, x_curr, y_curr) in
+ * level-0 pixels — the pts_last / pts_curr arrays of tracking.cpp:505-514.  Either may be NULL. */
+int vxorb_track_submit_info(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height,
+                            size_t stride, size_t frame_stride, float radius, int kp_cap,
+                            vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_kp_out, int match_cap,
+                            vxorb_match_t* match_out, int* n_match_out, vxorb_frame_info* info_out,
+                            float* pts_out, int* slot_out);
 int vxorb_track_wait(vxorb_handle* h, int slot);
 int vxorb_keypoint_capacity(const vxorb_handle* h);
 

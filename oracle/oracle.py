@@ -71,6 +71,12 @@ def lib():
         L.vxo_match_crosscheck.restype = C.c_int
         L.vxo_postfilter.argtypes = [vp, C.c_int, vp]
         L.vxo_postfilter.restype = C.c_int
+        L.vxo_image_stats.argtypes = [u8p, C.c_int, C.c_int, sz, vp, vp]
+        L.vxo_image_stats.restype = None
+        L.vxo_grid_coverage.argtypes = [f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+        L.vxo_grid_coverage.restype = C.c_int
+        L.vxo_correspondences.argtypes = [f32p, f32p, vp, C.c_int, f32p]
+        L.vxo_correspondences.restype = C.c_double
         _lib = L
     return _lib
 
@@ -221,3 +227,28 @@ def postfilter(matches):
     out = np.zeros(max(len(m), 1), MATCH_DTYPE)
     n = lib().vxo_postfilter(_p(m), len(m), _p(out))
     return out[:n].copy()
+
+
+def image_stats(gray):
+    """cv::meanStdDev of a gray image (Tracking::CheckImageQuality, tracking.cpp:120-139) -> (mean, stddev)."""
+    g = _img(gray)
+    out = np.zeros(2, np.float64)
+    lib().vxo_image_stats(_p(g), g.shape[1], g.shape[0], g.strides[0], out.ctypes.data, out.ctypes.data + 8)
+    return float(out[0]), float(out[1])
+
+
+def grid_coverage(xy, width, height, cols=5, rows=5):
+    """Tracking::CheckFeatureDistribution (tracking.cpp:93-118) -> (occupied cells, mask)."""
+    xy = _xy(xy) if xy is not None and len(xy) else np.zeros((0, 2), np.float32)
+    mask = np.zeros(1, np.uint32)
+    n = lib().vxo_grid_coverage(_p(xy), len(xy), width, height, cols, rows, _p(mask))
+    return int(n), int(mask[0])
+
+
+def correspondences(q_xy, t_xy, matches):
+    """Matched point pairs (tracking.cpp:505-514) and ComputeParallax (tracking.cpp:548-560) -> (pts[n,4], parallax)."""
+    m = np.ascontiguousarray(matches, dtype=MATCH_DTYPE)
+    q_xy, t_xy = _xy(q_xy), _xy(t_xy)
+    pts = np.zeros((max(len(m), 1), 4), np.float32)
+    par = lib().vxo_correspondences(_p(q_xy), _p(t_xy), _p(m), len(m), _p(pts))
+    return pts[:len(m)].copy(), float(par)

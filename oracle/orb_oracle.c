@@ -568,3 +568,62 @@ int vxo_postfilter(const vxorb_match_t* in, int n, vxorb_match_t* out) {
         if ((float)in[i].distance <= lim) out[m++] = in[i];
     return m;
 }
+
+/* ---- caller-side per-frame quantities --------------------------------- */
+
+/* cv::meanStdDev of an 8-bit single-channel image, as Tracking::CheckImageQuality calls it
+ * (core/frontend/tracking.cpp:126-127).  OpenCV accumulates integer sums, then evaluates
+ * mean = S * (1/N), sd = sqrt(max(Q * (1/N) - mean^2, 0)) in double (checked against cv2 4.13 by
+ * tests/golden/make_golden.py -> caller_kat.npz). */
+void vxo_image_stats(const uint8_t* img, int w, int h, size_t stride, double* mean, double* sd) {
+    uint64_t s = 0, q = 0;
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            const uint64_t p = img[(size_t)y * stride + x];
+            s += p;
+            q += p * p;
+        }
+    const double scale = 1.0 / (double)((int64_t)w * h);
+    const double m = (double)s * scale;
+    double var = (double)q * scale - m * m;
+    if (var < 0.0) var = 0.0;
+    *mean = m;
+    *sd = sqrt(var);
+}
+
+/* Tracking::CheckFeatureDistribution (core/frontend/tracking.cpp:93-118): occupied cells of a
+ * cols x rows grid; positions are the keypoints' float level-0 coordinates widened to double
+ * (Feature::position, orb_extractor.cpp:21).  Returns the count; *mask bit = col * rows + row. */
+int vxo_grid_coverage(const float* xy, int n, int width, int height, int cols, int rows, uint32_t* mask) {
+    uint32_t m = 0;
+    for (int i = 0; i < n; ++i) {
+        int col = (int)(((double)xy[2 * i] / width) * cols);
+        int row = (int)(((double)xy[2 * i + 1] / height) * rows);
+        if (col < 0) col = 0;
+        if (col > cols - 1) col = cols - 1;
+        if (row < 0) row = 0;
+        if (row > rows - 1) row = rows - 1;
+        m |= 1u << (col * rows + row);
+    }
+    if (mask) *mask = m;
+    int c = 0;
+    for (uint32_t t = m; t; t &= t - 1) ++c;
+    return c;
+}
+
+/* Matched point pairs (core/frontend/tracking.cpp:505-514) and Tracking::ComputeParallax
+ * (tracking.cpp:548-560): pts[4i..4i+3] = (x_last, y_last, x_curr, y_curr); returns the mean
+ * Euclidean distance in double, summed serially in match order as the reference does. */
+double vxo_correspondences(const float* q_xy, const float* t_xy, const vxorb_match_t* m, int n, float* pts) {
+    double sum = 0.0;
+    for (int i = 0; i < n; ++i) {
+        const float ax = q_xy[2 * m[i].query_idx], ay = q_xy[2 * m[i].query_idx + 1];
+        const float bx = t_xy[2 * m[i].train_idx], by = t_xy[2 * m[i].train_idx + 1];
+        if (pts) {
+            pts[4 * i] = ax; pts[4 * i + 1] = ay; pts[4 * i + 2] = bx; pts[4 * i + 3] = by;
+        }
+        const double dx = (double)ax - (double)bx, dy = (double)ay - (double)by;
+        sum += sqrt(dx * dx + dy * dy);
+    }
+    return n > 0 ? sum / n : 0.0;
+}

@@ -32,6 +32,11 @@ int main(int argc, char** argv) {
         cv::Mat img(h, w, ch == 3 ? CV_8UC3 : CV_8UC1, pix.data(), (size_t)w * ch);
         auto f = std::make_shared<Frame>((uint64_t)i, 0.1 * i, img);
         extractor->Extract(*f);
+        // the caller-side checks of tracking.cpp:93-139, answered from the device-computed frame info
+        auto* ce = dynamic_cast<CudaORBExtractor*>(extractor.get());
+        const vxorb_frame_info& fi_ = ce->last_frame_info();
+        fprintf(stderr, "FRAMEINFO %d %.17g %.17g %d %d %d\n", i, fi_.mean, fi_.stddev, fi_.grid_occupied,
+                ce->ImageQualityOk() ? 1 : 0, ce->FeatureDistributionOk() ? 1 : 0);
         frames.push_back(f);
     }
     fclose(fi);

@@ -215,5 +215,31 @@ def main():
     print("matcher", {k: len(v) for k, v in m.items() if k.endswith("matches")})
 
 
+def caller_kat():
+    """cv::meanStdDev on the gray frame exactly as Tracking::CheckImageQuality calls it
+    (core/frontend/tracking.cpp:120-139: cvtColor(BGR2GRAY) then meanStdDev) -> caller_kat.npz."""
+    rng = np.random.default_rng(23)
+    imgs = {
+        "synth": synth_scene(640, 480, 11),
+        "noise_odd": rng.integers(0, 256, (61, 97), dtype=np.uint8),
+        "const": np.full((100, 100), 7, np.uint8),
+        "bright": rng.integers(250, 256, (131, 203), dtype=np.uint8),
+        "dark_w3": rng.integers(0, 9, (75, 3), dtype=np.uint8),
+        "bgr": rng.integers(0, 256, (77, 123, 3), dtype=np.uint8),
+    }
+    out = {}
+    for k, im in imgs.items():
+        g = cv2.cvtColor(im, cv2.COLOR_BGR2GRAY) if im.ndim == 3 else im
+        mean, sd = cv2.meanStdDev(g)
+        out[k + "_img"] = im
+        out[k + "_stats"] = np.array([mean[0, 0], sd[0, 0]], np.float64)
+    np.savez_compressed(os.path.join(HERE, "caller_kat.npz"), **out)
+    print("caller", {k: v.tolist() for k, v in out.items() if k.endswith("_stats")})
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "caller":
+        caller_kat()
+    else:
+        main()
+        caller_kat()

@@ -44,6 +44,9 @@ def test_struct_layouts_match_header():
     assert vx.KNN2_DTYPE.itemsize == 16
     assert vx.CORNER_DTYPE.itemsize == 12
     assert ctypes.sizeof(vx.Params) == 14 * 4
+    assert vx.FRAME_INFO_DTYPE.itemsize == 40  # 3 doubles + 4 ints, no padding
+    assert [vx.FRAME_INFO_DTYPE.fields[k][1] for k in ("mean", "stddev", "parallax", "grid_occupied", "grid_mask",
+                                                       "n_keypoints", "n_matches")] == [0, 8, 16, 24, 28, 32, 36]
 
 
 def test_create_rejects_bad_params():

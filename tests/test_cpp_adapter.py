@@ -92,6 +92,16 @@ def test_cpp_adapter_matches_oracle(tmp_path):
         gf = m_filt[i - 1]
         assert np.array_equal(np.stack([gf["q"], gf["t"], gf["d"].astype(np.int32)], 1).reshape(-1, 3), matches_as_rows(of))
     assert len(feats[3][0]) == 0 and len(m_plain[2]) == 0
+    # CheckImageQuality / CheckFeatureDistribution (tracking.cpp:93-139) answered by the adapter
+    infos = [l.split()[1:] for l in log.splitlines() if l.startswith("FRAMEINFO")]
+    assert len(infos) == len(frames)
+    for (i, mean, sd, occ, q_ok, d_ok), f, (okp, _) in zip(infos, frames, ref):
+        om, osd = oracle.image_stats(f)
+        assert float(mean) == om and float(sd) == osd
+        oocc, _ = oracle.grid_coverage(np.stack([okp["x"], okp["y"]], 1) if len(okp) else None, 640, 480)
+        assert int(occ) == oocc
+        assert int(q_ok) == int(30 <= om <= 225 and osd >= 20) and int(d_ok) == int(oocc >= 12.5)
+    assert infos[3][4] == "0" and infos[3][5] == "0"  # blank frame fails both checks
     assert "Too few matches" not in log  # an empty side returns before the warning (orb_matcher.cpp:18-20)
 
 

@@ -381,3 +381,55 @@ def test_reference_interface_flow(golden_c1):
     blank = vx.Frame(2, 0.2, np.zeros((480, 640), np.uint8))
     extractor.Extract(blank)
     assert len(blank.Features()) == 0 and matcher.Match(last, blank, matches) == 0 and matches == []
+
+
+# ---- caller-side per-frame quantities ----------------------------------------
+
+def _check_info(info, gray, kp, w, h):
+    mean, sd = oracle.image_stats(gray)
+    assert info["mean"] == mean and info["stddev"] == sd  # integer sums + OpenCV's double expression: bit-exact
+    occ, mask = oracle.grid_coverage(np.stack([kp["x"], kp["y"]], 1) if len(kp) else None, w, h)
+    assert info["grid_occupied"] == occ and info["grid_mask"] == mask
+    assert info["n_keypoints"] == len(kp)
+
+
+@pytest.mark.parametrize("name", ["synth", "noise_odd", "const", "bright", "dark_w3", "bgr"])
+def test_extract_info_golden(h, name):
+    """Image statistics against cv2.meanStdDev (golden), grid coverage against the oracle, single frames."""
+    g = load_golden("caller_kat.npz")
+    img = g[name + "_img"]
+    kp, desc, info = h.extract_info(img)
+    assert info["mean"] == g[name + "_stats"][0] and info["stddev"] == g[name + "_stats"][1]
+    gray = oracle.bgr2gray(img) if img.ndim == 3 else img
+    okp, odesc = oracle.orb_extract(gray)
+    assert_kp_equal(kp, okp)
+    assert np.array_equal(desc, odesc)
+    _check_info(info, gray, kp, img.shape[1], img.shape[0])
+    assert info["n_matches"] == 0 and info["parallax"] == 0.0
+
+
+@pytest.mark.parametrize("size,radius", [((640, 480), 32.0), ((357, 291), 0.0)])
+def test_track_info_vs_oracle(size, radius):
+    """Streaming path with the per-frame info and matched positions, chunks of 3 + 2 frames."""
+    w, hh = size
+    frames = synth_sequence(w, hh, 5, seed=8)
+    ref = _oracle_sequence(frames, radius)
+    with vx.VxOrb(max_width=w, max_height=hh, max_batch=3) as hx:
+        got = hx.track_info(frames[:3], radius) + hx.track_info(frames[3:], radius)
+    prev_xy = None
+    for i, ((kp, desc, m, info, pts), (okp, odesc, om)) in enumerate(zip(got, ref)):
+        assert_kp_equal(kp, okp)
+        assert np.array_equal(matches_as_rows(m), matches_as_rows(om)), f"frame {i}"
+        _check_info(info, frames[i], kp, w, hh)
+        xy = np.stack([kp["x"], kp["y"]], 1)
+        assert info["n_matches"] == len(om)
+        if i == 0:
+            assert info["parallax"] == 0.0 and len(pts) == 0
+        else:
+            opts, opar = oracle.correspondences(prev_xy, xy, om)
+            assert np.array_equal(pts, opts)
+            # distances are computed un-fused in double on both sides; the GPU sums them with a fixed tree,
+            # the reference serially: 1e-12 relative covers the re-association
+            assert abs(info["parallax"] - opar) <= 1e-12 * max(1.0, abs(opar))
+            assert opar > 0.5  # the sequence really moves
+        prev_xy = xy

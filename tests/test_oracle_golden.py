@@ -149,3 +149,51 @@ def test_postfilter():
     assert list(out["query_idx"]) == [0, 1, 4]
     m["distance"] = [40, 90, 79, 81, 80]
     assert list(oracle.postfilter(m)["query_idx"]) == [0, 2, 4]
+
+
+# ---- caller-side per-frame quantities ----------------------------------------
+
+def test_image_stats_golden():
+    """Oracle restatement of cv::meanStdDev (Tracking::CheckImageQuality) is bit-exact against cv2."""
+    g = load_golden("caller_kat.npz")
+    for k in ("synth", "noise_odd", "const", "bright", "dark_w3", "bgr"):
+        img = g[k + "_img"]
+        gray = oracle.bgr2gray(img) if img.ndim == 3 else img
+        mean, sd = oracle.image_stats(gray)
+        assert mean == g[k + "_stats"][0] and sd == g[k + "_stats"][1], k
+
+
+def test_grid_coverage_restatement():
+    """Oracle vs a literal Python transcription of CheckFeatureDistribution (tracking.cpp:93-118)."""
+    rng = np.random.default_rng(4)
+    for n, (w, h) in [(0, (640, 480)), (1, (640, 480)), (40, (640, 480)), (1000, (1241, 376)), (7, (357, 291))]:
+        xy = (rng.uniform(0, 1, (n, 2)) * np.array([w, h]) * rng.choice([0.2, 1.0])).astype(np.float32)
+        if n > 2:
+            xy[0] = (w, h)           # past the last cell: clamped
+            xy[1] = (w * 0.6, 0.0)   # exactly on a cell boundary
+        grid = [[False] * 5 for _ in range(5)]
+        for x, y in xy:
+            col = min(max(int((float(x) / w) * 5), 0), 4)
+            row = min(max(int((float(y) / h) * 5), 0), 4)
+            grid[col][row] = True
+        want = sum(sum(r) for r in grid)
+        got, mask = oracle.grid_coverage(xy, w, h)
+        assert got == want and bin(mask).count("1") == want
+        assert all(bool(mask >> (c * 5 + r) & 1) == grid[c][r] for c in range(5) for r in range(5))
+
+
+def test_correspondences_restatement():
+    rng = np.random.default_rng(9)
+    qxy = rng.uniform(0, 640, (300, 2)).astype(np.float32)
+    txy = rng.uniform(0, 640, (280, 2)).astype(np.float32)
+    m = np.zeros(120, oracle.MATCH_DTYPE)
+    m["query_idx"] = np.sort(rng.permutation(300)[:120])
+    m["train_idx"] = rng.integers(0, 280, 120)
+    pts, par = oracle.correspondences(qxy, txy, m)
+    assert np.array_equal(pts[:, :2], qxy[m["query_idx"]]) and np.array_equal(pts[:, 2:], txy[m["train_idx"]])
+    d = qxy[m["query_idx"]].astype(np.float64) - txy[m["train_idx"]].astype(np.float64)
+    total = 0.0
+    for dx, dy in d:  # serial sum in match order, as ComputeParallax (tracking.cpp:548-560)
+        total += float(np.sqrt(dx * dx + dy * dy))
+    assert par == total / 120
+    assert oracle.correspondences(qxy, txy, m[:0])[1] == 0.0

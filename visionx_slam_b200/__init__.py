@@ -28,6 +28,8 @@ KEYPOINT_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("response", "<f4"), ("an
 MATCH_DTYPE = np.dtype([("query_idx", "<i4"), ("train_idx", "<i4"), ("distance", "<i4")])
 KNN2_DTYPE = np.dtype([("idx", "<i4", (2,)), ("dist", "<i4", (2,))])
 CORNER_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("score", "<i4")])
+FRAME_INFO_DTYPE = np.dtype([("mean", "<f8"), ("stddev", "<f8"), ("parallax", "<f8"), ("grid_occupied", "<i4"),
+                             ("grid_mask", "<u4"), ("n_keypoints", "<i4"), ("n_matches", "<i4")])
 
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_NOMEM = 0, -1, -2, -3, -4
 STAGES = ("pyramid", "fast", "select", "blur", "describe", "match")
@@ -58,6 +60,7 @@ _SYMBOLS = [
     ("vxorb_level_geometry", _i, [_vp, _i, _i, _vp, _vp, _vp, _vp]),
     ("vxorb_extract", _i, [_vp, _vp, _i, _i, _sz, _i, _vp, _vp, _vp]),
     ("vxorb_extract_bgr", _i, [_vp, _vp, _i, _i, _sz, _i, _vp, _vp, _vp]),
+    ("vxorb_extract_info", _i, [_vp, _vp, _i, _i, _i, _sz, _i, _vp, _vp, _vp, _vp]),
     ("vxorb_extract_batch", _i, [_vp, _vp, _i, _i, _i, _sz, _i, _vp, _vp, _vp]),
     ("vxorb_knn2", _i, [_vp, _vp, _i, _vp, _i, _vp]),
     ("vxorb_match", _i, [_vp, _vp, _i, _vp, _i, _f, _i, _vp, _vp]),
@@ -68,6 +71,7 @@ _SYMBOLS = [
     ("vxorb_track_slots", _i, [_vp]),
     ("vxorb_track_reset", _i, [_vp]),
     ("vxorb_track_submit", _i, [_vp, _vp, _i, _i, _i, _sz, _sz, _f, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
+    ("vxorb_track_submit_info", _i, [_vp, _vp, _i, _i, _i, _sz, _sz, _f, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
     ("vxorb_track_wait", _i, [_vp, _i]),
     ("vxorb_keypoint_capacity", _i, [_vp]),
     ("vxorb_host_alloc", _vp, [_sz]),
@@ -225,6 +229,21 @@ class VxOrb:
         out = (kp[:m].copy(), desc[:m].copy())
         return out + (rc, n.value) if return_code else out
 
+    def extract_info(self, img):
+        """extract() plus the frame's vxorb_frame_info: cv::meanStdDev of the gray image and the 5x5 grid
+        coverage of its keypoints (Tracking::CheckImageQuality / CheckFeatureDistribution)."""
+        img = np.ascontiguousarray(img, dtype=np.uint8)
+        cap = self.kp_cap
+        kp = np.zeros(cap, KEYPOINT_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        info = np.zeros(1, FRAME_INFO_DTYPE)
+        n = C.c_int(0)
+        h, w = img.shape[:2]
+        self._check(self._lib.vxorb_extract_info(self._h, _ptr(img), 3 if img.ndim == 3 else 1, w, h, img.strides[0], cap,
+                                                 _ptr(kp), _ptr(desc), C.byref(n), _ptr(info)))
+        m = min(n.value, cap)
+        return kp[:m].copy(), desc[:m].copy(), info[0].copy()
+
     def extract_batch(self, frames, kp_cap=None):
         frames = [np.ascontiguousarray(f, dtype=np.uint8) for f in frames]
         b = len(frames)
@@ -293,6 +312,25 @@ class VxOrb:
 
     def track_wait(self, slot):
         self._check(self._lib.vxorb_track_wait(self._h, slot))
+
+    def track_info(self, frames, radius):
+        """track() plus per-frame vxorb_frame_info and the matched positions (x_last, y_last, x_curr, y_curr)."""
+        frames = np.ascontiguousarray(frames, dtype=np.uint8)
+        b, h, w = frames.shape
+        kp = np.zeros((b, self.kp_cap), KEYPOINT_DTYPE)
+        desc = np.zeros((b, self.kp_cap, 32), np.uint8)
+        nk = np.zeros(b, np.int32)
+        mt = np.zeros((b, self.kp_cap), MATCH_DTYPE)
+        nm = np.zeros(b, np.int32)
+        info = np.zeros(b, FRAME_INFO_DTYPE)
+        pts = np.zeros((b, self.kp_cap, 4), np.float32)
+        slot = C.c_int(-1)
+        self._check(self._lib.vxorb_track_submit_info(self._h, _ptr(frames), b, w, h, frames.strides[1], frames.strides[0],
+                                                      radius, self.kp_cap, _ptr(kp), _ptr(desc), _ptr(nk), self.kp_cap,
+                                                      _ptr(mt), _ptr(nm), _ptr(info), _ptr(pts), C.byref(slot)))
+        self.track_wait(slot.value)
+        return [(kp[i, :nk[i]].copy(), desc[i, :nk[i]].copy(), mt[i, :nm[i]].copy(), info[i].copy(), pts[i, :nm[i]].copy())
+                for i in range(b)]
 
     def track(self, frames, radius):
         """Synchronous convenience: one chunk in, per-frame (kp, desc, matches) out."""

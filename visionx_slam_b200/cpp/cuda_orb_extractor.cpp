@@ -36,10 +36,10 @@ void CudaORBExtractor::Extract(Frame& frame) {
     int rc = VXORB_E_INVALID;
     if (!image.empty() && image.depth() == CV_8U && (image.channels() == 1 || image.channels() == 3)) {
         // cv::ORB converts 3-channel input to gray itself; system.cpp:46 feeds IMREAD_COLOR frames
-        auto fn = image.channels() == 3 ? vxorb_extract_bgr : vxorb_extract;
-        rc = fn(handle_, image.data, image.cols, image.rows, static_cast<size_t>(image.step), kp_cap_, kp_.data(),
-                desc.data, &n);
+        rc = vxorb_extract_info(handle_, image.data, image.channels(), image.cols, image.rows,
+                                static_cast<size_t>(image.step), kp_cap_, kp_.data(), desc.data, &n, &info_);
     }
+    if (rc != VXORB_OK && rc != VXORB_E_CAPACITY) info_ = vxorb_frame_info{};
     last_status_ = rc;
     if (rc != VXORB_OK && rc != VXORB_E_CAPACITY) {
         last_error_ = image.empty() ? "empty or unsupported image" : vxorb_last_error(handle_);

@@ -33,6 +33,15 @@ public:
 
     void Extract(Frame& frame) override;
 
+    // Per-frame quantities of the last Extract, computed on the device beside the extraction
+    // (vxorb_extract_info): what Tracking::CheckImageQuality (tracking.cpp:120-139) and
+    // Tracking::CheckFeatureDistribution (tracking.cpp:93-118) recompute on the host.
+    const vxorb_frame_info& last_frame_info() const { return info_; }
+    // mean in [30, 225] and stddev >= 20 (tracking.cpp:130-137)
+    bool ImageQualityOk() const { return !(info_.mean < 30 || info_.mean > 225) && !(info_.stddev < 20); }
+    // at least half of the 5 x 5 grid cells hold a feature (tracking.cpp:116)
+    bool FeatureDistributionOk() const { return info_.grid_occupied >= (5 * 5 * 0.5); }
+
     // Last vxorb status / message (VXORB_OK after a successful Extract).
     int last_status() const { return last_status_; }
     const std::string& last_error() const { return last_error_; }
@@ -43,6 +52,7 @@ private:
     vxorb_handle* handle_ = nullptr;
     int kp_cap_ = 0;
     std::vector<vxorb_keypoint> kp_;
+    vxorb_frame_info info_{};
     int last_status_ = VXORB_OK;
     std::string last_error_;
 };

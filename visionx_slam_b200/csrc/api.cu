@@ -37,6 +37,10 @@ struct Workspace {
     int batch = 0;          // frames of the chunk in flight / last processed
     bool in_flight = false;
     int* h_status = nullptr;  // pinned: status word copied back with every chunk
+    // caller-side per-frame quantities (frame_info.cu)
+    unsigned long long* sums = nullptr;   // [max_batch][2]
+    vxorb_frame_info* info = nullptr;     // [max_batch]
+    float4* pts = nullptr;                // [max_batch][kp_cap]
 };
 
 }  // namespace
@@ -125,6 +129,8 @@ void free_workspace(Workspace& w) {
     cudaFree(d.fin_key); cudaFree(d.fin_resp); cudaFree(d.fin_n); cudaFree(d.kp); cudaFree(d.desc);
     cudaFree(d.xy); cudaFree(d.kp_n); cudaFree(d.kp_total); cudaFree(d.knn); cudaFree(d.match);
     cudaFree(d.match_n); cudaFree(d.status);
+    cudaFree(w.sums); cudaFree(w.info); cudaFree(w.pts);
+    w.sums = nullptr; w.info = nullptr; w.pts = nullptr;
     d = DeviceBuffers();
 }
 
@@ -244,6 +250,9 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
         CK(cudaMalloc(&d.match_n, sizeof(int) * B));
         CK(cudaMalloc(&d.status, sizeof(int) * 4));
         CK(cudaMemset(d.status, 0, sizeof(int) * 4));
+        CK(cudaMalloc(&w.sums, sizeof(unsigned long long) * 2 * B));
+        CK(cudaMalloc(&w.info, sizeof(vxorb_frame_info) * B));
+        CK(cudaMalloc(&w.pts, sizeof(float4) * cap * B));
     }
     h->geo_w = W;
     h->geo_h = H;
@@ -352,6 +361,17 @@ int enqueue_track_match(vxorb_handle* h, Workspace& ws, int batch, float radius)
     n += launch_match_compact(d.knn, nullptr, h->kp_cap, 0, d.kp_n, batch, h->p.nn_ratio, 0, d.match, h->kp_cap,
                               d.match_n, s);
     sc.end(n);
+    CK(cudaGetLastError());
+    return VXORB_OK;
+}
+
+// Queues the caller-side per-frame quantities (image statistics, grid coverage, matched positions,
+// parallax) for frames 1..batch of the workspace; needs match / match_n of those pairs to be final.
+int enqueue_frame_info(vxorb_handle* h, Workspace& ws, int batch, bool want_pts) {
+    LevelTab lt = h->lt;
+    lt.batch = batch;
+    StageScope sc(h, ws.stream, VXORB_STAGE_MATCH);
+    sc.end(launch_frame_info(lt, ws.db, h->kp_cap, ws.sums, ws.info, want_pts ? ws.pts : nullptr, 5, 5, ws.stream));
     CK(cudaGetLastError());
     return VXORB_OK;
 }
@@ -612,7 +632,8 @@ int vxorb_level_geometry(const vxorb_handle* h, int width, int height, int* leve
 // ---- extraction ----------------------------------------------------------------------------------
 
 static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const uint8_t* bgr, int batch, int W, int H,
-                          size_t stride, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out) {
+                          size_t stride, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out,
+                          vxorb_frame_info* info_out = nullptr) {
     if (!h) return VXORB_E_INVALID;
     if (batch < 1 || batch > h->p.max_batch) return fail(h, VXORB_E_INVALID, "batch outside 1..max_batch");
     if (!n_out || kp_cap < 0 || (kp_cap > 0 && (!kp_out || !desc_out)))
@@ -641,6 +662,12 @@ static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const u
     }
     rc = enqueue_extract(h, ws, batch);
     if (rc) return rc;
+    if (info_out) {  // no pairs here: zero match counts, then statistics + grid coverage of every frame
+        CK(cudaMemsetAsync(ws.db.match_n, 0, sizeof(int) * batch, ws.stream));
+        rc = enqueue_frame_info(h, ws, batch, false);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(info_out, ws.info, sizeof(vxorb_frame_info) * batch, cudaMemcpyDeviceToHost, ws.stream));
+    }
     std::vector<int> counts((size_t)batch * 2 + 4);
     CK(cudaMemcpyAsync(counts.data(), ws.db.kp_n + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
     CK(cudaMemcpyAsync(counts.data() + batch, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
@@ -672,6 +699,16 @@ int vxorb_extract(vxorb_handle* h, const uint8_t* gray, int width, int height, s
     if (!h) return VXORB_E_INVALID;
     if (!gray) return fail(h, VXORB_E_INVALID, "null image");
     return extract_common(h, &gray, nullptr, 1, width, height, stride, kp_cap, kp_out, desc_out, n_out);
+}
+
+int vxorb_extract_info(vxorb_handle* h, const uint8_t* img, int channels, int width, int height, size_t stride,
+                       int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out, vxorb_frame_info* info_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!img || !info_out) return fail(h, VXORB_E_INVALID, "null image or info pointer");
+    if (channels != 1 && channels != 3) return fail(h, VXORB_E_INVALID, "channels must be 1 (gray) or 3 (BGR)");
+    if (channels == 3)
+        return extract_common(h, nullptr, img, 1, width, height, stride, kp_cap, kp_out, desc_out, n_out, info_out);
+    return extract_common(h, &img, nullptr, 1, width, height, stride, kp_cap, kp_out, desc_out, n_out, info_out);
 }
 
 int vxorb_extract_bgr(vxorb_handle* h, const uint8_t* bgr, int width, int height, size_t stride, int kp_cap,
@@ -791,13 +828,21 @@ static int enqueue_carry_out(vxorb_handle* h, Workspace& ws, int batch) {
 int vxorb_track_submit(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height, size_t stride,
                        size_t frame_stride, float radius, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out,
                        int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out, int* slot_out) {
+    return vxorb_track_submit_info(h, frames, batch, width, height, stride, frame_stride, radius, kp_cap, kp_out, desc_out,
+                                   n_kp_out, match_cap, match_out, n_match_out, nullptr, nullptr, slot_out);
+}
+
+int vxorb_track_submit_info(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height, size_t stride,
+                            size_t frame_stride, float radius, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out,
+                            int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out,
+                            vxorb_frame_info* info_out, float* pts_out, int* slot_out) {
     if (!h) return VXORB_E_INVALID;
     if (!frames || !slot_out) return fail(h, VXORB_E_INVALID, "null argument");
     if (batch < 1 || batch > h->p.max_batch) return fail(h, VXORB_E_INVALID, "batch outside 1..max_batch");
     if (stride < (size_t)width) return fail(h, VXORB_E_INVALID, "stride smaller than a row");
     if ((kp_out || desc_out) && kp_cap != h->kp_cap)
         return fail(h, VXORB_E_INVALID, "track outputs must use kp_cap == the handle's max_keypoints");
-    if (match_out && match_cap != h->kp_cap)
+    if ((match_out || pts_out) && match_cap != h->kp_cap)
         return fail(h, VXORB_E_INVALID, "track outputs must use match_cap == the handle's max_keypoints");
     CK(cudaSetDevice(h->p.device_id));
     int rc = ensure_geometry(h, width, height);
@@ -817,12 +862,18 @@ int vxorb_track_submit(vxorb_handle* h, const uint8_t* frames, int batch, int wi
     rc = enqueue_carry_out(h, ws, batch);
     if (rc) return rc;
     CK(cudaEventRecord(ws.done, s));  // descriptors, matches and the carry of this chunk are final
+    if (info_out || pts_out) {
+        rc = enqueue_frame_info(h, ws, batch, pts_out != nullptr);
+        if (rc) return rc;
+    }
     const size_t cap = (size_t)h->kp_cap;
     if (kp_out) CK(cudaMemcpyAsync(kp_out, ws.db.kp + cap, sizeof(vxorb_keypoint) * cap * batch, cudaMemcpyDeviceToHost, s));
     if (desc_out) CK(cudaMemcpyAsync(desc_out, ws.db.desc + cap * 32, 32 * cap * batch, cudaMemcpyDeviceToHost, s));
     if (n_kp_out) CK(cudaMemcpyAsync(n_kp_out, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
     if (match_out) CK(cudaMemcpyAsync(match_out, ws.db.match, sizeof(vxorb_match_t) * cap * batch, cudaMemcpyDeviceToHost, s));
     if (n_match_out) CK(cudaMemcpyAsync(n_match_out, ws.db.match_n, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+    if (info_out) CK(cudaMemcpyAsync(info_out, ws.info, sizeof(vxorb_frame_info) * batch, cudaMemcpyDeviceToHost, s));
+    if (pts_out) CK(cudaMemcpyAsync(pts_out, ws.pts, sizeof(float4) * cap * batch, cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(ws.h_status, ws.db.status, sizeof(int) * 4, cudaMemcpyDeviceToHost, s));
     ws.batch = batch;
     ws.in_flight = true;

@@ -132,6 +132,9 @@ int launch_knn2(const MatchArgs& a, cudaStream_t s);
 int launch_match_compact(const vxorb_knn2_t* knn, const vxorb_knn2_t* back, int knn_stride, int back_stride,
                          const int* q_n, int pairs, float nn_ratio, int mode, vxorb_match_t* out,
                          int out_stride, int* out_n, cudaStream_t s);
+// frame_info.cu: image sums over level 0, grid coverage, matched positions and parallax (2 launches)
+int launch_frame_info(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, unsigned long long* sums,
+                      vxorb_frame_info* info, float4* pts, int grid_cols, int grid_rows, cudaStream_t s);
 int launch_flush(uint8_t* buf, size_t bytes, cudaStream_t s);
 int launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t s);
 
