@@ -247,7 +247,9 @@ def run_ours(args, rank, world, local_rank):
 
     B = args.batch
     # every rank owns an independent sequence (BASELINE config 5: sequences sharded across GPUs)
-    base = synth_sequence(W, H, min(B, 32), seed=2026 + rank)
+    from visionx_slam_b200.shard import aggregate_throughput, max_over_ranks, sequence_seed, shard_sequences
+    my_sequence = shard_sequences(world, world, rank)[0]  # one sequence per rank
+    base = synth_sequence(W, H, min(B, 32), seed=sequence_seed(2026, my_sequence))
     reps = (B + len(base) - 1) // len(base)
     # forward-backward tiling keeps consecutive frames 1-3 px apart across the repeats
     seq = np.concatenate([base if r % 2 == 0 else base[::-1] for r in range(reps)])[:B]
@@ -318,14 +320,9 @@ def run_ours(args, rank, world, local_rank):
     popc_peak = h.measure_popc_rate()
 
     # -------- max over ranks ----------------------------------------------------------------------
-    t = torch.tensor([ms_resident, ms_e2e], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_resident_max, ms_e2e_max = (float(v) for v in t.cpu())
-
-    frames_total = B * args.steps * world
-    value = frames_total / (ms_resident_max * 1e-3)
-    e2e_value = frames_total / (ms_e2e_max * 1e-3)
+    ms_resident_max, ms_e2e_max = max_over_ranks([ms_resident, ms_e2e], world, device="cuda")
+    value = aggregate_throughput(B * args.steps, ms_resident_max, world)
+    e2e_value = aggregate_throughput(B * args.steps, ms_e2e_max, world)
 
     # -------- roofline of the dominant extraction kernel family, per-stage table ------------------
     peak, peak_src = peaks()
