@@ -198,7 +198,7 @@ def host_threads():
 
 def run_reference(args, rank, world):
     if rank != 0:
-        return
+        return None
     from visionx_slam_b200.synth import synth_sequence
     frames = list(synth_sequence(W, H, 24, seed=2026))
     thr = host_threads()
@@ -222,7 +222,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    return json.dumps(line)
 
 
 # ---- our arm -------------------------------------------------------------------------------------
@@ -390,10 +390,10 @@ def run_ours(args, rank, world, local_rank):
             "gpu_launches": int(launches_timed),
             "roofline": roofline, "stages": table, "cpu_baseline": cpu, "clocks": clocks,
         }
-        print(json.dumps(line))
     h.close()
     if world > 1:
         dist.destroy_process_group()
+    return json.dumps(line) if line is not None else None
 
 
 def _load_traffic():
@@ -423,10 +423,22 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.impl == "reference":
-        run_reference(args, rank, world)
-    else:
-        run_ours(args, rank, world, local_rank)
+    # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version banner
+    # there) are sent to stderr for the duration of the run, the line goes to the saved descriptor
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        if args.impl == "reference":
+            line = run_reference(args, rank, world)
+        else:
+            line = run_ours(args, rank, world, local_rank)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    if line is not None:
+        print(line, flush=True)
 
 
 if __name__ == "__main__":
