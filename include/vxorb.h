@@ -165,6 +165,18 @@ int vxorb_match_windowed(vxorb_handle* h, const uint8_t* query, const float* que
                          const uint8_t* train, const float* train_xy, int nt, float radius,
                          float nn_ratio, int out_cap, vxorb_match_t* out, int* n_out);
 
+/* Box-masked variants (BASELINE config 3, stereo left-right matching along the epipolar band) =
+ * cv knnMatch with mask[i][j] = box[0] <= xq_i - xt_j <= box[1] && box[2] <= yq_i - yt_j <= box[3]
+ * (float differences and compares).  box = {dx_min, dx_max, dy_min, dy_max}; the square window of
+ * radius r is the box {-r, r, -r, r}.  For a rectified pair with the left image as query:
+ * {0, max_disparity, -dy_tol, dy_tol}. */
+int vxorb_knn2_boxed(vxorb_handle* h, const uint8_t* query, const float* query_xy, int nq,
+                     const uint8_t* train, const float* train_xy, int nt, const float* box,
+                     vxorb_knn2_t* knn_out);
+int vxorb_match_boxed(vxorb_handle* h, const uint8_t* query, const float* query_xy, int nq,
+                      const uint8_t* train, const float* train_xy, int nt, const float* box,
+                      float nn_ratio, int out_cap, vxorb_match_t* out, int* n_out);
+
 /* cv::BFMatcher(NORM_HAMMING, crossCheck=true).match: (i, j) kept iff j is i's nearest train
  * row and i is j's nearest query row, both with lowest-index tie-break. */
 int vxorb_match_crosscheck(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train,

@@ -71,6 +71,10 @@ def lib():
         L.vxo_match_crosscheck.restype = C.c_int
         L.vxo_postfilter.argtypes = [vp, C.c_int, vp]
         L.vxo_postfilter.restype = C.c_int
+        L.vxo_knn2_boxed.argtypes = [u8p, f32p, C.c_int, u8p, f32p, C.c_int, f32p, vp]
+        L.vxo_knn2_boxed.restype = None
+        L.vxo_match_boxed.argtypes = [u8p, f32p, C.c_int, u8p, f32p, C.c_int, f32p, C.c_float, vp, C.c_int]
+        L.vxo_match_boxed.restype = C.c_int
         L.vxo_image_stats.argtypes = [u8p, C.c_int, C.c_int, sz, vp, vp]
         L.vxo_image_stats.restype = None
         L.vxo_grid_coverage.argtypes = [f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
@@ -252,3 +256,20 @@ def correspondences(q_xy, t_xy, matches):
     pts = np.zeros((max(len(m), 1), 4), np.float32)
     par = lib().vxo_correspondences(_p(q_xy), _p(t_xy), _p(m), len(m), _p(pts))
     return pts[:len(m)].copy(), float(par)
+
+
+def knn2_boxed(q, t, q_xy, t_xy, box):
+    """cv knnMatch(k=2) with the box mask dx in [box0, box1], dy in [box2, box3] on (query - train)."""
+    q, t, q_xy, t_xy = _desc(q), _desc(t), _xy(q_xy), _xy(t_xy)
+    b = np.ascontiguousarray(box, dtype=np.float32)
+    out = np.zeros(len(q), KNN2_DTYPE)
+    lib().vxo_knn2_boxed(_p(q), _p(q_xy), len(q), _p(t), _p(t_xy), len(t), _p(b), _p(out))
+    return out
+
+
+def match_boxed(q, t, q_xy, t_xy, box, nn_ratio=0.8):
+    q, t, q_xy, t_xy = _desc(q), _desc(t), _xy(q_xy), _xy(t_xy)
+    b = np.ascontiguousarray(box, dtype=np.float32)
+    out = np.zeros(max(len(q), 1), MATCH_DTYPE)
+    n = lib().vxo_match_boxed(_p(q), _p(q_xy), len(q), _p(t), _p(t_xy), len(t), _p(b), nn_ratio, _p(out), len(out))
+    return out[:n].copy()

@@ -569,6 +569,50 @@ int vxo_postfilter(const vxorb_match_t* in, int n, vxorb_match_t* out) {
     return m;
 }
 
+/* Box-masked 2-NN + ratio (cv knnMatch with mask[i][j] = box[0] <= xq-xt <= box[1] && box[2] <= yq-yt
+ * <= box[3]; BASELINE config 3 left-right matching).  Same tie-break and ratio rule as vxo_match. */
+void vxo_knn2_boxed(const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy, int nt,
+                    const float* box, vxorb_knn2_t* out) {
+    for (int i = 0; i < nq; ++i) {
+        int d0 = 1 << 30, d1 = 1 << 30, i0 = -1, i1 = -1;
+        for (int j = 0; j < nt; ++j) {
+            const float dx = qxy[2 * i] - txy[2 * j], dy = qxy[2 * i + 1] - txy[2 * j + 1];
+            if (!(dx >= box[0] && dx <= box[1] && dy >= box[2] && dy <= box[3])) continue;
+            int d = hamming256(q + (size_t)i * 32, t + (size_t)j * 32);
+            if (d < d0) {
+                d1 = d0; i1 = i0; d0 = d; i0 = j;
+            } else if (d < d1) {
+                d1 = d; i1 = j;
+            }
+        }
+        out[i].idx[0] = i0;
+        out[i].idx[1] = i1;
+        out[i].dist[0] = i0 >= 0 ? d0 : 0;
+        out[i].dist[1] = i1 >= 0 ? d1 : 0;
+    }
+}
+
+int vxo_match_boxed(const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy, int nt,
+                    const float* box, float nn_ratio, vxorb_match_t* out, int cap) {
+    if (nq <= 0 || nt <= 0) return 0;
+    vxorb_knn2_t* knn = (vxorb_knn2_t*)malloc(sizeof(vxorb_knn2_t) * (size_t)nq);
+    vxo_knn2_boxed(q, qxy, nq, t, txy, nt, box, knn);
+    int n = 0;
+    for (int i = 0; i < nq; ++i) {
+        if (knn[i].idx[1] < 0) continue;
+        if ((float)knn[i].dist[0] < nn_ratio * (float)knn[i].dist[1]) {
+            if (n < cap) {
+                out[n].query_idx = i;
+                out[n].train_idx = knn[i].idx[0];
+                out[n].distance = knn[i].dist[0];
+            }
+            ++n;
+        }
+    }
+    free(knn);
+    return n;
+}
+
 /* ---- caller-side per-frame quantities --------------------------------- */
 
 /* cv::meanStdDev of an 8-bit single-channel image, as Tracking::CheckImageQuality calls it

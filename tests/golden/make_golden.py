@@ -20,7 +20,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(HERE, "..", ".."))
-from visionx_slam_b200.synth import sha256, synth_scene  # noqa: E402
+from visionx_slam_b200.synth import sha256, synth_scene, synth_stereo_pair  # noqa: E402
 
 KP = np.dtype([("x", "<f4"), ("y", "<f4"), ("response", "<f4"), ("angle", "<f4"), ("octave", "<i4")])
 
@@ -237,9 +237,35 @@ def caller_kat():
     print("caller", {k: v.tolist() for k, v in out.items() if k.endswith("_stats")})
 
 
+def box_mask(qxy, txy, box):
+    dx = qxy[:, None, 0] - txy[None, :, 0]
+    dy = qxy[:, None, 1] - txy[None, :, 1]
+    b = np.asarray(box, np.float32)
+    return ((dx >= b[0]) & (dx <= b[1]) & (dy >= b[2]) & (dy <= b[3])).astype(np.uint8)
+
+
+def stereo_kat():
+    """BASELINE config 3 shape: KITTI-size 1241x376 rectified pair, 2000 kp per image, left -> right
+    matching through cv knnMatch with the epipolar-band mask 0 <= xl - xr <= 128, |yl - yr| <= 2
+    -> stereo_kat.npz.  Frames come from synth_stereo_pair (only their hashes are stored)."""
+    left, right = synth_stereo_pair(1241, 376, 31)
+    kl, dl = cv_extract(left, 2000)
+    kr, dr = cv_extract(right, 2000)
+    qxy = np.stack([kl["x"], kl["y"]], 1)
+    txy = np.stack([kr["x"], kr["y"]], 1)
+    box = np.array([0.0, 128.0, -2.0, 2.0], np.float32)
+    knn = cv_knn2(dl, dr, box_mask(qxy, txy, box))
+    m = ratio_matches(knn)
+    np.savez_compressed(os.path.join(HERE, "stereo_kat.npz"), left_sha=sha256(left), right_sha=sha256(right), box=box,
+                        kp_left=kl, desc_left=dl, kp_right=kr, desc_right=dr, knn=knn, matches=m)
+    print("stereo", len(kl), len(kr), "matches", len(m))
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "caller":
-        caller_kat()
-    else:
+    which = sys.argv[1] if len(sys.argv) > 1 else "all"
+    if which in ("all",):
         main()
+    if which in ("all", "caller"):
         caller_kat()
+    if which in ("all", "stereo"):
+        stereo_kat()

@@ -433,3 +433,39 @@ def test_track_info_vs_oracle(size, radius):
             assert abs(info["parallax"] - opar) <= 1e-12 * max(1.0, abs(opar))
             assert opar > 0.5  # the sequence really moves
         prev_xy = xy
+
+
+# ---- BASELINE config 3: stereo pair, left -> right matching along the epipolar band ------------------
+
+def test_stereo_pair_boxed_golden():
+    """1241x376 rectified pair, 2000 kp per view, extracted as one batch, then box-masked matching; all
+    against cv2 (stereo_kat.npz) bit for bit."""
+    from visionx_slam_b200.synth import synth_stereo_pair
+    g = load_golden("stereo_kat.npz")
+    left, right = synth_stereo_pair(1241, 376, 31)
+    with vx.VxOrb(n_features=2000, max_width=1241, max_height=376, max_batch=2, max_train=4096) as hx:
+        (kl, dl), (kr, dr) = hx.extract_batch([left, right])
+        assert_kp_equal(kl, g["kp_left"])
+        assert_kp_equal(kr, g["kp_right"])
+        assert np.array_equal(dl, g["desc_left"]) and np.array_equal(dr, g["desc_right"])
+        qxy, txy = np.stack([kl["x"], kl["y"]], 1), np.stack([kr["x"], kr["y"]], 1)
+        knn = hx.knn2_boxed(dl, dr, qxy, txy, g["box"])
+        assert _knn_equal(knn, g["knn"])
+        m = hx.match_boxed(dl, dr, qxy, txy, g["box"])
+        assert np.array_equal(matches_as_rows(m), g["matches"])
+        # temporal leg of the same config: square window against the oracle
+        mt = hx.match(dl, dr, q_xy=qxy, t_xy=txy, radius=64.0)
+        assert np.array_equal(matches_as_rows(mt), matches_as_rows(oracle.match(dl, dr, 0.8, qxy, txy, 64.0)))
+
+
+@pytest.mark.parametrize("box", [(0.0, 128.0, -2.0, 2.0), (-5.5, 0.25, -100.0, 3.0), (10.0, 10.0, 0.0, 0.0)])
+def test_match_boxed_vs_oracle(h, box):
+    rng = np.random.default_rng(int(box[1] * 4) + 7)
+    t = rng.integers(0, 256, (700, 32), dtype=np.uint8)
+    q = t[rng.permutation(700)[:500]].copy()
+    q[:, 3] ^= rng.integers(0, 4, 500).astype(np.uint8)
+    qxy = np.round(rng.uniform(0, 300, (500, 2)) * 4).astype(np.float32) / 4  # quarter-pixel lattice: exact ties on the bounds
+    txy = np.round(rng.uniform(0, 300, (700, 2)) * 4).astype(np.float32) / 4
+    assert _knn_equal(h.knn2_boxed(q, t, qxy, txy, box), oracle.knn2_boxed(q, t, qxy, txy, box))
+    assert np.array_equal(matches_as_rows(h.match_boxed(q, t, qxy, txy, box)),
+                          matches_as_rows(oracle.match_boxed(q, t, qxy, txy, box)))

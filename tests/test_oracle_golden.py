@@ -197,3 +197,27 @@ def test_correspondences_restatement():
         total += float(np.sqrt(dx * dx + dy * dy))
     assert par == total / 120
     assert oracle.correspondences(qxy, txy, m[:0])[1] == 0.0
+
+
+# ---- BASELINE config 3: stereo left -> right matching with the epipolar-band box mask ---------------
+
+def test_stereo_boxed_golden():
+    """Oracle extract of both views + box-masked 2-NN + ratio against cv2 (stereo_kat.npz)."""
+    from visionx_slam_b200.synth import synth_stereo_pair
+    g = load_golden("stereo_kat.npz")
+    left, right = synth_stereo_pair(1241, 376, 31)
+    assert sha256(left) == str(g["left_sha"]) and sha256(right) == str(g["right_sha"])
+    kl, dl = oracle.orb_extract(left, n_features=2000)
+    kr, dr = oracle.orb_extract(right, n_features=2000)
+    assert_kp_equal(kl, g["kp_left"]) and assert_kp_equal(kr, g["kp_right"])
+    assert np.array_equal(dl, g["desc_left"]) and np.array_equal(dr, g["desc_right"])
+    qxy, txy = np.stack([kl["x"], kl["y"]], 1), np.stack([kr["x"], kr["y"]], 1)
+    knn = oracle.knn2_boxed(dl, dr, qxy, txy, g["box"])
+    assert np.array_equal(knn["idx"], g["knn"]["idx"])
+    assert np.array_equal(np.where(knn["idx"] >= 0, knn["dist"], 0), np.where(g["knn"]["idx"] >= 0, g["knn"]["dist"], 0))
+    m = oracle.match_boxed(dl, dr, qxy, txy, g["box"])
+    assert np.array_equal(matches_as_rows(m), g["matches"])
+    assert len(m) > 1000
+    # the square window is the box {-r, r, -r, r}
+    assert np.array_equal(oracle.knn2_boxed(dl, dr, qxy, txy, [-40, 40, -40, 40])["idx"],
+                          oracle.knn2(dl, dr, qxy, txy, 40.0)["idx"])

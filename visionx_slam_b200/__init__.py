@@ -66,6 +66,8 @@ _SYMBOLS = [
     ("vxorb_match", _i, [_vp, _vp, _i, _vp, _i, _f, _i, _vp, _vp]),
     ("vxorb_knn2_windowed", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _f, _vp]),
     ("vxorb_match_windowed", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _i, _vp, _vp]),
+    ("vxorb_knn2_boxed", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp]),
+    ("vxorb_match_boxed", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _f, _i, _vp, _vp]),
     ("vxorb_match_crosscheck", _i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp]),
     ("vxorb_match_filtered", _i, [_vp, _vp, _i, _vp, _i, _f, _i, _vp, _vp]),
     ("vxorb_track_slots", _i, [_vp]),
@@ -283,6 +285,24 @@ class VxOrb:
             return self._match_call(self._lib.vxorb_match_windowed, q,
                                     (self._h, _ptr(q), _ptr(q_xy), len(q), _ptr(t), _ptr(t_xy), len(t), radius, nn_ratio))
         return self._match_call(self._lib.vxorb_match, q, (self._h, _ptr(q), len(q), _ptr(t), len(t), nn_ratio))
+
+    def knn2_boxed(self, q, t, q_xy, t_xy, box):
+        q, t, q_xy, t_xy = _desc(q), _desc(t), _xy(q_xy), _xy(t_xy)
+        b = np.ascontiguousarray(box, dtype=np.float32)
+        out = np.zeros(len(q), KNN2_DTYPE)
+        self._check(self._lib.vxorb_knn2_boxed(self._h, _ptr(q), _ptr(q_xy), len(q), _ptr(t), _ptr(t_xy), len(t), _ptr(b),
+                                               _ptr(out)))
+        return out
+
+    def match_boxed(self, q, t, q_xy, t_xy, box, nn_ratio=0.0):
+        """Stereo / epipolar-band matching: mask dx in [box0, box1], dy in [box2, box3] on (query - train)."""
+        q, t, q_xy, t_xy = _desc(q), _desc(t), _xy(q_xy), _xy(t_xy)
+        b = np.ascontiguousarray(box, dtype=np.float32)
+        out = np.zeros(max(len(q), 1), MATCH_DTYPE)
+        n = C.c_int(0)
+        self._check(self._lib.vxorb_match_boxed(self._h, _ptr(q), _ptr(q_xy), len(q), _ptr(t), _ptr(t_xy), len(t), _ptr(b),
+                                                nn_ratio, len(out), _ptr(out), C.byref(n)))
+        return out[:n.value].copy()
 
     def match_crosscheck(self, q, t):
         q, t = _desc(q), _desc(t)

@@ -428,7 +428,7 @@ int ensure_match_scratch(vxorb_handle* h, int rows) {
 // Host-buffer knn: uploads both descriptor sets and runs the knn kernel into m_knn (and, for the
 // cross-check, the reverse direction into m_back).
 int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy,
-                 int nt, float radius, bool reverse_too) {
+                 int nt, float radius, bool reverse_too, const float* box = nullptr) {
     if (nq < 0 || nt < 0 || (nq > 0 && !q) || (nt > 0 && !t)) return fail(h, VXORB_E_INVALID, "bad descriptor arguments");
     if (nq > h->p.max_train || nt > h->p.max_train || nt >= (1 << 20) || nq >= (1 << 20))
         return fail(h, VXORB_E_INVALID, "descriptor count exceeds max_train");
@@ -439,7 +439,8 @@ int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, co
     CK(cudaMemcpyAsync(h->m_n, n, sizeof(n), cudaMemcpyHostToDevice, s));
     if (nq) CK(cudaMemcpyAsync(h->m_q, q, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
     if (nt) CK(cudaMemcpyAsync(h->m_t, t, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
-    const bool win = radius > 0.f && qxy && txy;
+    const bool win = (radius > 0.f || box) && qxy && txy;
+    if (box && !win) return fail(h, VXORB_E_INVALID, "box mask needs query and train positions");
     if (win) {
         if (nq) CK(cudaMemcpyAsync(h->m_qxy, qxy, (size_t)nq * 8, cudaMemcpyHostToDevice, s));
         if (nt) CK(cudaMemcpyAsync(h->m_txy, txy, (size_t)nt * 8, cudaMemcpyHostToDevice, s));
@@ -452,6 +453,10 @@ int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, co
     a.q_pair_stride = a.t_pair_stride = 0;
     a.max_q = nq; a.max_t = nt; a.pairs = 1; a.radius = win ? radius : 0.f;
     a.knn = h->m_knn; a.knn_stride = 0;
+    if (box) {
+        a.boxed = 1;
+        for (int i = 0; i < 4; ++i) a.box[i] = box[i];
+    }
     int launches = launch_knn2(a, s);
     if (reverse_too) {
         MatchArgs b = a;
@@ -466,14 +471,15 @@ int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, co
 }
 
 int run_match_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy,
-                   int nt, float radius, float nn_ratio, int mode, int out_cap, vxorb_match_t* out, int* n_out) {
+                   int nt, float radius, float nn_ratio, int mode, int out_cap, vxorb_match_t* out, int* n_out,
+                   const float* box = nullptr) {
     if (!n_out || out_cap < 0 || (out_cap > 0 && !out)) return fail(h, VXORB_E_INVALID, "bad output arguments");
     *n_out = 0;
     if (nq <= 0 || nt <= 0) {  // orb_matcher.cpp:18-20: either side empty -> no matches
         if (nq < 0 || nt < 0) return fail(h, VXORB_E_INVALID, "negative descriptor count");
         return VXORB_OK;
     }
-    int rc = run_knn_host(h, q, qxy, nq, t, txy, nt, radius, mode == 2);
+    int rc = run_knn_host(h, q, qxy, nq, t, txy, nt, radius, mode == 2, box);
     if (rc) return rc;
     cudaStream_t s = h->ws[0].stream;
     if (nn_ratio <= 0.f) nn_ratio = h->p.nn_ratio;
@@ -728,12 +734,12 @@ int vxorb_extract_batch(vxorb_handle* h, const uint8_t* const* frames, int batch
 // ---- matching ------------------------------------------------------------------------------------
 
 static int knn_common(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, const uint8_t* t,
-                      const float* txy, int nt, float radius, vxorb_knn2_t* knn_out) {
+                      const float* txy, int nt, float radius, vxorb_knn2_t* knn_out, const float* box = nullptr) {
     if (!h) return VXORB_E_INVALID;
     if (nq > 0 && !knn_out) return fail(h, VXORB_E_INVALID, "null output");
     CK(cudaSetDevice(h->p.device_id));
     if (nq <= 0) return nq < 0 ? fail(h, VXORB_E_INVALID, "negative count") : VXORB_OK;
-    int rc = run_knn_host(h, q, qxy, nq, t, txy, nt, radius, false);
+    int rc = run_knn_host(h, q, qxy, nq, t, txy, nt, radius, false, box);
     if (rc) return rc;
     cudaStream_t s = h->ws[0].stream;
     CK(cudaMemcpyAsync(knn_out, h->m_knn, sizeof(vxorb_knn2_t) * (size_t)nq, cudaMemcpyDeviceToHost, s));
@@ -750,6 +756,27 @@ int vxorb_knn2_windowed(vxorb_handle* h, const uint8_t* query, const float* quer
     if (h && (!query_xy || !train_xy || !(radius > 0.f)))
         return fail(h, VXORB_E_INVALID, "windowed match needs positions and radius > 0");
     return knn_common(h, query, query_xy, nq, train, train_xy, nt, radius, knn_out);
+}
+
+static bool box_ok(const float* box) {
+    return box && box[0] <= box[1] && box[2] <= box[3];  // also rejects NaN bounds
+}
+
+int vxorb_knn2_boxed(vxorb_handle* h, const uint8_t* query, const float* query_xy, int nq, const uint8_t* train,
+                     const float* train_xy, int nt, const float* box, vxorb_knn2_t* knn_out) {
+    if (h && (!query_xy || !train_xy || !box_ok(box)))
+        return fail(h, VXORB_E_INVALID, "boxed match needs positions and box = {dx_min <= dx_max, dy_min <= dy_max}");
+    return knn_common(h, query, query_xy, nq, train, train_xy, nt, 0.f, knn_out, box);
+}
+
+int vxorb_match_boxed(vxorb_handle* h, const uint8_t* query, const float* query_xy, int nq, const uint8_t* train,
+                      const float* train_xy, int nt, const float* box, float nn_ratio, int out_cap,
+                      vxorb_match_t* out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!query_xy || !train_xy || !box_ok(box))
+        return fail(h, VXORB_E_INVALID, "boxed match needs positions and box = {dx_min <= dx_max, dy_min <= dy_max}");
+    CK(cudaSetDevice(h->p.device_id));
+    return run_match_host(h, query, query_xy, nq, train, train_xy, nt, 0.f, nn_ratio, 0, out_cap, out, n_out, box);
 }
 
 int vxorb_match(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, float nn_ratio,

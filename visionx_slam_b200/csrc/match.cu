@@ -33,7 +33,10 @@ knn2_kernel(const MatchArgs a) {
     const int qi = blockIdx.x * kQPerBlock + threadIdx.x;
     if (blockIdx.x * kQPerBlock >= nq) return;  // whole CTA idle
     const bool live = qi < nq;
-    const bool windowed = a.radius > 0.0f && a.q_xy != nullptr && a.t_xy != nullptr;
+    const bool windowed = (a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr;
+    // square window = the box [-r, r] x [-r, r] on (xq - xt, yq - yt): |d| <= r <=> -r <= d <= r in float
+    const float bx0 = a.boxed ? a.box[0] : -a.radius, bx1 = a.boxed ? a.box[1] : a.radius;
+    const float by0 = a.boxed ? a.box[2] : -a.radius, by1 = a.boxed ? a.box[3] : a.radius;
 
     const uint8_t* qbase = a.q_desc + (size_t)pair * a.q_pair_stride * 32;
     const uint8_t* tbase = a.t_desc + (size_t)pair * a.t_pair_stride * 32;
@@ -79,7 +82,8 @@ knn2_kernel(const MatchArgs a) {
         } else {
             for (int j = 0; j < tn; ++j) {
                 const float2 p = txy[j];
-                const bool in = fabsf(__fsub_rn(qx, p.x)) <= a.radius && fabsf(__fsub_rn(qy, p.y)) <= a.radius;
+                const float dx = __fsub_rn(qx, p.x), dy = __fsub_rn(qy, p.y);
+                const bool in = dx >= bx0 && dx <= bx1 && dy >= by0 && dy <= by1;
                 if (__any_sync(0xffffffffu, in)) {
                     const uint4 lo = *reinterpret_cast<const uint4*>(&tdesc[j][0]);
                     const uint4 hi = *reinterpret_cast<const uint4*>(&tdesc[j][4]);
@@ -390,7 +394,7 @@ cudaError_t init_match_kernels() {
 
 int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     if (a.pairs <= 0 || a.max_q <= 0) return 0;
-    const bool windowed = a.radius > 0.0f && a.q_xy != nullptr && a.t_xy != nullptr;
+    const bool windowed = a.radius > 0.0f && !a.boxed && a.q_xy != nullptr && a.t_xy != nullptr;
     if (windowed && a.max_t > 0 && a.max_q <= 65536 && window_smem_bytes(a.max_t, a.max_q) <= 200 * 1024) {
         // cell-binned path: one CTA per pair, the whole train set sits in shared memory in cell order
         knn2_window_kernel<<<a.pairs, kWinThreads, window_smem_bytes(a.max_t, a.max_q), s>>>(a, a.max_t, a.max_q);

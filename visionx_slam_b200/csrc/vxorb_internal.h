@@ -124,6 +124,10 @@ struct MatchArgs {
     int max_t = 0;                                  // upper bound of t_n (shared-memory sizing of the windowed path)
     int pairs;
     float radius;                                   // <= 0: brute force
+    // box mask (stereo / epipolar band): pair allowed iff box[0] <= xq - xt <= box[1] and
+    // box[2] <= yq - yt <= box[3]; used instead of the square window when boxed != 0
+    int boxed = 0;
+    float box[4] = {0.f, 0.f, 0.f, 0.f};
     vxorb_knn2_t* knn;                              // [pair][knn_stride]
     int knn_stride;
 };

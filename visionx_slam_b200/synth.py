@@ -67,5 +67,17 @@ def synth_sequence(w, h, n_frames, seed, max_step=3, noise=2.0):
     return frames
 
 
+def synth_stereo_pair(w=1241, h=376, seed=31):
+    """Rectified stereo pair of BASELINE config 3's shape: the right view is the left scene shifted left
+    by a row-dependent disparity (8..63 px) plus +-2 grey levels of noise."""
+    left = synth_scene(w, h, seed)
+    rng = np.random.default_rng(seed)
+    right = np.empty_like(left)
+    for y in range(h):
+        right[y] = np.roll(left[y], -(8 + (y * 56) // h))
+    right = np.clip(right.astype(np.int16) + rng.integers(-2, 3, right.shape), 0, 255).astype(np.uint8)
+    return left, right
+
+
 def sha256(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
