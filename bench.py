@@ -239,6 +239,14 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # several ranks share the host: keep this rank's threads (and, by first touch, its pinned
+        # staging buffers) on the CPUs NVML reports as local to its GPU
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
+        except Exception as e:  # no NVML / no permission: run unbound
+            sys.stderr.write(f"bench.py: CPU affinity not set ({e!r})\n")
 
     def barrier():
         if world > 1:
