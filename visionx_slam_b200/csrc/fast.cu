@@ -7,13 +7,13 @@
 // (so corner <=> score >= t); kept iff its score is strictly greater than the 8 neighbours'.
 // Integer work, bit-exact.
 //
-// Persistent CTAs (8 warps) walk over tiles whose score region is 128 x 40 px (emission region: the
-// inner 124 x 38); the level pixels a tile needs sit in shared memory as 32-bit words and the score
+// Persistent CTAs (8 warps) walk over tiles whose score region is 128 x 48 px (emission region: the
+// inner 124 x 46); the level pixels a tile needs sit in shared memory as 32-bit words and the score
 // map never leaves shared memory.  Warp w owns score rows w, w + 8, ... of the tile from the first
 // test to the emission, so a tile costs ONE CTA barrier (between scoring and NMS, which reads the
 // neighbouring rows other warps scored); score maps and tile buffers are double buffered.
 //   load    one TMA box per tile (cp.async.bulk.tensor.3d over a per-level {pitch, rows, frame}
-//           tensor map: 46 rows x 160 B = 3-row ring halo, halo words left and right, 16 B aligned start),
+//           tensor map: 54 rows x 160 B = 3-row ring halo, halo words left and right, 16 B aligned start),
 //           issued two tiles ahead right after the barrier that frees the buffer and completed
 //           through an mbarrier; pixels outside the plane are zero-filled by the TMA unit and are
 //           never part of a valid ring
@@ -21,7 +21,7 @@
 //           needs, for each opposite ring pair {k, k+8}, one pixel with |p - v| > t, so
 //           (F0|F8) & (F4|F12) with F = per-byte |p - v| > t (VABSDIFF4 + carry trick) is a
 //           necessary condition; 16-byte pixel rows -> 5 LDS, 2 PRMT, 4 VABSDIFF4, ~16 logic ops
-//           per 4 px.  Survivor bits of the warp's 5 rows collect in one register per lane and are
+//           per 4 px.  Survivor bits of the warp's 6 rows collect in one register per lane and are
 //           compacted into the warp's own list with one warp prefix sum (no atomics).
 //   stage 2 one lane scores one listed pixel, both polarities at once in s16x2 halves:
 //           D_k = (p_k - v + 256) | (v - p_k + 256) << 16 is ONE IMAD per ring pixel, min over 9
@@ -46,7 +46,10 @@ constexpr int TROWS = FSR + 6, TWORDS = FW / 4 + 8;  // tile rows, 32-bit words 
 constexpr uint32_t kTileBytes = TROWS * TWORDS * 4;
 constexpr int TPITCH = TWORDS * 4;
 constexpr int RPW = FSR / 8;                          // score rows per warp
-constexpr int kFastCtasPerSm = 6;                      // 35.4 KB of shared memory and 32 registers per thread
+#ifndef VXORB_FAST_CTAS
+#define VXORB_FAST_CTAS 5
+#endif
+constexpr int kFastCtasPerSm = VXORB_FAST_CTAS;                      // 41.4 KB of shared memory and 32 registers per thread; swept 3..8
 constexpr int WQCAP = RPW * FW;                       // pixels one warp tests per tile
 
 // ring offsets (dx, dy), k = 0..15, as byte offsets into the tile

@@ -34,8 +34,11 @@ constexpr int kBlurRows = 64;    // output rows per blur strip
 
 // FAST tiling (fast.cu): a CTA computes scores for kFastScoreW x kFastScoreH pixels and emits corners
 // from the inner kFastEmitW x kFastEmitH; tile origins are multiples of 4 px in x.
-constexpr int kFastScoreW = 128, kFastScoreH = 40;
-constexpr int kFastEmitW = 124, kFastEmitH = 38;
+#ifndef VXORB_FAST_ROWS
+#define VXORB_FAST_ROWS 48  // score rows per tile (multiple of 8, <= 64: one row in eight per warp); swept 24..64 on B200
+#endif
+constexpr int kFastScoreW = 128, kFastScoreH = VXORB_FAST_ROWS;
+constexpr int kFastEmitW = 124, kFastEmitH = kFastScoreH - 2;
 inline int fast_tiles_x(int w, int border) {
     const int first = ((border - 1) & ~3) + 1;  // first emission column a tile row can cover
     const int span = (w - border) - first;
