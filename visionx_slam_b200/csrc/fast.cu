@@ -46,6 +46,7 @@ constexpr int TROWS = FSR + 6, TWORDS = FW / 4 + 8;  // tile rows, 32-bit words 
 constexpr uint32_t kTileBytes = TROWS * TWORDS * 4;
 constexpr int TPITCH = TWORDS * 4;
 constexpr int RPW = FSR / 8;                          // score rows per warp
+static_assert(FSR % 8 == 0 && RPW >= 1 && RPW <= 8, "a lane keeps 4 survivor bits per row in one 32-bit register");
 #ifndef VXORB_FAST_CTAS
 #define VXORB_FAST_CTAS 5
 #endif
