@@ -81,7 +81,13 @@ namespace {
 
 constexpr int kPaW = 48, kPaH = 31, kPaBytes = kPaW * kPaH, kPaStride = 1536;  // orientation window (un-blurred)
 constexpr int kPbW = 64, kPbH = 37, kPbBytes = kPbW * kPbH, kPbStride = 2432;  // descriptor window (blurred)
-constexpr int kDescWarps = 4;
+#ifndef VXORB_DESC_WARPS
+#define VXORB_DESC_WARPS 4
+#endif
+#ifndef VXORB_DESC_GROUP
+#define VXORB_DESC_GROUP 16
+#endif
+constexpr int kDescWarps = VXORB_DESC_WARPS;
 constexpr int kDepthA = 4, kDepthB = 3;            // windows in flight per warp
 constexpr int kWinBytes = kDepthB * kPbStride;     // per-warp window memory, shared by both phases
 static_assert(kDepthA * kPaStride <= kWinBytes, "orientation windows must fit the per-warp region");
@@ -108,7 +114,7 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
 
 }  // namespace
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(32 * kDescWarps)
 describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                 const uint32_t* __restrict__ fin_key, const float* __restrict__ fin_resp,
                 const int* __restrict__ fin_n, int kp_cap, int group, vxorb_keypoint* __restrict__ kp_out,
@@ -117,7 +123,7 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
     __shared__ __align__(128) uint8_t win[kDescWarps][kWinBytes];
     const int f = blockIdx.y;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int g0 = (blockIdx.x * 4 + (threadIdx.x >> 5)) * group;  // first keypoint of this warp's group
+    const int g0 = (blockIdx.x * kDescWarps + (threadIdx.x >> 5)) * group;  // first keypoint of this warp's group
 
     // ---- setup: locate keypoint g0 + lane from the per-level counts -----------------------------
     const int g = g0 + lane;
@@ -320,7 +326,7 @@ cudaError_t init_device_tables() {
 int launch_describe(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, cudaStream_t s) {
     // 16 keypoints per warp amortise the per-group trigonometry; tiny batches use 4 so that one
     // frame still spreads over ~80 CTAs
-    const int group = lt.batch >= 8 ? 16 : 4;
+    const int group = lt.batch >= 8 ? VXORB_DESC_GROUP : 4;
     const int warps = (kp_cap + group - 1) / group;
     dim3 grid((warps + kDescWarps - 1) / kDescWarps, lt.batch);
     describe_kernel<<<grid, 32 * kDescWarps, 0, s>>>(lt, db.pyr, db.blur, db.fin_key, db.fin_resp, db.fin_n, kp_cap, group, db.kp,

@@ -30,7 +30,10 @@ constexpr int kPitchAlign = 32;
 constexpr int kApronY = 3;
 constexpr int kApronX = 16;
 constexpr int kApronRight = 12;
-constexpr int kBlurRows = 64;    // output rows per blur strip
+#ifndef VXORB_BLUR_ROWS
+#define VXORB_BLUR_ROWS 64
+#endif
+constexpr int kBlurRows = VXORB_BLUR_ROWS;    // output rows per blur strip
 
 // FAST tiling (fast.cu): a CTA computes scores for kFastScoreW x kFastScoreH pixels and emits corners
 // from the inner kFastEmitW x kFastEmitH; tile origins are multiples of 4 px in x.
