@@ -34,6 +34,10 @@ struct Workspace {
     DeviceBuffers db;
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
+    // side stream of the slot: the blur of a chunk runs here beside FAST + select (both only read the
+    // pyramid); forked after the pyramid and joined before the descriptors
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int batch = 0;          // frames of the chunk in flight / last processed
     bool in_flight = false;
     int* h_status = nullptr;  // pinned: status word copied back with every chunk
@@ -308,6 +312,19 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
         StageScope sc(h, s, VXORB_STAGE_PYRAMID);
         sc.end(launch_pyramid(lt, d, s));
     }
+    // The blur needs only the pyramid, FAST + select never touch the blurred planes: outside the
+    // instrumented (per-stage timed) mode the blur runs on the slot's side stream beside them and fills
+    // the issue slots FAST's barriers and select's tails leave idle.  Instrumented runs stay serial so a
+    // stage's events bracket that stage alone.
+    const bool overlap = !h->stage_enabled && ws.side != nullptr;
+    if (overlap) {
+        CK(cudaEventRecord(ws.ev_fork, s));
+        CK(cudaStreamWaitEvent(ws.side, ws.ev_fork, 0));
+        const int n = launch_blur(lt, d, ws.side);
+        h->launches += n;
+        h->stage_launches[VXORB_STAGE_BLUR] += n;
+        CK(cudaEventRecord(ws.ev_join, ws.side));
+    }
     {
         StageScope sc(h, s, VXORB_STAGE_FAST);
         const int n = launch_fast(lt, d, h->p.fast_threshold, kEdge, s);
@@ -318,7 +335,9 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
         StageScope sc(h, s, VXORB_STAGE_SELECT);
         sc.end(launch_select(lt, d, s));
     }
-    {
+    if (overlap) {
+        CK(cudaStreamWaitEvent(s, ws.ev_join, 0));
+    } else {
         StageScope sc(h, s, VXORB_STAGE_BLUR);
         sc.end(launch_blur(lt, d, s));
     }
@@ -585,6 +604,9 @@ int vxorb_create(const vxorb_params* p, vxorb_handle** out) {
     for (auto& w : h->ws) {
         if ((e = cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "stream");
         if ((e = cudaEventCreateWithFlags(&w.done, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
+        if ((e = cudaStreamCreateWithFlags(&w.side, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "side stream");
+        if ((e = cudaEventCreateWithFlags(&w.ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
+        if ((e = cudaEventCreateWithFlags(&w.ev_join, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
         if ((e = cudaHostAlloc(&w.h_status, sizeof(int) * 4, cudaHostAllocDefault)) != cudaSuccess) return bail(e, "pinned");
         w.h_status[0] = 0;
     }
@@ -605,6 +627,9 @@ void vxorb_destroy(vxorb_handle* h) {
     for (auto& w : h->ws) {
         if (w.stream) cudaStreamDestroy(w.stream);
         if (w.done) cudaEventDestroy(w.done);
+        if (w.side) cudaStreamDestroy(w.side);
+        if (w.ev_fork) cudaEventDestroy(w.ev_fork);
+        if (w.ev_join) cudaEventDestroy(w.ev_join);
         if (w.h_status) cudaFreeHost(w.h_status);
     }
     cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);

@@ -386,9 +386,12 @@ int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t
 
 // Picks the band height of one level: the largest of 16 / 8 / 4 rows whose biggest source chunk
 // (the last band takes the remainder rows, so it is the largest) stays under 40 KB of shared memory.
+#ifndef VXORB_BAND_ROWS
+#define VXORB_BAND_ROWS 16
+#endif
 bool plan_resize_bands(const uint32_t* ytaps, int dh, int sh, int spitch, int* band_rows, int* n_bands, int* smem) {
     if (dh < 8) return false;
-    for (int rows = 16; rows >= 4; rows >>= 1) {
+    for (int rows = VXORB_BAND_ROWS; rows >= 4; rows >>= 1) {
         const int nb = std::max(1, dh / rows);
         int worst = 0;
         for (int b = 0; b < nb; ++b) {
