@@ -12,6 +12,7 @@
 
 #include <algorithm>
 #include <mutex>
+#include <stdlib.h>
 #include <string>
 #include <vector>
 
@@ -316,7 +317,7 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
     // instrumented (per-stage timed) mode the blur runs on the slot's side stream beside them and fills
     // the issue slots FAST's barriers and select's tails leave idle.  Instrumented runs stay serial so a
     // stage's events bracket that stage alone.
-    const bool overlap = !h->stage_enabled && ws.side != nullptr;
+    const bool overlap = !h->stage_enabled && ws.side != nullptr && !getenv("VXORB_NO_OVERLAP");
     if (overlap) {
         CK(cudaEventRecord(ws.ev_fork, s));
         CK(cudaStreamWaitEvent(ws.side, ws.ev_fork, 0));
