@@ -265,38 +265,46 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
     uint32_t* ok = fin_key + lt.fin_off[l] + (size_t)f * fcap;
     float* orr = fin_resp + lt.fin_off[l] + (size_t)f * fcap;
     if (listed) {
-        // rank sort inside the shared list: non-survivors get the sentinel key and never count
+        // survivors are first compacted to the front of the shared list (order does not matter), then
+        // every survivor ranks its (y, x) key against the survivors only: dense lanes, nf-long loops
         uint32_t mykey[kSortCap / kThreads];
-        int cnt = 0;
+        float myresp[kSortCap / kThreads];
+        int mypos[kSortCap / kThreads];
 #pragma unroll
         for (int t = 0; t < kSortCap / kThreads; ++t) {
             const int j = tid + t * kThreads;
-            mykey[t] = 0xffffffffu;
-            if (j < ns && float_key(sresp[j]) >= thr2) {
-                mykey[t] = c[skey[j]] & 0xffffffu;
-                ++cnt;
+            bool keep = false;
+            mykey[t] = 0;
+            myresp[t] = 0.f;
+            if (j < ns) {
+                myresp[t] = sresp[j];
+                keep = float_key(myresp[t]) >= thr2;
+                if (keep) mykey[t] = c[skey[j]] & 0xffffffu;
             }
+            // warp-aggregated append (uniform trip count: every lane runs all kSortCap / kThreads rounds)
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            int base = 0;
+            if (lane == 0 && m) base = atomicAdd(&s_nf, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            mypos[t] = keep ? base + __popc(m & ((1u << lane) - 1u)) : -1;
         }
-        __syncthreads();
+        __syncthreads();  // every slot has been read: the list can be overwritten
 #pragma unroll
-        for (int t = 0; t < kSortCap / kThreads; ++t) {
-            const int j = tid + t * kThreads;
-            if (j < ns) skey[j] = mykey[t];
-        }
-        cnt = __reduce_add_sync(0xffffffffu, cnt);
-        if (lane == 0 && cnt) atomicAdd(&s_nf, cnt);
+        for (int t = 0; t < kSortCap / kThreads; ++t)
+            if (mypos[t] >= 0) {
+                skey[mypos[t]] = mykey[t];
+                sresp[mypos[t]] = myresp[t];
+            }
         __syncthreads();
-#pragma unroll
-        for (int t = 0; t < kSortCap / kThreads; ++t) {
-            const int j = tid + t * kThreads;
-            const uint32_t k = mykey[t];
-            if (k != 0xffffffffu) {
-                int rank = 0;
-                for (int jj = 0; jj < ns; ++jj) rank += skey[jj] < k ? 1 : 0;
-                if (rank < fcap) {
-                    ok[rank] = k;
-                    orr[rank] = sresp[j];
-                }
+        const int nf = s_nf;
+        for (int i = tid; i < nf; i += kThreads) {
+            const uint32_t k = skey[i];
+            int rank = 0;
+#pragma unroll 8
+            for (int jj = 0; jj < nf; ++jj) rank += skey[jj] < k ? 1 : 0;
+            if (rank < fcap) {
+                ok[rank] = k;
+                orr[rank] = sresp[i];
             }
         }
     } else {
