@@ -225,9 +225,12 @@ int vxorb_keypoint_capacity(const vxorb_handle* h);
 void* vxorb_host_alloc(size_t bytes);
 void vxorb_host_free(void* p);
 
-/* Device-resident form used to time the kernels alone: frames already uploaded with
- * vxorb_resident_upload are re-processed by vxorb_resident_run (no host copies); results stay on
- * the device and can be fetched with vxorb_resident_fetch. */
+/* Device-resident form used to time the kernels alone: the chunk uploaded with
+ * vxorb_resident_upload is kept in every pipeline slot and re-processed by vxorb_resident_run (no host
+ * copies).  Consecutive runs take the slots in turn, as consecutive vxorb_track_submit calls do, so
+ * up to vxorb_track_slots(h) passes are in flight; every pass is the next chunk of the same sequence
+ * (its first frame is matched against the previous pass's last frame).  Results stay on the device;
+ * vxorb_resident_fetch returns those of the most recent pass. */
 int vxorb_resident_upload(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height,
                           size_t stride, size_t frame_stride);
 int vxorb_resident_run(vxorb_handle* h, float radius);

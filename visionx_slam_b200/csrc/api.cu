@@ -62,6 +62,7 @@ struct vxorb_handle {
     Workspace ws[kSlots];
     int next_slot = 0;
     int last_slot = -1;  // slot that processed the previous chunk; -1 after reset
+    int res_batch = 0, res_next = 0, res_last = -1;  // resident mode: frames per slot, next / last slot used
     // last frame of the previous chunk (query side of the next chunk's first pair)
     uint8_t* carry_desc = nullptr;
     float* carry_xy = nullptr;
@@ -262,6 +263,8 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
     h->geo_w = W;
     h->geo_h = H;
     h->last_slot = -1;
+    h->res_batch = 0;  // resident frames belong to the previous geometry
+    h->res_last = -1;
     return VXORB_OK;
 }
 
@@ -878,6 +881,20 @@ static int enqueue_carry_out(vxorb_handle* h, Workspace& ws, int batch) {
     return VXORB_OK;
 }
 
+// Extraction, carry and pair matching of one chunk whose level 0 is already in ws.  The carry leaves
+// as soon as the descriptors exist (the next chunk, on another slot, only needs this chunk's last
+// frame), so `done` is recorded before this chunk's own matching starts.
+static int enqueue_chunk(vxorb_handle* h, Workspace& ws, int batch, float radius) {
+    int rc = enqueue_extract(h, ws, batch);
+    if (rc) return rc;
+    rc = enqueue_carry_in(h, ws);
+    if (rc) return rc;
+    rc = enqueue_carry_out(h, ws, batch);
+    if (rc) return rc;
+    CK(cudaEventRecord(ws.done, ws.stream));  // descriptors and the carry of this chunk are final
+    return enqueue_track_match(h, ws, batch, radius);
+}
+
 int vxorb_track_submit(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height, size_t stride,
                        size_t frame_stride, float radius, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out,
                        int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out, int* slot_out) {
@@ -906,15 +923,8 @@ int vxorb_track_submit_info(vxorb_handle* h, const uint8_t* frames, int batch, i
     cudaStream_t s = ws.stream;
     rc = upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
     if (rc) return rc;
-    rc = enqueue_extract(h, ws, batch);
+    rc = enqueue_chunk(h, ws, batch, radius);
     if (rc) return rc;
-    rc = enqueue_carry_in(h, ws);
-    if (rc) return rc;
-    rc = enqueue_track_match(h, ws, batch, radius);
-    if (rc) return rc;
-    rc = enqueue_carry_out(h, ws, batch);
-    if (rc) return rc;
-    CK(cudaEventRecord(ws.done, s));  // descriptors, matches and the carry of this chunk are final
     if (info_out || pts_out) {
         rc = enqueue_frame_info(h, ws, batch, pts_out != nullptr);
         if (rc) return rc;
@@ -947,6 +957,10 @@ int vxorb_track_wait(vxorb_handle* h, int slot) {
     return check_status(h, ws.h_status[0]);
 }
 
+// Resident mode keeps the same chunk in every pipeline slot; consecutive vxorb_resident_run calls take
+// the slots in turn, exactly like consecutive vxorb_track_submit calls, so the kernels of up to kSlots
+// passes are in flight together (each pass still waits for its predecessor's last-frame descriptors
+// before its first pair is matched).  Nothing is copied from or to the host.
 int vxorb_resident_upload(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height, size_t stride,
                           size_t frame_stride) {
     if (!h) return VXORB_E_INVALID;
@@ -955,45 +969,49 @@ int vxorb_resident_upload(vxorb_handle* h, const uint8_t* frames, int batch, int
     CK(cudaSetDevice(h->p.device_id));
     int rc = ensure_geometry(h, width, height);
     if (rc) return rc;
-    Workspace& ws = h->ws[0];
-    if (ws.in_flight) return fail(h, VXORB_E_INVALID, "slot 0 in flight");
-    rc = upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
-    if (rc) return rc;
-    CK(cudaMemsetAsync(ws.db.kp_n, 0, sizeof(int), ws.stream));
-    CK(cudaStreamSynchronize(ws.stream));
-    ws.batch = batch;
+    for (auto& ws : h->ws)
+        if (ws.in_flight) return fail(h, VXORB_E_INVALID, "a pipeline slot is in flight");
+    for (auto& ws : h->ws) {
+        rc = upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
+        if (rc) return rc;
+        CK(cudaMemsetAsync(ws.db.kp_n, 0, sizeof(int), ws.stream));
+        CK(cudaStreamSynchronize(ws.stream));
+        ws.batch = batch;
+    }
+    h->res_batch = batch;
+    h->res_next = 0;
+    h->res_last = -1;
     h->last_slot = -1;
     return VXORB_OK;
 }
 
 int vxorb_resident_run(vxorb_handle* h, float radius) {
     if (!h) return VXORB_E_INVALID;
-    Workspace& ws = h->ws[0];
-    if (ws.batch < 1 || h->geo_w == 0) return fail(h, VXORB_E_INVALID, "no resident frames; call vxorb_resident_upload");
+    if (h->res_batch < 1 || h->geo_w == 0) return fail(h, VXORB_E_INVALID, "no resident frames; call vxorb_resident_upload");
     CK(cudaSetDevice(h->p.device_id));
-    int rc = enqueue_extract(h, ws, ws.batch);
+    // instrumented runs stay on slot 0 so that every stage's events sit on one stream, one pass at a time
+    const int slot = h->stage_enabled ? 0 : h->res_next;
+    Workspace& ws = h->ws[slot];
+    if (ws.in_flight) return fail(h, VXORB_E_INVALID, "slot busy with a track submit");
+    const int rc = enqueue_chunk(h, ws, h->res_batch, radius);
     if (rc) return rc;
-    rc = enqueue_track_match(h, ws, ws.batch, radius);
-    if (rc) return rc;
-    // the chunk's last frame becomes the carry of the next run, as in the streaming path
-    const size_t cap = (size_t)h->kp_cap;
-    CK(cudaMemcpyAsync(ws.db.desc, ws.db.desc + cap * 32 * ws.batch, cap * 32, cudaMemcpyDeviceToDevice, ws.stream));
-    CK(cudaMemcpyAsync(ws.db.xy, ws.db.xy + cap * 2 * ws.batch, cap * 8, cudaMemcpyDeviceToDevice, ws.stream));
-    CK(cudaMemcpyAsync(ws.db.kp_n, ws.db.kp_n + ws.batch, sizeof(int), cudaMemcpyDeviceToDevice, ws.stream));
+    h->last_slot = slot;
+    h->res_last = slot;
+    h->res_next = (slot + 1) % kSlots;
     return VXORB_OK;
 }
 
 int vxorb_resident_fetch(vxorb_handle* h, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_kp_out,
                          int match_cap, vxorb_match_t* match_out, int* n_match_out) {
     if (!h) return VXORB_E_INVALID;
-    Workspace& ws = h->ws[0];
-    if (ws.batch < 1) return fail(h, VXORB_E_INVALID, "no resident frames");
+    if (h->res_batch < 1 || h->res_last < 0) return fail(h, VXORB_E_INVALID, "no resident pass to fetch");
+    Workspace& ws = h->ws[h->res_last];
     if ((kp_out || desc_out) && kp_cap != h->kp_cap) return fail(h, VXORB_E_INVALID, "kp_cap must equal max_keypoints");
     if (match_out && match_cap != h->kp_cap) return fail(h, VXORB_E_INVALID, "match_cap must equal max_keypoints");
     CK(cudaSetDevice(h->p.device_id));
     cudaStream_t s = ws.stream;
     const size_t cap = (size_t)h->kp_cap;
-    const int batch = ws.batch;
+    const int batch = h->res_batch;
     int status[4] = {0, 0, 0, 0};
     if (kp_out) CK(cudaMemcpyAsync(kp_out, ws.db.kp + cap, sizeof(vxorb_keypoint) * cap * batch, cudaMemcpyDeviceToHost, s));
     if (desc_out) CK(cudaMemcpyAsync(desc_out, ws.db.desc + cap * 32, 32 * cap * batch, cudaMemcpyDeviceToHost, s));
