@@ -86,6 +86,8 @@ struct vxorb_handle {
     float stage_ms[VXORB_STAGE_COUNT] = {0};
     int stage_launches[VXORB_STAGE_COUNT] = {0};
     long long launches = 0;
+    uint8_t* x_stage = nullptr;  // pinned staging block of the synchronous extract calls
+    size_t x_bytes = 0;
     uint8_t* flush_buf = nullptr;
     size_t flush_bytes = 0;
 };
@@ -639,6 +641,7 @@ void vxorb_destroy(vxorb_handle* h) {
     cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);
     cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n);
     cudaFree(h->s_a); cudaFree(h->s_b); cudaFree(h->flush_buf);
+    if (h->x_stage) cudaFreeHost(h->x_stage);
     for (auto& sp : h->spans) {
         cudaEventDestroy(sp.a);
         cudaEventDestroy(sp.b);
@@ -703,25 +706,47 @@ static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const u
         if (rc) return rc;
         CK(cudaMemcpyAsync(info_out, ws.info, sizeof(vxorb_frame_info) * batch, cudaMemcpyDeviceToHost, ws.stream));
     }
-    std::vector<int> counts((size_t)batch * 2 + 4);
-    CK(cudaMemcpyAsync(counts.data(), ws.db.kp_n + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
-    CK(cudaMemcpyAsync(counts.data() + batch, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
-    CK(cudaMemcpyAsync(counts.data() + 2 * batch, ws.db.status, sizeof(int) * 4, cudaMemcpyDeviceToHost, ws.stream));
+    // One round trip: counts, status and the first min(kp_cap, capacity) rows of every frame land in the
+    // handle's pinned staging block, one synchronisation, then the exact row counts are copied out on the host.
+    const int rows = std::min(kp_cap, h->kp_cap);
+    const size_t n_ints = (size_t)batch * 2 + 4;
+    const size_t kp_off = align_up(n_ints * sizeof(int), 64);
+    const size_t desc_off = kp_off + align_up(sizeof(vxorb_keypoint) * (size_t)rows * batch, 64);
+    const size_t need = desc_off + (size_t)32 * rows * batch;
+    if (need > h->x_bytes) {
+        if (h->x_stage) cudaFreeHost(h->x_stage);
+        h->x_stage = nullptr;
+        h->x_bytes = 0;
+        if (cudaHostAlloc(reinterpret_cast<void**>(&h->x_stage), need, cudaHostAllocDefault) != cudaSuccess)
+            return fail(h, VXORB_E_NOMEM, "pinned staging allocation failed");
+        h->x_bytes = need;
+    }
+    int* counts = reinterpret_cast<int*>(h->x_stage);
+    vxorb_keypoint* st_kp = reinterpret_cast<vxorb_keypoint*>(h->x_stage + kp_off);
+    uint8_t* st_desc = h->x_stage + desc_off;
+    CK(cudaMemcpyAsync(counts, ws.db.kp_n + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
+    CK(cudaMemcpyAsync(counts + batch, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
+    CK(cudaMemcpyAsync(counts + 2 * batch, ws.db.status, sizeof(int) * 4, cudaMemcpyDeviceToHost, ws.stream));
+    if (rows > 0) {
+        // frame f's rows sit at slot f + 1 with stride h->kp_cap on the device, stride `rows` in the staging block
+        CK(cudaMemcpy2DAsync(st_kp, sizeof(vxorb_keypoint) * (size_t)rows, ws.db.kp + h->kp_cap,
+                             sizeof(vxorb_keypoint) * (size_t)h->kp_cap, sizeof(vxorb_keypoint) * (size_t)rows, batch,
+                             cudaMemcpyDeviceToHost, ws.stream));
+        CK(cudaMemcpy2DAsync(st_desc, (size_t)32 * rows, ws.db.desc + (size_t)h->kp_cap * 32, (size_t)32 * h->kp_cap,
+                             (size_t)32 * rows, batch, cudaMemcpyDeviceToHost, ws.stream));
+    }
     CK(cudaStreamSynchronize(ws.stream));
     bool truncated = false;
     for (int f = 0; f < batch; ++f) {
         const int n = counts[f], total = counts[batch + f];
         n_out[f] = total;
-        const int m = std::min(n, kp_cap);
+        const int m = std::min(n, rows);
         if (total > m) truncated = true;
         if (m > 0) {
-            CK(cudaMemcpyAsync(kp_out + (size_t)f * kp_cap, ws.db.kp + (size_t)(f + 1) * h->kp_cap,
-                               sizeof(vxorb_keypoint) * m, cudaMemcpyDeviceToHost, ws.stream));
-            CK(cudaMemcpyAsync(desc_out + (size_t)f * kp_cap * 32, ws.db.desc + (size_t)(f + 1) * h->kp_cap * 32,
-                               (size_t)m * 32, cudaMemcpyDeviceToHost, ws.stream));
+            memcpy(kp_out + (size_t)f * kp_cap, st_kp + (size_t)f * rows, sizeof(vxorb_keypoint) * (size_t)m);
+            memcpy(desc_out + (size_t)f * kp_cap * 32, st_desc + (size_t)f * rows * 32, (size_t)m * 32);
         }
     }
-    CK(cudaStreamSynchronize(ws.stream));
     h->last_slot = -1;  // the synchronous extract calls do not take part in a tracked sequence
     const int status = counts[2 * batch];
     if (status & 3) return check_status(h, status);
