@@ -450,6 +450,18 @@ int ensure_match_scratch(vxorb_handle* h, int rows) {
     return VXORB_OK;
 }
 
+// Grows the handle's pinned host staging block (shared by the synchronous extract and match calls).
+int ensure_host_stage(vxorb_handle* h, size_t need) {
+    if (need <= h->x_bytes) return VXORB_OK;
+    if (h->x_stage) cudaFreeHost(h->x_stage);
+    h->x_stage = nullptr;
+    h->x_bytes = 0;
+    if (cudaHostAlloc(reinterpret_cast<void**>(&h->x_stage), need, cudaHostAllocDefault) != cudaSuccess)
+        return fail(h, VXORB_E_NOMEM, "pinned staging allocation failed");
+    h->x_bytes = need;
+    return VXORB_OK;
+}
+
 // Host-buffer knn: uploads both descriptor sets and runs the knn kernel into m_knn (and, for the
 // cross-check, the reverse direction into m_back).
 int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy,
@@ -460,15 +472,36 @@ int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, co
     int rc = ensure_match_scratch(h, std::max(std::max(nq, nt), 1));
     if (rc) return rc;
     cudaStream_t s = h->ws[0].stream;
-    const int n[2] = {nq, nt};
-    CK(cudaMemcpyAsync(h->m_n, n, sizeof(n), cudaMemcpyHostToDevice, s));
-    if (nq) CK(cudaMemcpyAsync(h->m_q, q, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
-    if (nt) CK(cudaMemcpyAsync(h->m_t, t, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
     const bool win = (radius > 0.f || box) && qxy && txy;
     if (box && !win) return fail(h, VXORB_E_INVALID, "box mask needs query and train positions");
+    // inputs go through the pinned staging block (pageable sources would make every copy a blocking one);
+    // the block is also large enough for the outputs the callers stage afterwards
+    const size_t q_off = 64, t_off = q_off + (size_t)nq * 32, qxy_off = t_off + (size_t)nt * 32;
+    const size_t txy_off = qxy_off + (size_t)nq * 8, in_end = txy_off + (size_t)nt * 8;
+    rc = ensure_host_stage(h, std::max(in_end, (size_t)64 + (size_t)nq * 16));
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(s));  // the block may still feed an earlier call's copies
+    int* n_st = reinterpret_cast<int*>(h->x_stage);
+    n_st[0] = nq;
+    n_st[1] = nt;
+    CK(cudaMemcpyAsync(h->m_n, n_st, 2 * sizeof(int), cudaMemcpyHostToDevice, s));
+    if (nq) {
+        memcpy(h->x_stage + q_off, q, (size_t)nq * 32);
+        CK(cudaMemcpyAsync(h->m_q, h->x_stage + q_off, (size_t)nq * 32, cudaMemcpyHostToDevice, s));
+    }
+    if (nt) {
+        memcpy(h->x_stage + t_off, t, (size_t)nt * 32);
+        CK(cudaMemcpyAsync(h->m_t, h->x_stage + t_off, (size_t)nt * 32, cudaMemcpyHostToDevice, s));
+    }
     if (win) {
-        if (nq) CK(cudaMemcpyAsync(h->m_qxy, qxy, (size_t)nq * 8, cudaMemcpyHostToDevice, s));
-        if (nt) CK(cudaMemcpyAsync(h->m_txy, txy, (size_t)nt * 8, cudaMemcpyHostToDevice, s));
+        if (nq) {
+            memcpy(h->x_stage + qxy_off, qxy, (size_t)nq * 8);
+            CK(cudaMemcpyAsync(h->m_qxy, h->x_stage + qxy_off, (size_t)nq * 8, cudaMemcpyHostToDevice, s));
+        }
+        if (nt) {
+            memcpy(h->x_stage + txy_off, txy, (size_t)nt * 8);
+            CK(cudaMemcpyAsync(h->m_txy, h->x_stage + txy_off, (size_t)nt * 8, cudaMemcpyHostToDevice, s));
+        }
     }
     StageScope sc(h, s, VXORB_STAGE_MATCH);
     MatchArgs a;
@@ -512,15 +545,20 @@ int run_match_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, 
                                         h->m_out, h->m_cap, h->m_out_n, s);
     h->stage_launches[VXORB_STAGE_MATCH] += 1;
     CK(cudaGetLastError());
-    int n = 0;
-    CK(cudaMemcpyAsync(&n, h->m_out_n, sizeof(int), cudaMemcpyDeviceToHost, s));
+    // one round trip: the count and the first min(out_cap, nq) rows go to the pinned staging block together
+    const int rows = std::min(out_cap, nq);
+    const size_t need = 64 + sizeof(vxorb_match_t) * (size_t)rows;
+    rc = ensure_host_stage(h, need);
+    if (rc) return rc;
+    int* n_st = reinterpret_cast<int*>(h->x_stage);
+    vxorb_match_t* out_st = reinterpret_cast<vxorb_match_t*>(h->x_stage + 64);
+    CK(cudaMemcpyAsync(n_st, h->m_out_n, sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (rows > 0) CK(cudaMemcpyAsync(out_st, h->m_out, sizeof(vxorb_match_t) * (size_t)rows, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
+    const int n = *n_st;
     *n_out = n;
-    const int m = std::min(n, out_cap);
-    if (m > 0) {
-        CK(cudaMemcpyAsync(out, h->m_out, sizeof(vxorb_match_t) * (size_t)m, cudaMemcpyDeviceToHost, s));
-        CK(cudaStreamSynchronize(s));
-    }
+    const int m = std::min(n, rows);
+    if (m > 0) memcpy(out, out_st, sizeof(vxorb_match_t) * (size_t)m);
     if (n > out_cap) return fail(h, VXORB_E_CAPACITY, "match output buffer too small");
     return VXORB_OK;
 }
@@ -713,14 +751,8 @@ static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const u
     const size_t kp_off = align_up(n_ints * sizeof(int), 64);
     const size_t desc_off = kp_off + align_up(sizeof(vxorb_keypoint) * (size_t)rows * batch, 64);
     const size_t need = desc_off + (size_t)32 * rows * batch;
-    if (need > h->x_bytes) {
-        if (h->x_stage) cudaFreeHost(h->x_stage);
-        h->x_stage = nullptr;
-        h->x_bytes = 0;
-        if (cudaHostAlloc(reinterpret_cast<void**>(&h->x_stage), need, cudaHostAllocDefault) != cudaSuccess)
-            return fail(h, VXORB_E_NOMEM, "pinned staging allocation failed");
-        h->x_bytes = need;
-    }
+    rc = ensure_host_stage(h, need);
+    if (rc) return rc;
     int* counts = reinterpret_cast<int*>(h->x_stage);
     vxorb_keypoint* st_kp = reinterpret_cast<vxorb_keypoint*>(h->x_stage + kp_off);
     uint8_t* st_desc = h->x_stage + desc_off;
