@@ -73,6 +73,7 @@ struct vxorb_handle {
     int* m_n = nullptr;  // [0] = nq, [1] = nt
     vxorb_knn2_t *m_knn = nullptr, *m_back = nullptr;
     vxorb_match_t* m_out = nullptr;
+    uint2* m_part = nullptr;  // per-split partial top-2 keys of the single-pair brute-force launch
     int* m_out_n = nullptr;
     int m_cap = 0;
     // single-image stage scratch
@@ -434,7 +435,8 @@ int check_status(vxorb_handle* h, int status) {
 int ensure_match_scratch(vxorb_handle* h, int rows) {
     if (rows <= h->m_cap) return VXORB_OK;
     cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);
-    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n);
+    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n); cudaFree(h->m_part);
+    h->m_part = nullptr;
     h->m_cap = 0;
     const size_t r = (size_t)rows;
     CK(cudaMalloc(&h->m_q, r * 32));
@@ -446,6 +448,7 @@ int ensure_match_scratch(vxorb_handle* h, int rows) {
     CK(cudaMalloc(&h->m_back, sizeof(vxorb_knn2_t) * r));
     CK(cudaMalloc(&h->m_out, sizeof(vxorb_match_t) * r));
     CK(cudaMalloc(&h->m_out_n, sizeof(int) * 4));
+    CK(cudaMalloc(&h->m_part, sizeof(uint2) * r * kMaxTrainSplits));
     h->m_cap = rows;
     return VXORB_OK;
 }
@@ -511,6 +514,7 @@ int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, co
     a.q_pair_stride = a.t_pair_stride = 0;
     a.max_q = nq; a.max_t = nt; a.pairs = 1; a.radius = win ? radius : 0.f;
     a.knn = h->m_knn; a.knn_stride = 0;
+    a.part = h->m_part;
     if (box) {
         a.boxed = 1;
         for (int i = 0; i < 4; ++i) a.box[i] = box[i];
@@ -677,7 +681,7 @@ void vxorb_destroy(vxorb_handle* h) {
         if (w.h_status) cudaFreeHost(w.h_status);
     }
     cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);
-    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n);
+    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n); cudaFree(h->m_part);
     cudaFree(h->s_a); cudaFree(h->s_b); cudaFree(h->flush_buf);
     if (h->x_stage) cudaFreeHost(h->x_stage);
     for (auto& sp : h->spans) {

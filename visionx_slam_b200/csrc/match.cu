@@ -58,8 +58,13 @@ knn2_kernel(const MatchArgs a) {
     }
 
     uint32_t k0 = kNoKey, k1 = kNoKey;
-    for (int t0 = 0; t0 < nt; t0 += kTrainTile) {
-        const int tn = min(kTrainTile, nt - t0);
+    // this CTA's share of the train rows (whole tiles; the last split takes the remainder)
+    const int tiles_all = (nt + kTrainTile - 1) / kTrainTile;
+    const int tiles_per = (tiles_all + a.splits - 1) / a.splits;
+    const int t_begin = min(nt, (int)blockIdx.z * tiles_per * kTrainTile);
+    const int t_end = min(nt, t_begin + tiles_per * kTrainTile);
+    for (int t0 = t_begin; t0 < t_end; t0 += kTrainTile) {
+        const int tn = min(kTrainTile, t_end - t0);
         __syncthreads();
         for (int i = threadIdx.x; i < tn * 2; i += kQPerBlock)
             reinterpret_cast<uint4*>(&tdesc[0][0])[i] =
@@ -96,7 +101,9 @@ knn2_kernel(const MatchArgs a) {
             }
         }
     }
-    if (live) {
+    if (live && a.splits > 1) {
+        a.part[((size_t)pair * a.splits + blockIdx.z) * a.max_q + qi] = make_uint2(k0, k1);
+    } else if (live) {
         vxorb_knn2_t r;
         r.idx[0] = k0 == kNoKey ? -1 : (int)(k0 & 0xfffffu);
         r.idx[1] = k1 == kNoKey ? -1 : (int)(k1 & 0xfffffu);
@@ -104,6 +111,26 @@ knn2_kernel(const MatchArgs a) {
         r.dist[1] = k1 == kNoKey ? 0 : (int)(k1 >> 20);
         reinterpret_cast<int4*>(a.knn + (size_t)pair * a.knn_stride)[qi] = make_int4(r.idx[0], r.idx[1], r.dist[0], r.dist[1]);
     }
+}
+
+// Folds the per-split packed top-2 keys of the split brute-force launch into the final 2-NN rows.  The
+// keys carry the global train index, so the two smallest over all splits are the two nearest
+// neighbours with OpenCV's lowest-index tie-break.
+__global__ void __launch_bounds__(256)
+knn2_merge_kernel(const MatchArgs a) {
+    const int pair = blockIdx.y;
+    const int qi = blockIdx.x * 256 + threadIdx.x;
+    if (qi >= a.q_n[pair]) return;
+    uint32_t k0 = kNoKey, k1 = kNoKey;
+    for (int sp = 0; sp < a.splits; ++sp) {
+        const uint2 p = a.part[((size_t)pair * a.splits + sp) * a.max_q + qi];
+        k1 = min(k1, max(k0, p.x));
+        k0 = min(k0, p.x);
+        k1 = min(k1, p.y);  // p.y >= p.x: it can only displace the second entry
+    }
+    reinterpret_cast<int4*>(a.knn + (size_t)pair * a.knn_stride)[qi] =
+        make_int4(k0 == kNoKey ? -1 : (int)(k0 & 0xfffffu), k1 == kNoKey ? -1 : (int)(k1 & 0xfffffu),
+                  k0 == kNoKey ? 0 : (int)(k0 >> 20), k1 == kNoKey ? 0 : (int)(k1 >> 20));
 }
 
 // ---- windowed 2-NN over a uniform cell grid ------------------------------------------------------
@@ -400,9 +427,26 @@ int launch_knn2(const MatchArgs& a, cudaStream_t s) {
         knn2_window_kernel<<<a.pairs, kWinThreads, window_smem_bytes(a.max_t, a.max_q), s>>>(a, a.max_t, a.max_q);
         return 1;
     }
-    dim3 grid((a.max_q + kQPerBlock - 1) / kQPerBlock, a.pairs);
-    knn2_kernel<<<grid, kQPerBlock, 0, s>>>(a);
-    return 1;
+    // few pairs: split the train rows over gridDim.z so that the launch still covers the GPU (two CTAs of
+    // 4 warps per SM at least), then merge the partial top-2 keys
+    MatchArgs b = a;
+    const int qblocks = (a.max_q + kQPerBlock - 1) / kQPerBlock;
+    const int tiles = (a.max_t + kTrainTile - 1) / kTrainTile;
+    int splits = 1;
+    if (a.part && a.max_t > 0) {
+        splits = (2 * 148 + qblocks * a.pairs - 1) / (qblocks * a.pairs);
+        splits = splits < 1 ? 1 : splits;
+        splits = splits > tiles ? tiles : splits;
+        splits = splits > kMaxTrainSplits ? kMaxTrainSplits : splits;
+        splits = splits < 1 ? 1 : splits;
+    }
+    b.splits = splits;
+    dim3 grid(qblocks, a.pairs, splits);
+    knn2_kernel<<<grid, kQPerBlock, 0, s>>>(b);
+    if (splits == 1) return 1;
+    dim3 mgrid((a.max_q + 255) / 256, a.pairs);
+    knn2_merge_kernel<<<mgrid, 256, 0, s>>>(b);
+    return 2;
 }
 
 int launch_match_compact(const vxorb_knn2_t* knn, const vxorb_knn2_t* back, int knn_stride, int back_stride,

@@ -136,7 +136,12 @@ struct MatchArgs {
     float box[4] = {0.f, 0.f, 0.f, 0.f};
     vxorb_knn2_t* knn;                              // [pair][knn_stride]
     int knn_stride;
+    // brute-force path with few pairs: the train set is split over gridDim.z CTAs per query block, each
+    // writing its packed top-2 keys to part[(pair * splits + split) * max_q + query]; a merge pass folds them
+    uint2* part = nullptr;                          // scratch for >= pairs * kMaxTrainSplits * max_q entries, or nullptr
+    int splits = 1;                                 // set by launch_knn2
 };
+constexpr int kMaxTrainSplits = 32;
 int launch_knn2(const MatchArgs& a, cudaStream_t s);
 // mode 0: ratio test; mode 1: ratio test + caller's post-filter; mode 2: cross-check with `back`
 int launch_match_compact(const vxorb_knn2_t* knn, const vxorb_knn2_t* back, int knn_stride, int back_stride,
