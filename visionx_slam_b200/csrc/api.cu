@@ -22,7 +22,10 @@ using namespace vxorb;
 
 namespace {
 
-constexpr int kSlots = 3;
+#ifndef VXORB_SLOTS
+#define VXORB_SLOTS 3
+#endif
+constexpr int kSlots = VXORB_SLOTS;
 std::string g_create_error = "";
 std::mutex g_create_mutex;
 
