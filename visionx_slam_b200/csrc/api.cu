@@ -90,6 +90,11 @@ struct vxorb_handle {
     float stage_ms[VXORB_STAGE_COUNT] = {0};
     int stage_launches[VXORB_STAGE_COUNT] = {0};
     long long launches = 0;
+    // single-frame extraction (the per-frame call of the reference's front end) is launch bound: its 14
+    // launches, the two memsets and the side-stream fork/join are captured once per geometry into a CUDA
+    // graph on slot 0 and replayed
+    cudaGraphExec_t x_graph = nullptr;
+    int x_graph_launches = 0;
     uint8_t* x_stage = nullptr;  // pinned staging block of the synchronous extract calls
     size_t x_bytes = 0;
     uint8_t* flush_buf = nullptr;
@@ -147,6 +152,8 @@ void free_workspace(Workspace& w) {
 }
 
 void free_geometry(vxorb_handle* h) {
+    if (h->x_graph) cudaGraphExecDestroy(h->x_graph);  // its nodes point into the buffers freed below
+    h->x_graph = nullptr;
     for (auto& w : h->ws) free_workspace(w);
     cudaFree(h->d_coef);
     cudaFree(h->carry_desc);
@@ -364,6 +371,36 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
         sc.end(n);
     }
     CK(cudaGetLastError());
+    return VXORB_OK;
+}
+
+// Single-frame extraction on slot 0 through a CUDA graph (captured on first use for the current geometry).
+int launch_extract_graph(vxorb_handle* h, Workspace& ws) {
+    if (!h->x_graph) {
+        const long long before = h->launches;
+        int stage_before[VXORB_STAGE_COUNT];
+        for (int i = 0; i < VXORB_STAGE_COUNT; ++i) stage_before[i] = h->stage_launches[i];
+        CK(cudaStreamBeginCapture(ws.stream, cudaStreamCaptureModeThreadLocal));
+        const int rc = enqueue_extract(h, ws, 1);
+        cudaGraph_t graph = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(ws.stream, &graph);
+        if (rc) {
+            if (graph) cudaGraphDestroy(graph);
+            return rc;
+        }
+        if (e != cudaSuccess || !graph) return fail(h, VXORB_E_CUDA, std::string("graph capture: ") + cudaGetErrorString(e));
+        const cudaError_t ei = cudaGraphInstantiate(&h->x_graph, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ei != cudaSuccess) {
+            h->x_graph = nullptr;
+            return fail(h, VXORB_E_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(ei));
+        }
+        h->x_graph_launches = (int)(h->launches - before);
+        h->launches = before;  // nothing ran during the capture; every replay below counts its kernels
+        for (int i = 0; i < VXORB_STAGE_COUNT; ++i) h->stage_launches[i] = stage_before[i];
+    }
+    CK(cudaGraphLaunch(h->x_graph, ws.stream));
+    h->launches += h->x_graph_launches;
     return VXORB_OK;
 }
 
@@ -743,7 +780,11 @@ static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const u
                                  cudaMemcpyHostToDevice, ws.stream));
         }
     }
-    rc = enqueue_extract(h, ws, batch);
+    if (batch == 1 && !h->stage_enabled && !getenv("VXORB_NO_GRAPH")) {
+        rc = launch_extract_graph(h, ws);
+    } else {
+        rc = enqueue_extract(h, ws, batch);
+    }
     if (rc) return rc;
     if (info_out) {  // no pairs here: zero match counts, then statistics + grid coverage of every frame
         CK(cudaMemsetAsync(ws.db.match_n, 0, sizeof(int) * batch, ws.stream));
