@@ -49,6 +49,7 @@ struct Workspace {
     unsigned long long* sums = nullptr;   // [max_batch][2]
     vxorb_frame_info* info = nullptr;     // [max_batch]
     float4* pts = nullptr;                // [max_batch][kp_cap]
+    uint8_t* stage_in = nullptr;          // [max_batch][H][W] densely packed upload staging
 };
 
 }  // namespace
@@ -146,8 +147,8 @@ void free_workspace(Workspace& w) {
     cudaFree(d.fin_key); cudaFree(d.fin_resp); cudaFree(d.fin_n); cudaFree(d.kp); cudaFree(d.desc);
     cudaFree(d.xy); cudaFree(d.kp_n); cudaFree(d.kp_total); cudaFree(d.knn); cudaFree(d.match);
     cudaFree(d.match_n); cudaFree(d.status);
-    cudaFree(w.sums); cudaFree(w.info); cudaFree(w.pts);
-    w.sums = nullptr; w.info = nullptr; w.pts = nullptr;
+    cudaFree(w.sums); cudaFree(w.info); cudaFree(w.pts); cudaFree(w.stage_in);
+    w.sums = nullptr; w.info = nullptr; w.pts = nullptr; w.stage_in = nullptr;
     d = DeviceBuffers();
 }
 
@@ -272,6 +273,7 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
         CK(cudaMalloc(&w.sums, sizeof(unsigned long long) * 2 * B));
         CK(cudaMalloc(&w.info, sizeof(vxorb_frame_info) * B));
         CK(cudaMalloc(&w.pts, sizeof(float4) * cap * B));
+        CK(cudaMalloc(&w.stage_in, (size_t)W * H * B));
     }
     h->geo_w = W;
     h->geo_h = H;
@@ -447,6 +449,14 @@ int upload_frames(vxorb_handle* h, Workspace& ws, const uint8_t* frames, int bat
                   size_t frame_stride) {
     const LevelTab& lt = h->lt;
     uint8_t* dst = ws.db.pyr + lt.off[0];
+    if (batch > 1 && stride == (size_t)W && frame_stride == (size_t)W * H && W % 16 == 0 && ws.stage_in &&
+        !getenv("VXORB_NO_FLAT_UPLOAD")) {
+        // densely packed chunk: one flat copy over the link, rows scattered into the planes on the device
+        CK(cudaMemcpyAsync(ws.stage_in, frames, (size_t)W * H * batch, cudaMemcpyHostToDevice, ws.stream));
+        h->launches += launch_unpack_frames(ws.stage_in, dst, W, H, lt.pitch[0], (size_t)lt.fstride[0], batch, ws.stream);
+        h->stage_launches[VXORB_STAGE_PYRAMID] += 1;
+        return VXORB_OK;
+    }
     if (stride > 0 && frame_stride % stride == 0 && frame_stride / stride >= (size_t)H) {
         // one strided 3-D copy: frame f, row y of the source -> plane f, row y (planes carry an apron)
         cudaMemcpy3DParms p;

@@ -371,6 +371,27 @@ static void launch_resize(const uint8_t* src, int sw, int sh, int spitch, size_t
     }
 }
 
+// Densely packed frames (row stride = width) -> level-0 planes.  The streaming path moves a chunk over
+// PCIe as ONE flat copy into a staging buffer (a strided 3-D copy of 640-byte rows reaches ~2 % less
+// of the link) and this kernel scatters the rows into the pitched, aproned planes: 16 B per thread.
+__global__ void __launch_bounds__(256)
+unpack_frames_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int w16, int h, int pitch,
+                     size_t fstride) {
+    const int i = blockIdx.x * 256 + threadIdx.x;  // 16-byte chunk within the frame
+    if (i >= w16 * h) return;
+    const int y = i / w16, c = i - y * w16;
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + (size_t)blockIdx.y * ((size_t)w16 * 16 * h)) + i);
+    *reinterpret_cast<uint4*>(dst + (size_t)blockIdx.y * fstride + (size_t)y * pitch + (size_t)c * 16) = v;
+}
+
+int launch_unpack_frames(const uint8_t* src, uint8_t* dst, int w, int h, int pitch, size_t fstride, int batch,
+                         cudaStream_t s) {
+    const int w16 = w / 16;
+    dim3 grid((w16 * h + 255) / 256, batch);
+    unpack_frames_kernel<<<grid, 256, 0, s>>>(src, dst, w16, h, pitch, fstride);
+    return 1;
+}
+
 int launch_gray_from_bgr(const uint8_t* bgr, size_t bgr_pitch, size_t bgr_fstride, uint8_t* dst, int w,
                          int h, int pitch, size_t fstride, int batch, cudaStream_t s) {
     dim3 block(32, 8), grid((w + 127) / 128, (h + 7) / 8, batch);
