@@ -299,38 +299,54 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
         const uint32_t sel01 = sx.x & 0xffffu, sel23 = sx.x >> 16;
         const int wofs = (int)(sx.y & 0xffffu);
         const uint32_t shift = sx.y >> 16;
-        for (int y = y_begin + warp; y < y_end; y += 8) {
-            const uint32_t ty = __ldg(ytab + y);
-            const int j0 = (int)(ty & 0xffffu);
-            const uint32_t cy1 = ty >> 16, cy0 = 256u - cy1;
-            const int j1 = min(j0 + 1, sh - 1);
-            const uint32_t* p0 = sm_w + (j0 - jlo) * spitch_w + wofs;
-            const uint32_t* p1 = sm_w + (j1 - jlo) * spitch_w + wofs;
-            uint32_t h0[4], h1[4];
-            {
-                const uint32_t w0 = p0[0], w1 = p0[1], w2 = p0[2];
-                const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
-                const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
-                h0[0] = __dp2a_lo(wg.x, b01, 0u);
-                h0[1] = __dp2a_hi(wg.y, b01, 0u);
-                h0[2] = __dp2a_lo(wg.z, b23, 0u);
-                h0[3] = __dp2a_hi(wg.w, b23, 0u);
-            }
-            {
-                const uint32_t w0 = p1[0], w1 = p1[1], w2 = p1[2];
-                const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
-                const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
-                h1[0] = __dp2a_lo(wg.x, b01, 0u);
-                h1[1] = __dp2a_hi(wg.y, b01, 0u);
-                h1[2] = __dp2a_lo(wg.z, b23, 0u);
-                h1[3] = __dp2a_hi(wg.w, b23, 0u);
-            }
+        // horizontal pass of one source row for this lane's output word: 4 x (p0 * c0 + p1 * c1), 8.8 fixed point
+        auto hpass = [&](int j, uint32_t (&hv)[4]) {
+            const uint32_t* p = sm_w + (j - jlo) * spitch_w + wofs;
+            const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+            const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
+            const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
+            hv[0] = __dp2a_lo(wg.x, b01, 0u);
+            hv[1] = __dp2a_hi(wg.y, b01, 0u);
+            hv[2] = __dp2a_lo(wg.z, b23, 0u);
+            hv[3] = __dp2a_hi(wg.w, b23, 0u);
+        };
+        auto vpass_store = [&](int y, const uint32_t (&h0)[4], const uint32_t (&h1)[4], uint32_t cy1) {
+            const uint32_t cy0 = 256u - cy1;
             uint32_t v[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) v[j] = h1[j] * cy1 + (h0[j] * cy0 + (1u << 15));  // 16.16, byte 2 = result
             if (active)
                 *reinterpret_cast<uint32_t*>(dst + (size_t)y * dpitch + 4 * k) =
                     __byte_perm(__byte_perm(v[0], v[1], 0x0062u), __byte_perm(v[2], v[3], 0x0062u), 0x5410u);
+        };
+        // a warp takes PAIRS of consecutive output rows: at scale 1.2 the second row's upper source row is
+        // the first row's lower one five times out of six, so its horizontal pass is reused
+        for (int y = y_begin + 2 * warp; y < y_end; y += 16) {
+            const uint32_t ty = __ldg(ytab + y);
+            const int j0 = (int)(ty & 0xffffu);
+            const int j1 = min(j0 + 1, sh - 1);
+            uint32_t ha[4], hb[4];
+            hpass(j0, ha);
+            hpass(j1, hb);
+            vpass_store(y, ha, hb, ty >> 16);
+            if (y + 1 < y_end) {
+                const uint32_t tz = __ldg(ytab + y + 1);
+                const int i0 = (int)(tz & 0xffffu);
+                const int i1 = min(i0 + 1, sh - 1);
+                uint32_t hc[4];
+                if (i0 == j1) {          // warp-uniform: depends on the row only
+                    if (i1 == i0) {      // clamped at the last source row
+                        vpass_store(y + 1, hb, hb, tz >> 16);
+                    } else {
+                        hpass(i1, hc);
+                        vpass_store(y + 1, hb, hc, tz >> 16);
+                    }
+                } else {
+                    hpass(i0, ha);
+                    hpass(i1, hc);
+                    vpass_store(y + 1, ha, hc, tz >> 16);
+                }
+            }
         }
     }
     __syncthreads();  // the band's pixels are visible to this CTA
