@@ -107,6 +107,18 @@ def test_extract_large_shapes(name):
         assert np.array_equal(desc, g["desc"])
 
 
+@pytest.mark.parametrize("w,hh,n", [(3840, 2160, 8000), (4095, 3071, 20000)])
+def test_extract_4k_vs_oracle(w, hh, n):
+    """Maximum sizes: 4K frames with per-level quotas far above the in-shared-memory sort capacity."""
+    img = synth_scene(w, hh, 5)
+    with vx.VxOrb(n_features=n, max_width=w, max_height=hh, max_batch=1, max_keypoints=n + n // 2) as hx:
+        kp, desc = hx.extract(img)
+    okp, odesc = oracle.orb_extract(img, n)
+    assert len(okp) == n
+    assert_kp_equal(kp, okp)
+    assert np.array_equal(desc, odesc)
+
+
 @pytest.mark.parametrize("name", ["grid", "noise", "blank", "tiny60", "small80x70", "lowtex", "odd_357x291"])
 def test_extract_adversarial(h, golden_adv, name):
     g = golden_adv
