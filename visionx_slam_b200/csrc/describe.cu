@@ -11,7 +11,7 @@
 // 4 (orientation) / 3 (descriptor) windows deep per warp, so the windows of the next keypoints are
 // in flight while keypoint i is processed.  (TMA boxes were measured first: at 31-37 rows of 48-64 B
 // per box the TMA unit's per-row rate, ~5 cycles/row/SM, became the limiter.)
-//   orientation  31 rows x 48 B of the un-blurred level.  lane = patch row v; nine LDS words, a
+//   orientation  31 rows x 48 B of the un-blurred level.  lane = patch row v; three LDS.128, a
 //                funnel shift to the patch origin, then IDP.4A does the work:
 //                m10 += dp4a(pixels, u-weights), rowsum += dp4a(pixels, mask), m01 += v*rowsum;
 //                two REDUX adds per keypoint
@@ -24,6 +24,8 @@
 //                gathers per lane are LDS.U8 instead of scattered global loads
 // Float rules are load-bearing: every op is an explicit *_rn intrinsic so nvcc cannot contract.
 #include <float.h>
+
+#include <type_traits>
 
 #include "vxorb_internal.h"
 
@@ -106,10 +108,8 @@ __device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
     asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
 }
-__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
-    uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
-    return v;
+__device__ __forceinline__ void lds_v4(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr));
 }
 
 }  // namespace
@@ -230,19 +230,31 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
         const int kx = __shfl_sync(0xffffffffu, x, i);
         const uint32_t off = (uint32_t)(kx - 15) & 15u;
         const uint32_t sh = (off & 3u) * 8u;
-        const uint32_t rw = win0 + slot * kPaStride + my_row + (off & ~3u);
+        const uint32_t rw = win0 + slot * kPaStride + my_row;
         cp_async_wait<kDepthA - 1>();  // this lane's chunks of keypoint i have landed ...
         __syncwarp();                  // ... and so have everyone else's
-        uint32_t wd[9];
+        // three 16-byte loads per lane (rows are 48 B apart, so a quarter warp covers all 32 banks: no
+        // conflicts, a third of the wavefronts of nine word loads); the window's word offset inside the
+        // row is the same for every lane, so the word selection is a warp-uniform switch
+        uint32_t W[12];
 #pragma unroll
-        for (int j = 0; j < 9; ++j) wd[j] = lds_u32(rw + 4 * j);
+        for (int j = 0; j < 3; ++j) lds_v4(rw + 16 * j, W[4 * j], W[4 * j + 1], W[4 * j + 2], W[4 * j + 3]);
         int m10 = 0;
         uint32_t rs = 0;
+        auto moments = [&](auto O) {
+            constexpr int o = decltype(O)::value;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const uint32_t a = __funnelshift_r(wd[j], wd[j + 1], sh);
-            m10 = dp4a_us(a, wu[j], m10);
-            rs = __dp4a(a, wm[j], rs);
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t a = __funnelshift_r(W[o + j], W[o + j + 1], sh);
+                m10 = dp4a_us(a, wu[j], m10);
+                rs = __dp4a(a, wm[j], rs);
+            }
+        };
+        switch (off >> 2) {
+            case 0: moments(std::integral_constant<int, 0>{}); break;
+            case 1: moments(std::integral_constant<int, 1>{}); break;
+            case 2: moments(std::integral_constant<int, 2>{}); break;
+            default: moments(std::integral_constant<int, 3>{}); break;
         }
         int m01 = v * (int)rs;
         m10 = __reduce_add_sync(0xffffffffu, m10);
