@@ -299,6 +299,7 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
         const uint32_t sel01 = sx.x & 0xffffu, sel23 = sx.x >> 16;
         const int wofs = (int)(sx.y & 0xffffu);
         const uint32_t shift = sx.y >> 16;
+        uint8_t* const dcol = dst + 4 * k;  // a level plane is far below 4 GB: 32-bit row offsets from here
         // horizontal pass of one source row for this lane's output word: 4 x (p0 * c0 + p1 * c1), 8.8 fixed point
         auto hpass = [&](int j, uint32_t (&hv)[4]) {
             const uint32_t* p = sm_w + (j - jlo) * spitch_w + wofs;
@@ -316,7 +317,7 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
 #pragma unroll
             for (int j = 0; j < 4; ++j) v[j] = h1[j] * cy1 + (h0[j] * cy0 + (1u << 15));  // 16.16, byte 2 = result
             if (active)
-                *reinterpret_cast<uint32_t*>(dst + (size_t)y * dpitch + 4 * k) =
+                *reinterpret_cast<uint32_t*>(dcol + (uint32_t)(y * dpitch)) =
                     __byte_perm(__byte_perm(v[0], v[1], 0x0062u), __byte_perm(v[2], v[3], 0x0062u), 0x5410u);
         };
         // a warp takes PAIRS of consecutive output rows: at scale 1.2 the second row's upper source row is
