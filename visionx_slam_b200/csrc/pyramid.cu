@@ -250,11 +250,16 @@ namespace {
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 }  // namespace
 
+// FULL: 16-row bands of a large batch — eight row pairs side by side, one warp each (the throughput shape, 32
+// registers).  !FULL: any band height, pairs_par pairs side by side and the per-word tables prefetched while the
+// band is in flight (the latency shape for a few frames: 39 registers, which would cost the batched case a CTA
+// per SM).
+template <bool FULL>
 __global__ void __launch_bounds__(256)
 resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, size_t sfstride,
                    uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
                    const uint32_t* __restrict__ ytab, const uint4* __restrict__ xw4, const uint2* __restrict__ xw2,
-                   int words, int band_rows, int n_bands) {
+                   int words, int band_rows, int n_bands, int pairs_par) {
     extern __shared__ __align__(128) uint8_t rows_sm[];
     __shared__ __align__(8) unsigned long long bar;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -275,6 +280,18 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
                      "l"(g), "r"(bytes), "r"(smem_addr(&bar))
                      : "memory");
     }
+    // pairs_par (8, 4, 2 or 1) row pairs are worked on side by side; the 8 / pairs_par warps of a pair split
+    // its words 32 at a time, so a short band (small batches: more, shorter bands) still occupies all 8 warps
+    if (FULL) pairs_par = 8;
+    const int pw = warp & (pairs_par - 1), gw = warp / pairs_par, gstep = (8 / pairs_par) * 32;
+    // the per-word tables of the first group are fetched while the band is still in flight
+    uint4 wg_next = make_uint4(0, 0, 0, 0);
+    uint2 sx_next = make_uint2(0, 0);
+    if (!FULL && gw * 32 < words) {
+        const int kk = min(gw * 32 + lane, words - 1);
+        wg_next = __ldg(xw4 + kk);
+        sx_next = __ldg(xw2 + kk);
+    }
     __syncthreads();  // barrier initialised before anyone polls it
     asm volatile(
         "{\n"
@@ -290,12 +307,24 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
 
     const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(rows_sm);
     const int spitch_w = spitch >> 2;
-    for (int k0 = 0; k0 < words; k0 += 32) {
+    for (int k0 = gw * 32; k0 < words; k0 += gstep) {
         const int k = k0 + lane;
         const bool active = k < words;
-        const int kk = active ? k : words - 1;
-        const uint4 wg = __ldg(xw4 + kk);
-        const uint2 sx = __ldg(xw2 + kk);
+        uint4 wg;
+        uint2 sx;
+        if (FULL) {
+            const int kk = active ? k : words - 1;
+            wg = __ldg(xw4 + kk);
+            sx = __ldg(xw2 + kk);
+        } else {
+            wg = wg_next;
+            sx = sx_next;
+            if (k0 + gstep < words) {
+                const int kn = min(k + gstep, words - 1);
+                wg_next = __ldg(xw4 + kn);
+                sx_next = __ldg(xw2 + kn);
+            }
+        }
         const uint32_t sel01 = sx.x & 0xffffu, sel23 = sx.x >> 16;
         const int wofs = (int)(sx.y & 0xffffu);
         const uint32_t shift = sx.y >> 16;
@@ -322,7 +351,7 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
         };
         // a warp takes PAIRS of consecutive output rows: at scale 1.2 the second row's upper source row is
         // the first row's lower one five times out of six, so its horizontal pass is reused
-        for (int y = y_begin + 2 * warp; y < y_end; y += 16) {
+        for (int y = y_begin + 2 * pw; y < y_end; y += 2 * pairs_par) {
             const uint32_t ty = __ldg(ytab + y);
             const int j0 = (int)(ty & 0xffffu);
             const int j1 = min(j0 + 1, sh - 1);
@@ -449,7 +478,9 @@ bool plan_resize_bands(const uint32_t* ytaps, int dh, int sh, int spitch, int* b
 }
 
 cudaError_t init_pyramid_kernels() {
-    return cudaFuncSetAttribute(resize_band_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    const cudaError_t e = cudaFuncSetAttribute(resize_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(resize_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
 // Builds levels 1.. of every frame and the reflect-101 apron of every level.  Returns launches.
@@ -463,10 +494,17 @@ int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) 
             const uint4* xw4 = reinterpret_cast<const uint4*>(db.coef + lt.xw_off[l]);
             const uint2* xw2 = reinterpret_cast<const uint2*>(db.coef + lt.xw_off[l] + 4 * words);
             const uint8_t* src_plane = db.pyr + lt.off[l - 1] - plane_origin(lt.w[l - 1]);
-            dim3 grid(lt.n_bands[l], lt.batch);
-            resize_band_kernel<<<grid, 256, lt.band_smem[l], s>>>(
+            // A few frames alone leave most SMs without a band: 4-row bands then (4x the CTAs, the level chain is
+            // the critical path of a single-frame call).  The planned shared memory covers the tallest planned
+            // band, which is taller than any 4..7-row band.
+            const bool small = lt.batch < 8 && lt.band_rows[l] > 4;
+            const int rows = small ? 4 : lt.band_rows[l];
+            const int nb = small ? std::max(1, lt.h[l] / 4) : lt.n_bands[l];
+            dim3 grid(nb, lt.batch);
+            auto kern = rows == 16 ? resize_band_kernel<true> : resize_band_kernel<false>;
+            kern<<<grid, 256, lt.band_smem[l], s>>>(
                 src_plane, lt.h[l - 1], lt.pitch[l - 1], (size_t)lt.fstride[l - 1], db.pyr + lt.off[l], lt.w[l], lt.h[l],
-                lt.pitch[l], (size_t)lt.fstride[l], tab + lt.w[l], xw4, xw2, words, lt.band_rows[l], lt.n_bands[l]);
+                lt.pitch[l], (size_t)lt.fstride[l], tab + lt.w[l], xw4, xw2, words, rows, nb, rows / 2);
             ++launches;
         }
         return launches;
