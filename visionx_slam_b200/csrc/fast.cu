@@ -280,13 +280,16 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                     idx = q16[e];
                     const int r = idx >> 7, c = idx & 127;
                     const int gx = X + c, gy = Y + r;
-                    if (r >= 1 && r <= kFastEmitH && c >= 1 && c <= kFastEmitW && gx >= border && gy >= border &&
-                        gx < ex_max && gy < ey_max) {
-                        const uint8_t* p = sc + idx;
-                        const int s = p[0];
-                        keep = s > p[-FW - 1] && s > p[-FW] && s > p[-FW + 1] && s > p[-1] && s > p[1] &&
-                               s > p[FW - 1] && s > p[FW] && s > p[FW + 1];
-                    }
+                    const bool inside = r >= 1 && r <= kFastEmitH && c >= 1 && c <= kFastEmitW && gx >= border &&
+                                        gy >= border && gx < ex_max && gy < ey_max;
+                    // branch-free: strictly greater than all eight neighbours <=> greater than their maximum
+                    // (lanes outside the emission domain read around a safe interior cell instead)
+                    const uint8_t* p = sc + (inside ? idx : FW + 1);
+                    const int s = p[0];
+                    const int m0 = max(max((int)p[-FW - 1], (int)p[-FW]), (int)p[-FW + 1]);
+                    const int m1 = max(max((int)p[-1], (int)p[1]), (int)p[FW - 1]);
+                    const int m2 = max((int)p[FW], (int)p[FW + 1]);
+                    keep = inside && s > max(max(m0, m1), m2);
                 }
                 __syncwarp();
                 const uint32_t m = __ballot_sync(0xffffffffu, keep);
