@@ -179,22 +179,34 @@ knn2_merge_kernel(const MatchArgs a) {
 // ---- windowed 2-NN over a uniform cell grid ------------------------------------------------------
 // The brute-force kernel above tests every (query, train) pair against the window.  With a square
 // window of radius r only ~(2r)^2 / (W*H) of the train rows can pass (1.3 % at r = 32 on 640x480),
-// so this kernel first bins the train keypoints of the pair into a kCellGrid x kCellGrid grid of
-// cells at least r wide (counting sort in shared memory: histogram, block scan, scatter of
+// so this kernel first bins the train keypoints of the pair into a kGridX x kGridY grid of
+// cells at least r / 2 wide (counting sort in shared memory: histogram, block scan, scatter of
 // descriptor + position + original index in cell order), and every query thread then visits only
-// the cells its window touches: <= 3 x 3 cells, each cell row one contiguous range of the sorted
+// the cells its window touches: <= 5 x 5 cells (80 x 80 px at r = 32 against the 65 x 65 window), each cell row one contiguous range of the sorted
 // list.  The exact window test (same float expression as the brute-force kernel) is still applied
 // per candidate, and the packed key (distance << 20 | original train index) keeps OpenCV's
 // tie-break (lowest train index) whatever the visiting order.  Cell lookup is conservative: the
 // cell range is computed from a slightly widened radius with the same monotonic float expression
 // that bins the train points, so no in-window row can be missed.
-constexpr int kCellGrid = 32;
-constexpr int kCells = kCellGrid * kCellGrid;
+#ifndef VXORB_WIN_GX
+#define VXORB_WIN_GX 64
+#endif
+#ifndef VXORB_WIN_GY
+#define VXORB_WIN_GY 32
+#endif
+#ifndef VXORB_WIN_DIV
+#define VXORB_WIN_DIV 2
+#endif
+constexpr int kGridX = VXORB_WIN_GX, kGridY = VXORB_WIN_GY;
+constexpr int kCells = kGridX * kGridY;
 constexpr int kWinThreads = 1024;
+constexpr int kCellsPerThread = kCells / kWinThreads;
+constexpr float kCellPerRadius = 1.0f / VXORB_WIN_DIV;  // cells are at least radius / 2 wide: a window touches <= 5 x 5
+static_assert(kCells % kWinThreads == 0 && kCellsPerThread >= 1, "whole cells per thread in the block scan");
 
-__device__ __forceinline__ int cell_of(float v, float org, float inv) {
+__device__ __forceinline__ int cell_of(float v, float org, float inv, int n) {
     const float c = floorf(__fmul_rn(__fsub_rn(v, org), inv));
-    return (int)fminf(fmaxf(c, 0.0f), (float)(kCellGrid - 1));
+    return (int)fminf(fmaxf(c, 0.0f), (float)(n - 1));
 }
 
 static size_t window_smem_bytes(int max_t, int max_q) {
@@ -253,23 +265,27 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
         __syncthreads();
     }
     const float orgx = bounds[0], orgy = bounds[1];
-    // cells at least r wide, and wide enough that kCellGrid of them cover the bounding box
-    const float csx = fmaxf(r, (bounds[2] - orgx) * (1.0f / kCellGrid) * 1.0001f);
-    const float csy = fmaxf(r, (bounds[3] - orgy) * (1.0f / kCellGrid) * 1.0001f);
+    // cells at least r / 2 wide, and wide enough that kGridX x kGridY of them cover the bounding box
+    const float csx = fmaxf(r * kCellPerRadius, (bounds[2] - orgx) * (1.0f / kGridX) * 1.0001f);
+    const float csy = fmaxf(r * kCellPerRadius, (bounds[3] - orgy) * (1.0f / kGridY) * 1.0001f);
     const float invx = 1.0f / csx, invy = 1.0f / csy;
 
     // ---- 2. counting sort of the train rows by cell --------------------------------------------
     for (int i = tid; i < nt; i += kWinThreads) {
         const float2 p = __ldg(txy_g + i);
-        atomicAdd(&cell_start[cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx)], 1);
+        atomicAdd(&cell_start[cell_of(p.y, orgy, invy, kGridY) * kGridX + cell_of(p.x, orgx, invx, kGridX)], 1);
     }
     __syncthreads();
     // exclusive scan of the kCells counts in cell_start (one per thread: warp scan, then warp totals);
     // leaves the running offsets in cursor as well
     auto scan_cells = [&]() {
-        static_assert(kCells == kWinThreads, "one cell per thread");
-        const int c = cell_start[tid];
-        int incl = c;
+        int c[kCellsPerThread], sum = 0;
+#pragma unroll
+        for (int i = 0; i < kCellsPerThread; ++i) {
+            c[i] = cell_start[tid * kCellsPerThread + i];
+            sum += c[i];
+        }
+        int incl = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int n = __shfl_up_sync(0xffffffffu, incl, o);
@@ -277,17 +293,21 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
         }
         if (lane == 31) warp_tot[warp] = incl;
         __syncthreads();
-        int base = incl - c;
+        int base = incl - sum;
         for (int wv = 0; wv < warp; ++wv) base += warp_tot[wv];
-        cell_start[tid] = base;
-        cursor[tid] = base;
-        if (tid == kWinThreads - 1) cell_start[kCells] = base + c;
+#pragma unroll
+        for (int i = 0; i < kCellsPerThread; ++i) {
+            cell_start[tid * kCellsPerThread + i] = base;
+            cursor[tid * kCellsPerThread + i] = base;
+            base += c[i];
+        }
+        if (tid == kWinThreads - 1) cell_start[kCells] = base;
         __syncthreads();
     };
     scan_cells();
     for (int i = tid; i < nt; i += kWinThreads) {
         const float2 p = __ldg(txy_g + i);
-        const int cell = cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx);
+        const int cell = cell_of(p.y, orgy, invy, kGridY) * kGridX + cell_of(p.x, orgx, invx, kGridX);
         const int pos = atomicAdd(&cursor[cell], 1);
         txy[pos] = p;
         tidx[pos] = i;
@@ -301,25 +321,28 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
     // max-over-lanes iterations) and broadcast reads of the sorted train rows.  Counting sort of the
     // query rows by the cell of their position in the train grid; cell_start is saved first.
     const float2* qxy_g = reinterpret_cast<const float2*>(a.q_xy + (size_t)pair * a.q_pair_stride * 2);
-    int my_start[2];
-    my_start[0] = cell_start[tid];
-    my_start[1] = tid == 0 ? cell_start[kCells] : 0;
+    int my_start[kCellsPerThread + 1];
+#pragma unroll
+    for (int i = 0; i < kCellsPerThread; ++i) my_start[i] = cell_start[tid * kCellsPerThread + i];
+    my_start[kCellsPerThread] = tid == 0 ? cell_start[kCells] : 0;
     __syncthreads();
-    cell_start[tid] = 0;
+#pragma unroll
+    for (int i = 0; i < kCellsPerThread; ++i) cell_start[tid * kCellsPerThread + i] = 0;
     __syncthreads();
     for (int i = tid; i < nq; i += kWinThreads) {
         const float2 p = __ldg(qxy_g + i);
-        atomicAdd(&cell_start[cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx)], 1);
+        atomicAdd(&cell_start[cell_of(p.y, orgy, invy, kGridY) * kGridX + cell_of(p.x, orgx, invx, kGridX)], 1);
     }
     __syncthreads();
     scan_cells();
     for (int i = tid; i < nq; i += kWinThreads) {
         const float2 p = __ldg(qxy_g + i);
-        qorder[atomicAdd(&cursor[cell_of(p.y, orgy, invy) * kCellGrid + cell_of(p.x, orgx, invx)], 1)] = (uint16_t)i;
+        qorder[atomicAdd(&cursor[cell_of(p.y, orgy, invy, kGridY) * kGridX + cell_of(p.x, orgx, invx, kGridX)], 1)] = (uint16_t)i;
     }
     __syncthreads();
-    cell_start[tid] = my_start[0];  // back to the train offsets
-    if (tid == 0) cell_start[kCells] = my_start[1];
+#pragma unroll
+    for (int i = 0; i < kCellsPerThread; ++i) cell_start[tid * kCellsPerThread + i] = my_start[i];  // back to the train offsets
+    if (tid == 0) cell_start[kCells] = my_start[kCellsPerThread];
     __syncthreads();
 
     for (int rank = tid; rank < nq; rank += kWinThreads) {
@@ -335,11 +358,11 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
         const float qx = qp.x, qy = qp.y;
         // widened radius for the cell range only (covers the rounding of qx - tx and of qx +- r)
         const float rw = r + r * 1.0e-4f + fmaxf(fabsf(qx), fabsf(qy)) * 1.0e-6f;
-        const int cx0 = cell_of(qx - rw, orgx, invx), cx1 = cell_of(qx + rw, orgx, invx);
-        const int cy0 = cell_of(qy - rw, orgy, invy), cy1 = cell_of(qy + rw, orgy, invy);
+        const int cx0 = cell_of(qx - rw, orgx, invx, kGridX), cx1 = cell_of(qx + rw, orgx, invx, kGridX);
+        const int cy0 = cell_of(qy - rw, orgy, invy, kGridY), cy1 = cell_of(qy + rw, orgy, invy, kGridY);
         uint32_t k0 = kNoKey, k1 = kNoKey;
         for (int cy = cy0; cy <= cy1; ++cy) {
-            const int j0 = cell_start[cy * kCellGrid + cx0], j1 = cell_start[cy * kCellGrid + cx1 + 1];
+            const int j0 = cell_start[cy * kGridX + cx0], j1 = cell_start[cy * kGridX + cx1 + 1];
             for (int j = j0; j < j1; ++j) {
                 const float2 p = txy[j];
                 if (fabsf(__fsub_rn(qx, p.x)) <= r && fabsf(__fsub_rn(qy, p.y)) <= r) {
@@ -459,13 +482,13 @@ int launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t s) {
 
 // Opts the windowed kernel into large dynamic shared memory on the current device (vxorb_create).
 cudaError_t init_match_kernels() {
-    return cudaFuncSetAttribute(knn2_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    return cudaFuncSetAttribute(knn2_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
 }
 
 int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     if (a.pairs <= 0 || a.max_q <= 0) return 0;
     const bool windowed = a.radius > 0.0f && !a.boxed && a.q_xy != nullptr && a.t_xy != nullptr;
-    if (windowed && a.max_t > 0 && a.max_q <= 65536 && window_smem_bytes(a.max_t, a.max_q) <= 200 * 1024) {
+    if (windowed && a.max_t > 0 && a.max_q <= 65536 && window_smem_bytes(a.max_t, a.max_q) <= 224 * 1024) {
         // cell-binned path: one CTA per pair, the whole train set sits in shared memory in cell order
         knn2_window_kernel<<<a.pairs, kWinThreads, window_smem_bytes(a.max_t, a.max_q), s>>>(a, a.max_t, a.max_q);
         return 1;
