@@ -149,6 +149,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
     __syncthreads();
 
     uint16_t* q16 = wq[warp];
+    const uint32_t relcol = (uint32_t)lane * 0x04040404u + 0x03020100u;  // this lane's four tile-relative columns
     int it = 0;
     for (int t = blockIdx.x; t < total_tiles; t += grid, ++it) {
         const int buf = it & 1;
@@ -166,12 +167,12 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
         // score domain (global coordinates, inclusive)
         const int sx_min = max(3, border - 1), sx_max = min(w - 4, w - border);
         const int sy_min = max(3, border - 1), sy_max = min(h - 4, h - border);
-        uint32_t colmask = 0;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int gx = X + 4 * lane + j;
-            if (gx >= sx_min && gx <= sx_max) colmask |= 0x80u << (8 * j);
-        }
+        // bit 7 of byte j <=> column X + 4*lane + j lies in [sx_min, sx_max].  Tile-relative columns are bytes
+        // 0..127, so both comparisons are one packed add / subtract against a tile-uniform constant: byte + (128 - lo)
+        // and (128 + hi) - byte carry into bit 7 exactly when byte >= lo resp. byte <= hi, never across bytes.
+        const int clo = min(max(sx_min - X, 0), 128), chi = min(max(sx_max - X, -1), 127);
+        const uint32_t colmask = (relcol + (uint32_t)(128 - clo) * 0x01010101u) &
+                                 ((uint32_t)(128 + chi) * 0x01010101u - relcol) & 0x80808080u;
         mbar_wait(&mbar[buf], (uint32_t)(it >> 1) & 1u);
 
         // ---- stage 1: 4-pixel-wide necessary-condition test -----------------------------------
@@ -179,12 +180,14 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
         {
             const uint32_t cadd = (uint32_t)(HI ? 255 - threshold : 127 - threshold) * 0x01010101u;
             uint32_t acc = 0;
+            // rows of the score domain, tile-relative: [ylo, ylo + yspan]; an empty domain gets an unreachable ylo
+            const int ylo = sy_max >= sy_min ? sy_min - Y : (1 << 20);
+            const uint32_t yspan = sy_max >= sy_min ? (uint32_t)(sy_max - sy_min) : 0u;
 #pragma unroll
             for (int i = 0; i < RPW; ++i) {
                 const int r = i * 8 + warp;  // rows interleaved over warps: a corner cluster spreads over several warps
-                const int gy = Y + r;
                 uint32_t q = 0;
-                if (gy >= sy_min && gy <= sy_max) {
+                if ((uint32_t)(r - ylo) <= yspan) {  // sy_min <= Y + r <= sy_max in one unsigned compare
                     const uint32_t* row = &tile[r + 3][lane + wo];
                     const uint32_t wl = row[0], v = row[1], wr = row[2];
                     const uint32_t up = tile[r][lane + 1 + wo], dn = tile[r + 6][lane + 1 + wo];
