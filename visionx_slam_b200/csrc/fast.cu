@@ -247,12 +247,10 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                     uint32_t m9[16];
 #pragma unroll
                     for (int k = 0; k < 16; ++k) m9[k] = __vimin3_s16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
-                    uint32_t best = m9[15];
+                    uint32_t best = __vimax3_s16x2(m9[0], m9[1], m9[2]);  // 16 values: seven 3-input maxima + one 2-input
 #pragma unroll
-                    for (int k = 0; k < 15; k += 3) {
-                        best = __vimax3_s16x2(best, m9[k], m9[k + 1]);
-                        best = __vmaxs2(best, m9[k + 2]);
-                    }
+                    for (int k = 3; k < 15; k += 2) best = __vimax3_s16x2(best, m9[k], m9[k + 1]);
+                    best = __vmaxs2(best, m9[15]);
                     const int s = max((int)(best & 0xffffu), (int)(best >> 16)) - 257;
                     if (s >= threshold) {
                         sc[idx] = (uint8_t)s;
