@@ -218,6 +218,15 @@ int vxorb_track_submit_info(vxorb_handle* h, const uint8_t* frames, int batch, i
                             vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_kp_out, int match_cap,
                             vxorb_match_t* match_out, int* n_match_out, vxorb_frame_info* info_out,
                             float* pts_out, int* slot_out);
+/* vxorb_track_submit_info for 3-channel frames in BGR byte order, what System::Run hands to Tracking
+ * (system.cpp:46) and cv::ORB converts internally (orb_extractor.cpp:13): stride >= 3 * width bytes per
+ * row; the chunk is converted on the device with the conversion of vxorb_extract_bgr.  info_out and
+ * pts_out may be NULL. */
+int vxorb_track_submit_bgr(vxorb_handle* h, const uint8_t* bgr_frames, int batch, int width, int height,
+                           size_t stride, size_t frame_stride, float radius, int kp_cap,
+                           vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_kp_out, int match_cap,
+                           vxorb_match_t* match_out, int* n_match_out, vxorb_frame_info* info_out,
+                           float* pts_out, int* slot_out);
 int vxorb_track_wait(vxorb_handle* h, int slot);
 int vxorb_keypoint_capacity(const vxorb_handle* h);
 

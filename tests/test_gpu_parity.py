@@ -354,6 +354,36 @@ def test_track_sequence_chunks(radius):
         assert np.array_equal(matches_as_rows(again[1][2]), matches_as_rows(ref[5][2]))
 
 
+def test_track_bgr_chunks():
+    """Colour chunks through the streaming path (what System::Run feeds, system.cpp:46): converted on the device,
+    then identical to streaming the oracle's gray conversion; a strided (padded-row) chunk gives the same."""
+    rng = np.random.default_rng(12)
+    gray = synth_sequence(320, 240, 5, seed=8)
+    # a real colour sequence: three differently weighted / offset copies of the scene, not gray replicated
+    bgr = np.stack([gray, np.roll(gray, 2, axis=2), 255 - gray], axis=-1).astype(np.uint8)
+    bgr[..., 1] = np.clip(bgr[..., 1].astype(np.int32) + rng.integers(-6, 7, gray.shape), 0, 255).astype(np.uint8)
+    conv = np.stack([oracle.bgr2gray(f) for f in bgr])
+    with vx.VxOrb(n_features=500, max_width=320, max_height=240, max_batch=5) as hx:
+        want = hx.track(conv, 24.0)
+        hx.track_reset()
+        got = hx.track_bgr(bgr, 24.0)
+        hx.track_reset()
+        padded = np.zeros((5, 240, 336, 3), np.uint8)
+        padded[:, :, :320] = bgr
+        got_strided = hx.track_bgr(padded[:, :, :320], 24.0)  # rows 1008 B apart: the strided upload path
+    okp, odesc = oracle.orb_extract(conv[1], 500)
+    assert_kp_equal(want[1][0], okp)
+    for (kp, desc, m), (wkp, wdesc, wm) in zip(got, want):
+        assert_kp_equal(kp, wkp)
+        assert np.array_equal(desc, wdesc)
+        assert np.array_equal(matches_as_rows(m), matches_as_rows(wm))
+    for (kp, desc, m), (wkp, wdesc, wm) in zip(got_strided, want):
+        assert_kp_equal(kp, wkp)
+        assert np.array_equal(desc, wdesc)
+        assert np.array_equal(matches_as_rows(m), matches_as_rows(wm))
+    assert len(got[1][2]) > 100
+
+
 def test_track_pipelined_slots():
     """Three chunks in flight on the three pipeline slots, pinned buffers, waits in order."""
     frames = synth_sequence(640, 480, 9, seed=5)

@@ -74,6 +74,7 @@ _SYMBOLS = [
     ("vxorb_track_reset", _i, [_vp]),
     ("vxorb_track_submit", _i, [_vp, _vp, _i, _i, _i, _sz, _sz, _f, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
     ("vxorb_track_submit_info", _i, [_vp, _vp, _i, _i, _i, _sz, _sz, _f, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
+    ("vxorb_track_submit_bgr", _i, [_vp, _vp, _i, _i, _i, _sz, _sz, _f, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
     ("vxorb_track_wait", _i, [_vp, _i]),
     ("vxorb_keypoint_capacity", _i, [_vp]),
     ("vxorb_host_alloc", _vp, [_sz]),
@@ -332,6 +333,25 @@ class VxOrb:
 
     def track_wait(self, slot):
         self._check(self._lib.vxorb_track_wait(self._h, slot))
+
+    def track_bgr(self, frames, radius):
+        """track() for a (B,H,W,3) BGR chunk (converted on the device as cv::ORB converts a colour input)."""
+        frames = np.asarray(frames)
+        if frames.dtype != np.uint8 or frames.ndim != 4 or frames.strides[3] != 1 or frames.strides[2] != 3:
+            frames = np.ascontiguousarray(frames, dtype=np.uint8)  # padded rows / frames are passed through as strides
+        b, h, w, c = frames.shape
+        assert c == 3
+        kp = np.zeros((b, self.kp_cap), KEYPOINT_DTYPE)
+        desc = np.zeros((b, self.kp_cap, 32), np.uint8)
+        nk = np.zeros(b, np.int32)
+        mt = np.zeros((b, self.kp_cap), MATCH_DTYPE)
+        nm = np.zeros(b, np.int32)
+        slot = C.c_int(-1)
+        self._check(self._lib.vxorb_track_submit_bgr(self._h, _ptr(frames), b, w, h, frames.strides[1], frames.strides[0],
+                                                     radius, self.kp_cap, _ptr(kp), _ptr(desc), _ptr(nk), self.kp_cap,
+                                                     _ptr(mt), _ptr(nm), None, None, C.byref(slot)))
+        self.track_wait(slot.value)
+        return [(kp[i, :nk[i]].copy(), desc[i, :nk[i]].copy(), mt[i, :nm[i]].copy()) for i in range(b)]
 
     def track_info(self, frames, radius):
         """track() plus per-frame vxorb_frame_info and the matched positions (x_last, y_last, x_curr, y_curr)."""

@@ -50,6 +50,7 @@ struct Workspace {
     vxorb_frame_info* info = nullptr;     // [max_batch]
     float4* pts = nullptr;                // [max_batch][kp_cap]
     uint8_t* stage_in = nullptr;          // [max_batch][H][W] densely packed upload staging
+    uint8_t* stage_bgr = nullptr;         // [max_batch][H][3 W] colour upload staging, allocated on the first BGR chunk
 };
 
 }  // namespace
@@ -147,8 +148,8 @@ void free_workspace(Workspace& w) {
     cudaFree(d.fin_key); cudaFree(d.fin_resp); cudaFree(d.fin_n); cudaFree(d.kp); cudaFree(d.desc);
     cudaFree(d.xy); cudaFree(d.kp_n); cudaFree(d.kp_total); cudaFree(d.knn); cudaFree(d.match);
     cudaFree(d.match_n); cudaFree(d.status);
-    cudaFree(w.sums); cudaFree(w.info); cudaFree(w.pts); cudaFree(w.stage_in);
-    w.sums = nullptr; w.info = nullptr; w.pts = nullptr; w.stage_in = nullptr;
+    cudaFree(w.sums); cudaFree(w.info); cudaFree(w.pts); cudaFree(w.stage_in); cudaFree(w.stage_bgr);
+    w.sums = nullptr; w.info = nullptr; w.pts = nullptr; w.stage_in = nullptr; w.stage_bgr = nullptr;
     d = DeviceBuffers();
 }
 
@@ -471,6 +472,32 @@ int upload_frames(vxorb_handle* h, Workspace& ws, const uint8_t* frames, int bat
             CK(cudaMemcpy2DAsync(dst + (size_t)f * lt.fstride[0], lt.pitch[0], frames + (size_t)f * frame_stride,
                                  stride, W, H, cudaMemcpyHostToDevice, ws.stream));
     }
+    return VXORB_OK;
+}
+
+// Copies `batch` host BGR frames (3 bytes per pixel) into the workspace's colour staging buffer and converts
+// them into level 0 on the device (the conversion cv::ORB applies to a 3-channel input).
+int upload_bgr_frames(vxorb_handle* h, Workspace& ws, const uint8_t* frames, int batch, int W, int H, size_t stride,
+                      size_t frame_stride) {
+    const LevelTab& lt = h->lt;
+    const size_t row = (size_t)W * 3, frame = row * H;
+    if (!ws.stage_bgr) {
+        if (cudaMalloc(&ws.stage_bgr, frame * (size_t)h->p.max_batch) != cudaSuccess) {
+            ws.stage_bgr = nullptr;
+            cudaGetLastError();
+            return fail(h, VXORB_E_NOMEM, "device allocation of the BGR staging buffer failed");
+        }
+    }
+    if (stride == row && frame_stride == frame) {
+        CK(cudaMemcpyAsync(ws.stage_bgr, frames, frame * batch, cudaMemcpyHostToDevice, ws.stream));
+    } else {
+        for (int f = 0; f < batch; ++f)
+            CK(cudaMemcpy2DAsync(ws.stage_bgr + (size_t)f * frame, row, frames + (size_t)f * frame_stride, stride, row, H,
+                                 cudaMemcpyHostToDevice, ws.stream));
+    }
+    h->launches += launch_gray_from_bgr(ws.stage_bgr, row, frame, ws.db.pyr + lt.off[0], W, H, lt.pitch[0],
+                                        (size_t)lt.fstride[0], batch, ws.stream);
+    h->stage_launches[VXORB_STAGE_PYRAMID] += 1;
     return VXORB_OK;
 }
 
@@ -1017,14 +1044,15 @@ int vxorb_track_submit(vxorb_handle* h, const uint8_t* frames, int batch, int wi
                                    n_kp_out, match_cap, match_out, n_match_out, nullptr, nullptr, slot_out);
 }
 
-int vxorb_track_submit_info(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height, size_t stride,
-                            size_t frame_stride, float radius, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out,
-                            int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out,
-                            vxorb_frame_info* info_out, float* pts_out, int* slot_out) {
+static int track_submit_common(vxorb_handle* h, const uint8_t* frames, int channels, int batch, int width, int height,
+                               size_t stride, size_t frame_stride, float radius, int kp_cap, vxorb_keypoint* kp_out,
+                               uint8_t* desc_out, int* n_kp_out, int match_cap, vxorb_match_t* match_out,
+                               int* n_match_out, vxorb_frame_info* info_out, float* pts_out, int* slot_out) {
     if (!h) return VXORB_E_INVALID;
     if (!frames || !slot_out) return fail(h, VXORB_E_INVALID, "null argument");
+    if (channels != 1 && channels != 3) return fail(h, VXORB_E_INVALID, "channels must be 1 (gray) or 3 (BGR)");
     if (batch < 1 || batch > h->p.max_batch) return fail(h, VXORB_E_INVALID, "batch outside 1..max_batch");
-    if (stride < (size_t)width) return fail(h, VXORB_E_INVALID, "stride smaller than a row");
+    if (width < 1 || height < 1 || stride < (size_t)width * channels) return fail(h, VXORB_E_INVALID, "stride smaller than a row");
     if ((kp_out || desc_out) && kp_cap != h->kp_cap)
         return fail(h, VXORB_E_INVALID, "track outputs must use kp_cap == the handle's max_keypoints");
     if ((match_out || pts_out) && match_cap != h->kp_cap)
@@ -1036,7 +1064,8 @@ int vxorb_track_submit_info(vxorb_handle* h, const uint8_t* frames, int batch, i
     Workspace& ws = h->ws[slot];
     if (ws.in_flight) return fail(h, VXORB_E_INVALID, "all pipeline slots in flight; call vxorb_track_wait first");
     cudaStream_t s = ws.stream;
-    rc = upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
+    rc = channels == 3 ? upload_bgr_frames(h, ws, frames, batch, width, height, stride, frame_stride)
+                       : upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
     if (rc) return rc;
     rc = enqueue_chunk(h, ws, batch, radius);
     if (rc) return rc;
@@ -1059,6 +1088,22 @@ int vxorb_track_submit_info(vxorb_handle* h, const uint8_t* frames, int batch, i
     h->next_slot = (slot + 1) % kSlots;
     *slot_out = slot;
     return VXORB_OK;
+}
+
+int vxorb_track_submit_info(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height, size_t stride,
+                            size_t frame_stride, float radius, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out,
+                            int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out,
+                            vxorb_frame_info* info_out, float* pts_out, int* slot_out) {
+    return track_submit_common(h, frames, 1, batch, width, height, stride, frame_stride, radius, kp_cap, kp_out, desc_out,
+                               n_kp_out, match_cap, match_out, n_match_out, info_out, pts_out, slot_out);
+}
+
+int vxorb_track_submit_bgr(vxorb_handle* h, const uint8_t* bgr_frames, int batch, int width, int height, size_t stride,
+                           size_t frame_stride, float radius, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out,
+                           int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out,
+                           vxorb_frame_info* info_out, float* pts_out, int* slot_out) {
+    return track_submit_common(h, bgr_frames, 3, batch, width, height, stride, frame_stride, radius, kp_cap, kp_out,
+                               desc_out, n_kp_out, match_cap, match_out, n_match_out, info_out, pts_out, slot_out);
 }
 
 int vxorb_track_wait(vxorb_handle* h, int slot) {
