@@ -41,7 +41,7 @@ struct Workspace {
     // side stream of the slot: the blur of a chunk runs here beside FAST + select (both only read the
     // pyramid); forked after the pyramid and joined before the descriptors
     cudaStream_t side = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork0 = nullptr, ev_apron = nullptr;
     int batch = 0;          // frames of the chunk in flight / last processed
     bool in_flight = false;
     int* h_status = nullptr;  // pinned: status word copied back with every chunk
@@ -328,15 +328,28 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
     CK(cudaMemsetAsync(d.cand_n, 0, sizeof(int) * kMaxLevels * h->p.max_batch, s));
     CK(cudaMemsetAsync(d.status, 0, sizeof(int) * 4, s));
     // cand_n / fin_n are indexed [level * batch + frame] with the launch's batch
-    {
-        StageScope sc(h, s, VXORB_STAGE_PYRAMID);
-        sc.end(launch_pyramid(lt, d, s));
-    }
     // The blur needs only the pyramid, FAST + select never touch the blurred planes: outside the
     // instrumented (per-stage timed) mode the blur runs on the slot's side stream beside them and fills
     // the issue slots FAST's barriers and select's tails leave idle.  Instrumented runs stay serial so a
     // stage's events bracket that stage alone.
     const bool overlap = !h->stage_enabled && ws.side != nullptr && !getenv("VXORB_NO_OVERLAP");
+    // Level 0's reflect apron is read by FAST and the blur, not by the resampling: for a few frames (where the
+    // level chain is the critical path) it is built on the side stream while the chain already runs.  Large
+    // batches keep it in line: there it only takes SMs from the first resize level (A/B: -0.7 % resident).
+    const bool apron_aside = overlap && lt.resize_band && batch < 8;
+    if (apron_aside) {
+        CK(cudaEventRecord(ws.ev_fork0, s));
+        CK(cudaStreamWaitEvent(ws.side, ws.ev_fork0, 0));
+        const int n = launch_apron(lt, d, 1, ws.side);
+        h->launches += n;
+        h->stage_launches[VXORB_STAGE_PYRAMID] += n;
+        CK(cudaEventRecord(ws.ev_apron, ws.side));
+    }
+    {
+        StageScope sc(h, s, VXORB_STAGE_PYRAMID);
+        sc.end(launch_pyramid(lt, d, s, !apron_aside));
+    }
+    if (apron_aside) CK(cudaStreamWaitEvent(s, ws.ev_apron, 0));
     if (overlap) {
         CK(cudaEventRecord(ws.ev_fork, s));
         CK(cudaStreamWaitEvent(ws.side, ws.ev_fork, 0));
@@ -732,6 +745,8 @@ int vxorb_create(const vxorb_params* p, vxorb_handle** out) {
         if ((e = cudaStreamCreateWithFlags(&w.side, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "side stream");
         if ((e = cudaEventCreateWithFlags(&w.ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
         if ((e = cudaEventCreateWithFlags(&w.ev_join, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
+        if ((e = cudaEventCreateWithFlags(&w.ev_fork0, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
+        if ((e = cudaEventCreateWithFlags(&w.ev_apron, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
         if ((e = cudaHostAlloc(&w.h_status, sizeof(int) * 4, cudaHostAllocDefault)) != cudaSuccess) return bail(e, "pinned");
         w.h_status[0] = 0;
     }
@@ -755,6 +770,8 @@ void vxorb_destroy(vxorb_handle* h) {
         if (w.side) cudaStreamDestroy(w.side);
         if (w.ev_fork) cudaEventDestroy(w.ev_fork);
         if (w.ev_join) cudaEventDestroy(w.ev_join);
+        if (w.ev_fork0) cudaEventDestroy(w.ev_fork0);
+        if (w.ev_apron) cudaEventDestroy(w.ev_apron);
         if (w.h_status) cudaFreeHost(w.h_status);
     }
     cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);

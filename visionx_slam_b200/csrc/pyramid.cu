@@ -484,10 +484,12 @@ cudaError_t init_pyramid_kernels() {
 }
 
 // Builds levels 1.. of every frame and the reflect-101 apron of every level.  Returns launches.
-int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
+int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, bool level0_apron) {
     int launches = 0;
     if (lt.resize_band) {
-        launches += launch_apron(lt, db, 1, s);  // level 0 comes from the upload; the bands write their own apron
+        // level 0 comes from the upload; the bands write their own apron.  The resampling reads no apron byte of
+        // its source, so a caller may build level 0's apron elsewhere (beside the chain) and pass false.
+        if (level0_apron) launches += launch_apron(lt, db, 1, s);
         for (int l = 1; l < lt.n_levels; ++l) {
             const int words = (lt.w[l] + 3) / 4;
             const uint32_t* tab = db.coef + lt.coef_off[l];

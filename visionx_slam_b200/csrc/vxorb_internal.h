@@ -110,7 +110,7 @@ int launch_gray_from_bgr(const uint8_t* bgr, size_t bgr_pitch, size_t bgr_fstrid
 // w must be a multiple of 16; src holds `batch` frames of w*h bytes back to back (16 B aligned)
 int launch_unpack_frames(const uint8_t* src, uint8_t* dst, int w, int h, int pitch, size_t fstride, int batch,
                          cudaStream_t s);
-int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
+int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, bool level0_apron = true);
 int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh,
                          int dpitch, const uint32_t* xtab, const uint32_t* ytab, bool fast, cudaStream_t s);
 bool resize_taps_fit_fast_path(const uint32_t* xtaps, int dw);
