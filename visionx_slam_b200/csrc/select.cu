@@ -137,7 +137,10 @@ __device__ __forceinline__ void top_bin_scan(const int* hist, int k, int lane, i
 
 }  // namespace
 
-__global__ void __launch_bounds__(kThreads)
+#ifndef VXORB_SELECT_CTAS
+#define VXORB_SELECT_CTAS 4
+#endif
+__global__ void __launch_bounds__(kThreads, VXORB_SELECT_CTAS)
 select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ cand,
               const int* __restrict__ cand_n, float* __restrict__ resp, uint32_t* __restrict__ fin_key,
               float* __restrict__ fin_resp, int* __restrict__ fin_n, int* __restrict__ status) {
