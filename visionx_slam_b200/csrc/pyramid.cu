@@ -307,7 +307,12 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
 
     const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(rows_sm);
     const int spitch_w = spitch >> 2;
-    for (int k0 = gw * 32; k0 < words; k0 += gstep) {
+    // FULL: when the last group of 32 words of a row is at most half full, it is not given a warp-iteration per
+    // row pair; the tails of 2 (<= 16 words) or 4 (<= 8 words) row pairs share one iteration below.
+    const int rem = words & 31;
+    const int seg = (FULL && rem != 0 && rem <= 16) ? (rem <= 8 ? 8 : 16) : 0;
+    const int words_main = seg ? words - rem : words;
+    for (int k0 = gw * 32; k0 < words_main; k0 += gstep) {
         const int k = k0 + lane;
         const bool active = k < words;
         uint4 wg;
@@ -377,6 +382,47 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
                     vpass_store(y + 1, ha, hc, tz >> 16);
                 }
             }
+        }
+    }
+    if (seg) {
+        const int sub = lane / seg, kq = lane & (seg - 1), ppi = 32 / seg;
+        const bool has_word = kq < rem;
+        const int k = words_main + (has_word ? kq : 0);
+        const uint4 wg = __ldg(xw4 + k);
+        const uint2 sx = __ldg(xw2 + k);
+        const uint32_t sel01 = sx.x & 0xffffu, sel23 = sx.x >> 16;
+        const int wofs = (int)(sx.y & 0xffffu);
+        const uint32_t shift = sx.y >> 16;
+        uint8_t* const dcol = dst + 4 * k;
+        auto hpass = [&](int j, uint32_t (&hv)[4]) {
+            const uint32_t* p = sm_w + (j - jlo) * spitch_w + wofs;
+            const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+            const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
+            const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
+            hv[0] = __dp2a_lo(wg.x, b01, 0u);
+            hv[1] = __dp2a_hi(wg.y, b01, 0u);
+            hv[2] = __dp2a_lo(wg.z, b23, 0u);
+            hv[3] = __dp2a_hi(wg.w, b23, 0u);
+        };
+        auto row_out = [&](int y, bool on) {  // rows differ between the lanes of the warp here: no reuse of passes
+            const uint32_t ty = __ldg(ytab + y);
+            const int j0 = (int)(ty & 0xffffu);
+            const int j1 = min(j0 + 1, sh - 1);
+            uint32_t h0[4], h1[4], v[4];
+            hpass(j0, h0);
+            hpass(j1, h1);
+            const uint32_t cy1 = ty >> 16, cy0 = 256u - cy1;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = h1[j] * cy1 + (h0[j] * cy0 + (1u << 15));
+            if (on)
+                *reinterpret_cast<uint32_t*>(dcol + (uint32_t)(y * dpitch)) =
+                    __byte_perm(__byte_perm(v[0], v[1], 0x0062u), __byte_perm(v[2], v[3], 0x0062u), 0x5410u);
+        };
+        const int n_pairs = (y_end - y_begin + 1) >> 1;
+        for (int p0 = warp * ppi; p0 < n_pairs; p0 += 8 * ppi) {
+            const int y = y_begin + 2 * (p0 + sub);
+            row_out(min(y, y_end - 1), has_word && y < y_end);
+            row_out(min(y + 1, y_end - 1), has_word && y + 1 < y_end);
         }
     }
     __syncthreads();  // the band's pixels are visible to this CTA
