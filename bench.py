@@ -1,28 +1,29 @@
 #!/usr/bin/env python
-"""bench.py — ORB extract+match frames/s on BASELINE.json's config 2 (streaming 640x480 TUM-shape
-sequence, 1000 kp/frame, frame-to-frame windowed matching), one rank per B200.
+"""bench.py — ORB extract+match frames/s (640x480, 1000 kp) with the REFERENCE'S OWN matcher on both arms:
+brute-force Hamming 2-NN + ratio 0.8 (core/feature/orb_matcher.cpp:22-36), one rank per B200.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-A "step" is one pass of the hot path (8-level pyramid, FAST+NMS, retainBest, Harris, IC angle,
-7x7 blur, rBRIEF, windowed Hamming 2-NN + ratio test) over one chunk of `--batch` consecutive
-frames of a synthetic sequence.  Three numbers come out of one run:
+A "step" is one pass of the hot path (8-level pyramid, FAST+NMS, retainBest, Harris, IC angle, 7x7 blur,
+rBRIEF, Hamming 2-NN + ratio test of every frame against its predecessor) over `--chunks` consecutive
+chunks of `--batch` frames of a synthetic streaming sequence (default 8 x 128 = 1024 frames per step).
 
-  value  frames/s with the chunk already resident in HBM (vxorb_resident_run), CUDA events on the
-         library's own streams, max over ranks.  The K passes are pipelined over the handle's three
-         slots exactly as the streaming path pipelines chunks (pass i+1 waits for pass i's last-frame
-         descriptors before its first pair is matched); nothing crosses PCIe.  The working set of a chunk (pyramid + blurred
-         pyramid + lists, ~2.3 MB/frame) is larger than the 126 MB L2 at the default batch.
-  e2e    the same metric through the public streaming call (vxorb_track_submit/_wait) with pinned
-         HOST frames in and keypoints, descriptors and matches copied back to the host inside the
-         timed region, pipelined over the handle's slots.
+  value  frames/s with the chunk already resident in HBM (vxorb_resident_run), CUDA events on the library's
+         own streams, max over ranks.  Passes are pipelined over the handle's three slots exactly as the
+         streaming path pipelines chunks; nothing crosses PCIe.  The working set of a chunk (pyramid + blurred
+         pyramid + lists, ~2.3 MB/frame) is larger than the 126 MB L2.
+  e2e    the same metric through the public streaming call (vxorb_track_submit/_wait) with pinned HOST frames
+         in and keypoints, descriptors and matches copied back to the host inside the timed region.
   roofline / stages: per-stage CUDA-event times of a separate, serial instrumented pass over the same chunk,
          each against its algorithmic bytes and MEASURED_PEAKS.json.
+  windowed: the same two numbers with BASELINE config 2's windowed (r = 32 px) matcher, as extra keys.
+  per_call / c3 / c4: BASELINE configs 1, 3 and 4 measured in the same run (rank 0, N = 1 only).
+  parity_checked: after the timed region, frames of the resident batch (keypoints, descriptors, match rows)
+         are compared with the CPU oracle bit for bit; a mismatch aborts the run.
 
-`--impl reference` times the reference's own CPU path (cv2 = the OpenCV the reference's
-ORBExtractor/ORBMatcher wrap, core/feature/orb_extractor.cpp:13, orb_matcher.cpp:22-36) on the
-host cores; if cv2 is missing it falls back to the C oracle port.  No file under /root/reference
-is read at run time.
+`--impl reference` times the reference's own CPU path (cv2 = the OpenCV the reference's ORBExtractor /
+ORBMatcher wrap, orb_extractor.cpp:13, orb_matcher.cpp:22-36) on the host cores, same workload and matcher;
+if cv2 is missing it falls back to the C oracle port.  No file under /root/reference is read at run time.
 """
 import argparse
 import json
@@ -39,11 +40,19 @@ if ROOT not in sys.path:
 
 W, H, NKP, RADIUS = 640, 480, 1000, 32.0
 METRIC = "ORB extract+match frames/s (640x480, 1k kp)"
-WORKLOAD = "config2: streaming 640x480 TUM-shape synthetic sequence, 1000 kp/frame, 8 levels x1.2, " \
-           "frame-to-frame windowed (r=32 px) Hamming 2-NN + ratio 0.8"
+WORKLOAD = "streaming 640x480 TUM-shape synthetic sequence, 1000 kp/frame, 8 levels x1.2, frame-to-frame " \
+           "brute-force Hamming 2-NN + ratio 0.8 (the reference's matcher, orb_matcher.cpp:22-36)"
+
+
+def make_config(batch, chunks):
+    """Identical on both arms (the driver compares it)."""
+    return {"workload": WORKLOAD, "matcher": "bruteforce", "frames_per_step_per_gpu": batch * chunks,
+            "chunk_frames": batch, "chunks_per_step": chunks,
+            "sharding": "one independent sequence per GPU, no collective",
+            "l2_policy": f"inputs larger than L2: {batch} frames x ~2.3 MB working set per chunk"}
+
 
 # ---- algorithmic bytes per frame (SURVEY.md 8d staged-minimum model), computed from the geometry ----
-
 
 def level_sizes(w=W, h=H, n_levels=8, sf=1.2):
     sf = float(np.float32(sf))
@@ -54,8 +63,8 @@ def level_sizes(w=W, h=H, n_levels=8, sf=1.2):
     return out
 
 
-def algorithmic_bytes(n_kp=NKP):
-    px = [a * b for a, b in level_sizes()]
+def algorithmic_bytes(n_kp=NKP, w=W, h=H):
+    px = [a * b for a, b in level_sizes(w, h)]
     s = sum(px)
     return {
         "pyramid": (s - px[-1]) + (s - px[0]),   # read every source level + write levels 1..7
@@ -65,6 +74,9 @@ def algorithmic_bytes(n_kp=NKP):
         "describe": n_kp * 512 + n_kp * (32 + 24),  # 512 gathers + descriptor + keypoint record
         "match": 0,                               # integer-pipe bound: popc ops, not bytes
     }
+
+
+EXTRACT_STAGES = ("pyramid", "fast", "select", "blur", "describe")
 
 
 def peaks():
@@ -110,7 +122,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._stop.wait(0.004)
 
     def start(self):
         if self._nv:
@@ -134,7 +146,7 @@ def cpu_reference(frames, seconds_target, threads, windowed):
     """Times cv::ORB::detectAndCompute + BFMatcher.knnMatch(k=2) + ratio (orb_extractor.cpp:13,
     orb_matcher.cpp:22-36) over consecutive frames of the sequence: `threads` workers, each with
     OpenCV's internal pool set to 1 thread, take disjoint sub-sequences (frame-level parallelism is
-    how the CPU path uses many cores: cv::ORB itself is serial).  Returns (frames/s, frames, s)."""
+    how the CPU path uses many cores: cv::ORB itself is serial).  Returns (frames/s, frames, s, kind)."""
     import concurrent.futures as cf
     try:
         import cv2
@@ -216,8 +228,9 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / max(1, args.steps),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "reference_path": "cv2 (OpenCV) ORB_create(1000,1.2,8).detectAndCompute + "
-                   "BFMatcher(NORM_HAMMING).knnMatch(k=2) + ratio 0.8, brute force as orb_matcher.cpp:22-36"},
+        "config": make_config(args.batch, args.chunks),
+        "reference_path": "cv2 (OpenCV) ORB_create(1000,1.2,8).detectAndCompute + BFMatcher(NORM_HAMMING).knnMatch(k=2) + "
+                          "ratio 0.8, brute force as orb_matcher.cpp:22-36; each step is a bounded sample of the workload",
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": thr, "kind": kind,
                          "sample": f"{total_n} frames of the synthetic 640x480 sequence in {total_t:.1f} s, "
                                    f"{thr} worker threads x 1 OpenCV thread"},
@@ -229,18 +242,207 @@ def run_reference(args, rank, world):
 
 # ---- our arm -------------------------------------------------------------------------------------
 
-def run_ours(args, rank, world, local_rank):
-    import torch
-    import torch.distributed as dist
+def check_parity(vx, res, seq, radius, frames_to_check):
+    """The fetched resident result against the CPU oracle (test infrastructure used as the checker only):
+    keypoints, descriptors and the match rows of frame f against its predecessor (frame 0: the carried last
+    frame of the previous pass).  Raises on any difference."""
+    import oracle
+    B = len(seq)
+    need = sorted({f for f in frames_to_check} | {(f - 1) % B for f in frames_to_check})
+    ext = {f: oracle.orb_extract(seq[f]) for f in need}
+    for f in frames_to_check:
+        kp, desc, m = res[f]
+        okp, odesc = ext[f]
+        pk, pd = ext[(f - 1) % B]
+        for name in ("x", "y", "response", "angle", "octave"):
+            if not np.array_equal(kp[name], okp[name]):
+                raise SystemExit(f"bench.py: PARITY FAILURE frame {f} keypoint field {name}")
+        if not np.array_equal(desc, odesc):
+            raise SystemExit(f"bench.py: PARITY FAILURE frame {f} descriptors")
+        win = radius > 0
+        om = oracle.match(pd, odesc, 0.8, np.stack([pk["x"], pk["y"]], 1) if win else None,
+                          np.stack([okp["x"], okp["y"]], 1) if win else None, radius)
+        if not (np.array_equal(m["query_idx"], om["query_idx"]) and np.array_equal(m["train_idx"], om["train_idx"]) and
+                np.array_equal(m["distance"], om["distance"])):
+            raise SystemExit(f"bench.py: PARITY FAILURE frame {f} match rows (radius {radius})")
+    return {"frames": list(frames_to_check), "radius": radius, "fields": "keypoints, descriptors, match rows",
+            "oracle": "oracle/orb_oracle.c (pinned by the cv2 golden vectors)"}
 
+
+def median_ms(fn, n, warm=10):
+    for _ in range(warm):
+        fn()
+    t = np.empty(n)
+    for i in range(n):
+        t0 = time.perf_counter()
+        fn()
+        t[i] = time.perf_counter() - t0
+    return float(np.median(t) * 1e3), float(np.min(t) * 1e3)
+
+
+def cv2_per_call(a, b, n_features, train=None, n=30):
+    """cv2 single-thread medians for the same inputs (detectAndCompute; knnMatch + ratio)."""
+    try:
+        import cv2
+    except ImportError:
+        return None
+    cv2.setNumThreads(1)
+    orb = cv2.ORB_create(n_features, 1.2, 8)
+    bf = cv2.BFMatcher(cv2.NORM_HAMMING)
+    _, da = orb.detectAndCompute(a, None)
+    _, db = orb.detectAndCompute(b, None)
+    t = db if train is None else train
+
+    def m():
+        return sum(1 for r in bf.knnMatch(da, t, 2) if len(r) >= 2 and r[0].distance < 0.8 * r[1].distance)
+    ext_ms, _ = median_ms(lambda: orb.detectAndCompute(a, None), n, warm=3)
+    match_ms, _ = median_ms(m, max(3, n // 6) if train is not None else n, warm=1)
+    return {"detectAndCompute_ms": ext_ms, "knnMatch_ratio_ms": match_ms, "threads": 1, "cv2": cv2.__version__}
+
+
+def bench_per_call(vx, peak):
+    """BASELINE config 1: what Tracking::ProcessFrame pays per frame through the drop-in entry points
+    (tracking.cpp:42 Extract, :289 Match): one 640x480 pair, host buffers in and out, synchronous calls."""
+    from visionx_slam_b200.synth import synth_scene
+    a = synth_scene(W, H, 11)
+    b = np.ascontiguousarray(np.roll(a, (3, 5), axis=(0, 1)))
+    out = {"config": "config1: one synthetic 640x480 pair (B = roll(A,(3,5))), 1000 kp, host buffers, synchronous calls"}
+    with vx.VxOrb(max_batch=1) as h1:
+        cap = h1.kp_cap
+        kp = np.zeros(cap, vx.KEYPOINT_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        mt = np.zeros(cap, vx.MATCH_DTYPE)
+        na = h1.extract_into(a, kp, desc)
+        da = desc[:na].copy()
+        nb = h1.extract_into(b, kp, desc)
+        db = desc[:nb].copy()
+        out["extract_ms"], out["extract_ms_min"] = median_ms(lambda: h1.extract_into(a, kp, desc), 300)
+        out["match_ms"], out["match_ms_min"] = median_ms(lambda: h1.match_into(da, db, mt), 300)
+        # device-resident descriptors: Extract keeps its result on the GPU under an id, Match takes two ids
+        ida = h1.extract_into(a, kp, desc, want_id=True)[1]
+        idb = h1.extract_into(b, kp, desc, want_id=True)[1]
+        nm_ids = h1.match_ids_into(ida, idb, mt)
+        nm_host = h1.match_into(da, db, mt)
+        assert nm_ids == nm_host, "match by ids differs from match by host descriptors"
+        out["match_ids_ms"], out["match_ids_ms_min"] = median_ms(lambda: h1.match_ids_into(ida, idb, mt), 300)
+
+        def frame():
+            i = h1.extract_into(b, kp, desc, want_id=True)[1]
+            h1.match_ids_into(ida, i, mt)
+        out["extract_plus_match_ms"], _ = median_ms(frame, 300)
+        out["keypoints"], out["matches"] = int(na), int(nm_host)
+        ab = sum(v for k, v in algorithmic_bytes(na).items() if k in EXTRACT_STAGES)
+        out["extract_frac_of_hbm_peak"] = ab / (out["extract_ms"] * 1e-3) / 1e9 / peak
+    out["cv2_single_thread"] = cv2_per_call(a, b, NKP)
+    return out
+
+
+def bench_config(vx, peak, popc_peak, w, h, n_kp, batch, radius, steps, label, bytes_model):
+    """Resident-batch extraction + temporal matching throughput of another BASELINE geometry."""
+    from visionx_slam_b200.synth import synth_sequence
+    seq = synth_sequence(w, h, batch, seed=404)
+    out = {"config": label, "batch": batch}
+    with vx.VxOrb(n_features=n_kp, max_width=w, max_height=h, max_batch=batch, max_train=max(16384, 2 * n_kp)) as hc:
+        hc.resident_upload(seq)
+        for _ in range(3):
+            hc.resident_run(radius)
+        hc.sync()
+        hc.timer_begin()
+        for _ in range(steps):
+            hc.resident_run(radius)
+        ms = hc.timer_end()
+        out["frames_per_s_resident"] = batch * steps / (ms * 1e-3)
+        hc.stage_times_reset(True)
+        for _ in range(steps):
+            hc.resident_run(radius)
+        st = hc.stage_times()
+        hc.stage_times_reset(False)
+        res = hc.resident_fetch()
+        nk = float(np.mean([len(r[0]) for r in res]))
+        ext_ms = sum(st[s][0] for s in EXTRACT_STAGES) / steps
+        out["keypoints_per_frame"] = nk
+        out["extract_ms_per_frame_serial"] = ext_ms / batch
+        out["algorithmic_bytes_per_frame"] = bytes_model
+        out["extraction_frac_of_hbm_peak"] = bytes_model * batch / (ext_ms * 1e-3) / 1e9 / peak
+        out["stages_ms_per_batch"] = {s: st[s][0] / steps for s in st}
+        out["match"] = {"radius": radius, "ms_per_pair": st["match"][0] / steps / batch}
+    return out, seq, res
+
+
+def bench_c3(vx, peak, popc_peak):
+    """BASELINE config 3: 1241x376, 2000 kp — batched extraction with temporal windowed matching (resident), and
+    the left->right box-masked stereo match of one pair through the host-buffer call."""
+    from visionx_slam_b200.synth import synth_stereo_pair
+    out, _, _ = bench_config(vx, peak, popc_peak, 1241, 376, 2000, 32, 64.0, 5,
+                             "config3: KITTI-shape 1241x376, 2000 kp/frame, temporal windowed (r=64) matching, batch 32 resident",
+                             7853539)
+    left, right = synth_stereo_pair(1241, 376, 31)
+    with vx.VxOrb(n_features=2000, max_width=1241, max_height=376, max_batch=2, max_train=4096) as hs:
+        (kl, dl), (kr, dr) = hs.extract_batch([left, right])
+        qxy, txy = np.stack([kl["x"], kl["y"]], 1), np.stack([kr["x"], kr["y"]], 1)
+        box = np.float32([0.0, 128.0, -2.0, 2.0])
+        m = hs.match_boxed(dl, dr, qxy, txy, box)
+        ms, ms_min = median_ms(lambda: hs.match_boxed(dl, dr, qxy, txy, box), 100)
+        pair_ms, _ = median_ms(lambda: hs.extract_batch([left, right]), 50)
+        out["stereo"] = {"left_right_boxed_match_ms": ms, "left_right_boxed_match_ms_min": ms_min,
+                         "matches": int(len(m)), "extract_stereo_pair_ms": pair_ms,
+                         "box": "0 <= xl - xr <= 128, |yl - yr| <= 2", "path": "host buffers, synchronous calls"}
+    return out
+
+
+def bench_c4(vx, peak, popc_peak):
+    """BASELINE config 4: 1920x1080, 4000 kp, brute-force match of the frame against a 16 384-row local map."""
+    out, seq, res = bench_config(vx, peak, popc_peak, 1920, 1080, 4000, 8, 0.0, 4,
+                                 "config4: 1920x1080, 4000 kp/frame, batch 8 resident; frame vs 16 384-descriptor map brute force",
+                                 32133669)
+    rng = np.random.default_rng(0)
+    train = rng.integers(0, 256, (16384, 32), dtype=np.uint8)
+    q = res[1][1]
+    k = min(len(q), 2000)
+    train[:k] = q[:k] ^ (rng.integers(0, 256, (k, 32), dtype=np.uint8) & rng.integers(0, 256, (k, 32), dtype=np.uint8)
+                         & rng.integers(0, 256, (k, 32), dtype=np.uint8))  # the frame's own rows, ~1/8 of the bits flipped
+    with vx.VxOrb(n_features=4000, max_width=1920, max_height=1080, max_batch=1, max_train=16384) as h4:
+        cap = h4.kp_cap
+        kp = np.zeros(cap, vx.KEYPOINT_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        mt = np.zeros(cap, vx.MATCH_DTYPE)
+        n = h4.extract_into(seq[1], kp, desc)
+        out["extract_call_ms"], _ = median_ms(lambda: h4.extract_into(seq[1], kp, desc), 60)
+        qd = desc[:n].copy()
+        nm = h4.match_into(qd, train, mt)
+        out["map_match_call_ms"], _ = median_ms(lambda: h4.match_into(qd, train, mt), 60)
+        # the map stays on the device between frames (it changes by a few rows per keyframe): resident set + frame id
+        sid = h4.set_upload(train)
+        fid = h4.extract_into(seq[1], kp, desc, want_id=True)[1]
+        assert h4.match_ids_into(fid, sid, mt) == nm
+        out["map_match_resident_call_ms"], _ = median_ms(lambda: h4.match_ids_into(fid, sid, mt), 100)
+        h4.stage_times_reset(True)
+        reps = 20
+        for _ in range(reps):
+            h4.match_ids_into(fid, sid, mt)
+        ms = h4.stage_times()["match"][0] / reps
+        h4.stage_times_reset(False)
+        pairs = float(n) * 16384.0
+        out["map_match"] = {"nq": int(n), "nt": 16384, "matches": int(nm), "device_ms": ms,
+                            "popc_issued_per_s": pairs * 4 / (ms * 1e-3), "popc_algorithmic_per_s": pairs * 8 / (ms * 1e-3),
+                            "frac_of_popc_peak_issued_4_per_pair": pairs * 4 / (ms * 1e-3) / popc_peak,
+                            "frac_of_popc_peak_algorithmic_8_per_pair": pairs * 8 / (ms * 1e-3) / popc_peak,
+                            "popc_peak_per_s_measured": popc_peak,
+                            "note": "Harley-Seal distance: the kernel issues 4 POPC per (query, train) pair where the "
+                                    "SURVEY 8d model counts 8"}
+    return out
+
+
+def run_ours(args, rank, world, local_rank):
     import visionx_slam_b200 as vx
+    from visionx_slam_b200.shard import (aggregate_throughput, host_barrier, init_host_group, max_over_ranks,
+                                         sequence_seed, shard_sequences)
     from visionx_slam_b200.synth import synth_sequence
 
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device — the ORB path has no CPU fallback")
-    torch.cuda.set_device(local_rank)
+    # torch.distributed (gloo, CPU tensors) carries only the barrier and the max over ranks: the data path has no
+    # collective (SURVEY.md 8e), so no NCCL communicator is created
+    init_host_group(world)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         # several ranks share the host: keep this rank's threads (and, by first touch, its pinned
         # staging buffers) on the CPUs NVML reports as local to its GPU
         try:
@@ -250,158 +452,178 @@ def run_ours(args, rank, world, local_rank):
         except Exception as e:  # no NVML / no permission: run unbound
             sys.stderr.write(f"bench.py: CPU affinity not set ({e!r})\n")
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    B = args.batch
+    B, CH = args.batch, args.chunks
+    passes = args.steps * CH
     # every rank owns an independent sequence (BASELINE config 5: sequences sharded across GPUs)
-    from visionx_slam_b200.shard import aggregate_throughput, max_over_ranks, sequence_seed, shard_sequences
     my_sequence = shard_sequences(world, world, rank)[0]  # one sequence per rank
     base = synth_sequence(W, H, min(B, 32), seed=sequence_seed(2026, my_sequence))
     reps = (B + len(base) - 1) // len(base)
     # forward-backward tiling keeps consecutive frames 1-3 px apart across the repeats
     seq = np.concatenate([base if r % 2 == 0 else base[::-1] for r in range(reps)])[:B]
 
-    h = vx.VxOrb(device_id=local_rank, max_width=W, max_height=H, max_batch=B)
+    h = vx.VxOrb(device_id=local_rank, max_width=W, max_height=H, max_batch=B)  # raises without a B200: no CPU fallback
     cap = h.kp_cap
-    lib_launches0 = h.launch_count()
 
-    # -------- value: chunk resident in HBM --------------------------------------------------------
+    def barrier():
+        h.sync()
+        host_barrier(world)
+        h.sync()
+
+    def resident_timed(radius, n_warm, n_timed):
+        for _ in range(n_warm):
+            h.resident_run(radius)
+        barrier()
+        l0 = h.launch_count()
+        h.timer_begin()
+        for _ in range(n_timed):
+            h.resident_run(radius)
+        ms = h.timer_end()
+        return ms, h.launch_count() - l0
+
+    # -------- value: chunk resident in HBM, brute-force matcher ------------------------------------
     h.resident_upload(seq)
-    for _ in range(args.warmup):
-        h.resident_run(RADIUS)
-    h.sync()
-    barrier()
     sampler = ClockSampler(local_rank)
+    barrier()
     sampler.start()
-    l0 = h.launch_count()
-    h.timer_begin()
-    for _ in range(args.steps):
-        h.resident_run(RADIUS)
-    ms_resident = h.timer_end()
-    launches_timed = h.launch_count() - l0
+    ms_resident, launches_timed = resident_timed(0.0, args.warmup * CH, passes)
     barrier()
     # instrumented pass over the same resident chunk: CUDA events around every kernel family on the
     # library's stream.  It runs the stages strictly one after another (the production schedule above lets
-    # the blur run beside FAST + select on a side stream), so a stage's time is that stage alone; `value`
-    # comes from the un-instrumented loop above, the roofline and the stage table from this one.
+    # the blur run beside FAST + select on a side stream and pipelines passes over the slots), so a stage's
+    # time is that stage alone; `value` comes from the un-instrumented loop above, the roofline and the stage
+    # table from this one.
+    n_instr = max(4, min(passes, 24))
     h.stage_times_reset(True)
     h.timer_begin()
-    for _ in range(args.steps):
-        h.resident_run(RADIUS)
+    for _ in range(n_instr):
+        h.resident_run(0.0)
     ms_serial = h.timer_end()
     stages = h.stage_times()
     h.stage_times_reset(False)
-    # the reference's own matcher is brute force (orb_matcher.cpp:22-25): the same instrumented pass with
-    # radius 0 gives the match stage of the all-pairs kernel, reported against the measured popcount peak
-    bf_steps = max(2, min(5, args.steps))
     h.resident_run(0.0)
-    h.sync()
-    h.stage_times_reset(True)
-    for _ in range(bf_steps):
-        h.resident_run(0.0)
-    h.sync()
-    stages_bf = h.stage_times()
-    h.stage_times_reset(False)
-    h.resident_run(RADIUS)  # leave the windowed result resident for the fetch below
-    barrier()
+    h.resident_run(0.0)  # second pass: frame 0 is matched against the carried last frame
     res = h.resident_fetch()
     n_kp = float(np.mean([len(r[0]) for r in res]))
-    n_match = float(np.mean([len(r[2]) for r in res[1:]])) if B > 1 else 0.0
+    n_match = float(np.mean([len(r[2]) for r in res]))
+    parity = None
+    if rank == 0:
+        parity = [check_parity(vx, res, seq, 0.0, [0, 1, B // 2, B - 1])]
 
     # -------- e2e: pinned host frames in, keypoints + descriptors + matches out ------------------
     slots = h.track_slots()
-    chunks = max(1, min(slots, 3))  # chunks in flight: with 3 the H2D of chunk i+2 hides behind the kernels of chunk i
-    pin_in = [vx.PinnedArray((B, H, W), np.uint8) for _ in range(chunks)]
+    inflight_max = max(1, min(slots, 3))  # chunks in flight: with 3 the H2D of chunk i+2 hides behind the kernels of chunk i
+    pin_in = [vx.PinnedArray((B, H, W), np.uint8) for _ in range(inflight_max)]
     for p in pin_in:
         p.array[:] = seq
     outs = [dict(kp=vx.PinnedArray((B, cap), vx.KEYPOINT_DTYPE), desc=vx.PinnedArray((B, cap, 32), np.uint8),
                  nk=vx.PinnedArray((B,), np.int32), mt=vx.PinnedArray((B, cap), vx.MATCH_DTYPE),
-                 nm=vx.PinnedArray((B,), np.int32)) for _ in range(chunks)]
+                 nm=vx.PinnedArray((B,), np.int32)) for _ in range(inflight_max)]
 
-    def e2e_steps(n):
+    def e2e_chunks(n, radius):
         inflight = []
         for i in range(n):
-            k = i % chunks
-            if len(inflight) == chunks:
+            k = i % inflight_max
+            if len(inflight) == inflight_max:
                 h.track_wait(inflight.pop(0))
             o = outs[k]
-            inflight.append(h.track_submit(pin_in[k].array, RADIUS, o["kp"].array, o["desc"].array, o["nk"].array,
+            inflight.append(h.track_submit(pin_in[k].array, radius, o["kp"].array, o["desc"].array, o["nk"].array,
                                            o["mt"].array, o["nm"].array))
         for s in inflight:
             h.track_wait(s)
 
-    h.track_reset()
-    e2e_steps(max(args.warmup, chunks))
-    barrier()
-    h.timer_begin()
-    t0 = time.perf_counter()
-    e2e_steps(args.steps)
-    ms_e2e_dev = h.timer_end()
-    ms_e2e_wall = 1e3 * (time.perf_counter() - t0)
+    def e2e_timed(radius, n_warm, n_timed):
+        h.track_reset()
+        e2e_chunks(max(n_warm, inflight_max), radius)
+        barrier()
+        h.timer_begin()
+        t0 = time.perf_counter()
+        e2e_chunks(n_timed, radius)
+        dev = h.timer_end()
+        wall = 1e3 * (time.perf_counter() - t0)
+        return dev, wall
+
+    ms_e2e_dev, ms_e2e_wall = e2e_timed(0.0, args.warmup * CH, passes)
     ms_e2e = max(ms_e2e_dev, ms_e2e_wall)
     barrier()
     clocks = sampler.stop()
-    h2d = int(B * W * H)
-    d2h = int(B * (cap * (20 + 32 + 12) + 8) + 16)
+    h2d_chunk = int(B * W * H)
+    d2h_chunk = int(B * (cap * (20 + 32 + 12) + 8) + 16)
     e2e_nkp = float(np.mean(outs[0]["nk"].array))
+    if rank == 0:  # the streamed result of the last chunk written to outs[k] is the same sequence: check it too
+        k = (passes - 1) % inflight_max
+        o = outs[k]
+        streamed = [(o["kp"].array[i, :o["nk"].array[i]], o["desc"].array[i, :o["nk"].array[i]],
+                     o["mt"].array[i, :o["nm"].array[i]]) for i in range(B)]
+        parity.append(dict(check_parity(vx, streamed, seq, 0.0, [0, B - 1]), path="vxorb_track_submit (e2e)"))
+
+    # -------- BASELINE config 2's windowed matcher, as extra keys ----------------------------------
+    win_passes = max(CH, min(passes, 40))
+    ms_res_win, _ = resident_timed(RADIUS, 3, win_passes)
+    h.stage_times_reset(True)
+    for _ in range(4):
+        h.resident_run(RADIUS)
+    stages_win = h.stage_times()
+    h.stage_times_reset(False)
+    h.resident_run(RADIUS)
+    h.resident_run(RADIUS)
+    res_win = h.resident_fetch()
+    if rank == 0:
+        parity.append(check_parity(vx, res_win, seq, RADIUS, [0, B - 1]))
+    win_dev, win_wall = e2e_timed(RADIUS, 3, win_passes)
+    ms_e2e_win = max(win_dev, win_wall)
 
     popc_peak = h.measure_popc_rate()
 
     # -------- max over ranks ----------------------------------------------------------------------
-    ms_resident_max, ms_e2e_max = max_over_ranks([ms_resident, ms_e2e], world, device="cuda")
-    value = aggregate_throughput(B * args.steps, ms_resident_max, world)
-    e2e_value = aggregate_throughput(B * args.steps, ms_e2e_max, world)
+    ms_resident_max, ms_e2e_max, ms_res_win_max, ms_e2e_win_max = max_over_ranks(
+        [ms_resident, ms_e2e, ms_res_win, ms_e2e_win], world)
+    value = aggregate_throughput(B * passes, ms_resident_max, world)
+    e2e_value = aggregate_throughput(B * passes, ms_e2e_max, world)
 
     # -------- roofline of the dominant extraction kernel family, per-stage table ------------------
     peak, peak_src = peaks()
     ab = algorithmic_bytes(int(round(n_kp)))
     table = {}
     for s, (ms, n_launch) in stages.items():
-        per_step_ms = ms / args.steps
-        e = {"ms_per_step": per_step_ms, "launches_per_step": n_launch / args.steps,
-             "share": ms / ms_serial if ms_serial > 0 else None}  # of the serial (instrumented) step
+        e = {"ms_per_chunk": ms / n_instr, "launches_per_chunk": n_launch / n_instr,
+             "share": ms / ms_serial if ms_serial > 0 else None}  # of the serial (instrumented) pass
         if ab[s] > 0 and ms > 0:
             e["algorithmic_bytes_per_frame"] = ab[s]
-            e["achieved_gbs"] = ab[s] * B * args.steps / (ms * 1e-3) / 1e9
+            e["achieved_gbs"] = ab[s] * B * n_instr / (ms * 1e-3) / 1e9
             e["frac_of_hbm_peak"] = e["achieved_gbs"] / peak
         if s == "match" and ms > 0:
-            pairs = (B - 1 + 1) * args.steps  # frame 0 matches the carried last frame from step 2 on
-            popc = n_kp * n_kp * 8 * pairs
-            e["allpairs_equiv_popc_per_s"] = popc / (ms * 1e-3)
+            pairs = float(B) * n_instr * n_kp * n_kp  # (query, train) pairs evaluated: all pairs, as the reference's matcher
+            e["bound"] = "integer pipe: POPC 16 lanes/clk/SM (measured with vxorb_measure_popc_rate)"
             e["popc_peak_per_s_measured"] = popc_peak
-            e["frac_of_popc_peak_allpairs_equiv"] = e["allpairs_equiv_popc_per_s"] / popc_peak
-            ms_bf = stages_bf["match"][0]
-            if ms_bf > 0:
-                popc_bf = n_kp * n_kp * 8 * B * bf_steps  # 8 x 32-bit popcounts per (query, train) pair, all pairs
-                e["bruteforce"] = {"ms_per_step": ms_bf / bf_steps, "popc_per_s": popc_bf / (ms_bf * 1e-3),
-                                   "frac_of_popc_peak": popc_bf / (ms_bf * 1e-3) / popc_peak,
-                                   "note": "all-pairs 2-NN of the same 128 pairs (radius 0), the matcher the reference "
-                                           "itself runs; bound: integer pipe, POPC 16 lanes/clk/SM"}
+            e["popc_algorithmic_per_s"] = pairs * 8 / (ms * 1e-3)   # 8 x popc.b32 per pair
+            e["popc_issued_per_s"] = pairs * 4 / (ms * 1e-3)        # Harley-Seal: the kernel issues 4 per pair
+            e["frac_of_popc_peak_algorithmic_8_per_pair"] = e["popc_algorithmic_per_s"] / popc_peak
+            e["frac_of_popc_peak_issued_4_per_pair"] = e["popc_issued_per_s"] / popc_peak
+            ms_w = stages_win["match"][0]
+            e["windowed_r32_ms_per_chunk"] = ms_w / 4
         table[s] = e
     hbm_stages = [s for s in ("pyramid", "fast", "blur", "describe") if stages[s][0] > 0]
     dom = max(hbm_stages, key=lambda s: stages[s][0])
     dom_ms, dom_launches = stages[dom]
+    ext_ms = sum(stages[s][0] for s in EXTRACT_STAGES)
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": table[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
         "frac": table[dom]["achieved_gbs"] / peak,
         "traffic": TRAFFIC.get(dom) if B == 128 else None,  # the ncu capture was taken at batch 128
         "peak_source": peak_src,
-        "bytes_per_launch": ab[dom] * B / max(1.0, dom_launches / args.steps),
+        "bytes_per_launch": ab[dom] * B / max(1.0, dom_launches / n_instr),
         "avg_launch_ms": dom_ms / max(1, dom_launches),
         "extraction_total": {
             "algorithmic_bytes_per_frame": sum(ab[s] for s in hbm_stages),
-            "achieved_gbs": sum(ab[s] for s in hbm_stages) * B * args.steps /
-            (sum(stages[s][0] for s in ("pyramid", "fast", "select", "blur", "describe")) * 1e-3) / 1e9,
+            "achieved_gbs": sum(ab[s] for s in hbm_stages) * B * n_instr / (ext_ms * 1e-3) / 1e9,
+            "ms_per_chunk_serial": ext_ms / n_instr,
         },
     }
     roofline["extraction_total"]["frac"] = roofline["extraction_total"]["achieved_gbs"] / peak
 
     line = None
     if rank == 0:
-        cpu = None
+        cpu = per_call = c3 = c4 = None
         if world == 1 and not args.no_cpu_baseline:
             thr = host_threads()
             fps, n, dt, kind = cpu_reference(list(base), 12.0, thr, windowed=False)
@@ -412,29 +634,39 @@ def run_ours(args, rank, world, local_rank):
             if kind == "reference":
                 fps1, n1, dt1, _ = cpu_reference(list(base), 4.0, 1, windowed=False)
                 cpu["single_thread_value"] = fps1
+        if world == 1 and not args.no_configs:
+            per_call = bench_per_call(vx, peak)
+            c3 = bench_c3(vx, peak, popc_peak)
+            c4 = bench_c4(vx, peak, popc_peak)
         line = {
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_resident_max / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_frames_per_step_per_gpu": B, "keypoints_per_frame": n_kp,
-                       "matches_per_frame": n_match, "sharding": "one independent sequence per GPU, no collective",
-                       "l2_policy": f"inputs larger than L2: {B} frames x ~2.3 MB working set per step"},
-            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e_max / args.steps, "ms_device_events": ms_e2e_dev / args.steps,
-                    "ms_wall": ms_e2e_wall / args.steps, "chunks_in_flight": chunks, "keypoints_per_frame": e2e_nkp,
+            "config": make_config(B, CH),
+            "observed": {"keypoints_per_frame": n_kp, "matches_per_frame": n_match},
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d_chunk * CH,
+                    "d2h_bytes_per_step": d2h_chunk * CH, "ms_per_step": ms_e2e_max / args.steps,
+                    "ms_device_events": ms_e2e_dev / args.steps, "ms_wall": ms_e2e_wall / args.steps,
+                    "chunks_in_flight": inflight_max, "keypoints_per_frame": e2e_nkp,
                     # host->device link rate the streaming path sustained (this rank); a PCIe Gen5 x16 link tops
                     # out near 52-55 GB/s with the D2H running beside it (scratch/h2d_test.cu), which caps e2e
-                    "h2d_gbs": h2d / (ms_e2e / args.steps * 1e-3) / 1e9},
+                    "h2d_gbs": h2d_chunk * passes / (ms_e2e * 1e-3) / 1e9,
+                    "d2h_gbs": d2h_chunk * passes / (ms_e2e * 1e-3) / 1e9},
             "gpu_launches": int(launches_timed),
-            "schedule": {"ms_per_step_overlapped": ms_resident / args.steps, "ms_per_step_serial_instrumented": ms_serial / args.steps,
+            "parity_checked": True, "parity": parity,
+            "windowed": {"note": "BASELINE config 2's matcher (square window r = 32 px, cv knnMatch(mask)) instead of brute force",
+                         "value": aggregate_throughput(B * win_passes, ms_res_win_max, world),
+                         "e2e": aggregate_throughput(B * win_passes, ms_e2e_win_max, world),
+                         "ms_per_chunk": ms_res_win_max / win_passes, "unit": "frames/s"},
+            "schedule": {"ms_per_chunk_pipelined": ms_resident / passes, "ms_per_chunk_serial_instrumented": ms_serial / n_instr,
                          "note": "value is timed on the production schedule: passes pipelined over the handle's 3 slots, the blur on "
                                  "a side stream beside FAST + select; the stage table and the roofline come from a serial "
                                  "pass on one stream with events around every stage"},
             "roofline": roofline, "stages": table, "cpu_baseline": cpu, "clocks": clocks,
+            "per_call": per_call, "c3": c3, "c4": c4,
         }
     h.close()
-    if world > 1:
-        dist.destroy_process_group()
+    host_barrier(world)
     return json.dumps(line) if line is not None else None
 
 
@@ -457,16 +689,18 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=128, help="frames per step per GPU")
+    ap.add_argument("--batch", type=int, default=128, help="frames per chunk (one vxorb_track_submit / resident pass)")
+    ap.add_argument("--chunks", type=int, default=8, help="chunks per step")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the per_call / c3 / c4 keys")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version banner
-    # there) are sent to stderr for the duration of the run, the line goes to the saved descriptor
+    # stdout carries exactly ONE JSON line: libraries that write to fd 1 are sent to stderr for the duration
+    # of the run, the line goes to the saved descriptor
     sys.stdout.flush()
     real_stdout = os.dup(1)
     os.dup2(2, 1)

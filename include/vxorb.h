@@ -60,7 +60,7 @@ typedef struct vxorb_params {
     int max_height;
     int max_batch;      /* largest number of frames per batched call                            */
     int max_keypoints;  /* per-frame output capacity; 0 = n_features + n_features/4 + 64        */
-    int max_train;      /* largest train (and query) descriptor count for the match calls       */
+    int max_train;      /* sizing hint for the match scratch (it grows on demand; < 2^20 rows per side) */
 } vxorb_params;
 
 /* One keypoint as cv::ORB reports it (orb_extractor.cpp:19-24 keeps pt and response). */
@@ -138,6 +138,14 @@ int vxorb_extract_info(vxorb_handle* h, const uint8_t* img, int channels, int wi
                        size_t stride, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out,
                        vxorb_frame_info* info_out);
 
+/* vxorb_extract_info (info_out may be NULL here) that also keeps the frame's descriptors and positions ON THE
+ * DEVICE under *id_out, so that ORBMatcher::Match(last, curr) (tracking.cpp:289, 340, 863) can run on two ids
+ * without re-uploading what Extract just produced.  Every single-frame extract call takes the next entry of a
+ * ring of 8 resident frames; an id stays valid until 8 more single-frame extractions have run on the handle. */
+int vxorb_extract_id(vxorb_handle* h, const uint8_t* img, int channels, int width, int height, size_t stride,
+                     int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out,
+                     vxorb_frame_info* info_out, long long* id_out);
+
 /* `batch` independent gray frames of identical size.  frames[i] points at frame i.  Outputs are
  * frame-major: kp_out[i*kp_cap + k], desc_out[(i*kp_cap + k)*32], n_out[i]. */
 int vxorb_extract_batch(vxorb_handle* h, const uint8_t* const* frames, int batch, int width,
@@ -186,6 +194,20 @@ int vxorb_match_crosscheck(vxorb_handle* h, const uint8_t* query, int nq, const 
  * min_dist = min(100, min distance); keep distance <= max(2*min_dist, 30). */
 int vxorb_match_filtered(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train,
                          int nt, float nn_ratio, int out_cap, vxorb_match_t* out, int* n_out);
+
+/* ---- device-resident descriptor sets ------------------------------------------------------------
+ * vxorb_set_upload keeps n descriptor rows (and, optionally, their level-0 positions: xy may be NULL) on the
+ * device under *id_out until vxorb_set_free — a local map (BASELINE config 4) or a keyframe.  vxorb_match_ids
+ * matches two resident sets (frame ids from vxorb_extract_id and / or uploaded sets) with the semantics of
+ * vxorb_match (mode 0), vxorb_match_filtered (mode 1) or vxorb_match_crosscheck (mode 2); radius > 0 applies
+ * the square window of vxorb_match_windowed.  Only the matches cross the link.  An id that is unknown, freed
+ * or overwritten gives VXORB_E_INVALID: fall back to the host-buffer calls. */
+int vxorb_set_upload(vxorb_handle* h, const uint8_t* desc, const float* xy, int n, long long* id_out);
+int vxorb_set_free(vxorb_handle* h, long long id);
+/* Rows of a resident set, or VXORB_E_INVALID when the id is not (or no longer) resident. */
+int vxorb_set_size(const vxorb_handle* h, long long id);
+int vxorb_match_ids(vxorb_handle* h, long long query_id, long long train_id, float radius, float nn_ratio,
+                    int mode, int out_cap, vxorb_match_t* out, int* n_out);
 
 /* ---- streaming sequence path (BASELINE config 2): batched extract + frame-to-frame match ---
  *
@@ -275,6 +297,10 @@ int vxorb_measure_popc_rate(vxorb_handle* h, double* popc_per_s_out);
 /* ---- stage isolation (parity tests only; each runs one kernel family on host buffers) ------ */
 int vxorb_debug_resize(vxorb_handle* h, const uint8_t* src, int sw, int sh, size_t sstride,
                        uint8_t* dst, int dw, int dh, size_t dstride);
+/* The production pyramid kernel (one level, one image): band_rows = 16 runs the throughput shape of the batched
+ * path, 8 or 4 the latency shape (small batches, wide levels).  dw, dh >= 8 and scale <= ~2. */
+int vxorb_debug_resize_band(vxorb_handle* h, const uint8_t* src, int sw, int sh, size_t sstride,
+                            uint8_t* dst, int dw, int dh, size_t dstride, int band_rows);
 /* FAST-9/16 + score + strict 3x3 NMS over one image; corners with border <= x < w-border (same
  * for y), border >= 3, are written in row-major order.  cv::FastFeatureDetector == border 3. */
 int vxorb_debug_fast(vxorb_handle* h, const uint8_t* img, int width, int height, size_t stride,

@@ -24,8 +24,10 @@ int main(int argc, char** argv) {
     if (fread(hdr, 4, 4, fi) != 4) return 3;
     const int n = hdr[0], w = hdr[1], h = hdr[2], ch = hdr[3];
     std::vector<unsigned char> pix((size_t)w * h * ch);
-    std::shared_ptr<FeatureExtractor> extractor = std::make_shared<CudaORBExtractor>();  // system.cpp:15
-    std::shared_ptr<FeatureMatcher> matcher = std::make_shared<CudaORBMatcher>();        // system.cpp:16
+    auto cuda_extractor = std::make_shared<CudaORBExtractor>();
+    std::shared_ptr<FeatureExtractor> extractor = cuda_extractor;                                       // system.cpp:15
+    std::shared_ptr<FeatureMatcher> matcher = std::make_shared<CudaORBMatcher>(cuda_extractor);         // system.cpp:16
+    std::shared_ptr<FeatureMatcher> standalone = std::make_shared<CudaORBMatcher>();  // own handle: always uploads
     std::vector<Frame::Ptr> frames;
     for (int i = 0; i < n; ++i) {
         if (fread(pix.data(), 1, pix.size(), fi) != pix.size()) return 3;
@@ -60,6 +62,14 @@ int main(int argc, char** argv) {
             const int m = pass == 0 ? matcher->Match(frames[i - 1], frames[i], matches)
                                     : cm->MatchFiltered(frames[i - 1], frames[i], matches);
             if (m != (int)matches.size()) return 6;
+            if (pass == 0) {  // the upload path of a matcher with its own handle must give the same rows
+                std::vector<cv::DMatch> again;
+                if (standalone->Match(frames[i - 1], frames[i], again) != m) return 8;
+                for (int k = 0; k < m; ++k)
+                    if (again[k].queryIdx != matches[k].queryIdx || again[k].trainIdx != matches[k].trainIdx ||
+                        again[k].distance != matches[k].distance)
+                        return 8;
+            }
             fwrite(&m, 4, 1, fo);
             for (auto& d : matches) {
                 if (d.imgIdx != 0) return 7;
@@ -69,5 +79,7 @@ int main(int argc, char** argv) {
             }
         }
     fclose(fo);
+    fprintf(stderr, "MATCHPATH resident=%d upload=%d standalone_upload=%d\n", cm->resident_calls(), cm->upload_calls(),
+            dynamic_cast<CudaORBMatcher*>(standalone.get())->upload_calls());
     return 0;
 }

@@ -102,6 +102,9 @@ def test_cpp_adapter_matches_oracle(tmp_path):
         assert int(occ) == oocc
         assert int(q_ok) == int(30 <= om <= 225 and osd >= 20) and int(d_ok) == int(oocc >= 12.5)
     assert infos[3][4] == "0" and infos[3][5] == "0"  # blank frame fails both checks
+    # the shared-handle matcher served the non-empty pairs from the descriptors Extract left on the device
+    path = [l for l in log.splitlines() if l.startswith("MATCHPATH")][0]
+    assert "resident=4 upload=0" in path, path  # 2 pairs x (Match + MatchFiltered); the blank pair returns early
     assert "Too few matches" not in log  # an empty side returns before the warning (orb_matcher.cpp:18-20)
 
 

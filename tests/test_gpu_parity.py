@@ -5,6 +5,9 @@ bit-exact; Harris/orientation floats within 1e-4 relative (we assert bit equalit
 the stated tolerance only in `test_float_tolerance_statement`); descriptors bit-exact.
 Every test here needs a B200 and is marked gpu.
 """
+import os
+from concurrent.futures import ThreadPoolExecutor
+
 import numpy as np
 import pytest
 
@@ -39,6 +42,19 @@ def test_resize_stage(h, shape, dst):
     rng = np.random.default_rng(shape[0] * 7 + dst[1])
     src = rng.integers(0, 256, shape, dtype=np.uint8)
     got = h.debug_resize(src, dst[1], dst[0])
+    assert np.array_equal(got, oracle.resize_linear_exact(src, dst[1], dst[0]))
+
+
+@pytest.mark.parametrize("band_rows", [16, 8, 4])
+@pytest.mark.parametrize("shape,dst", [((480, 640), (400, 533)), ((400, 533), (333, 444)), ((278, 370), (231, 309)),
+                                       ((161, 214), (134, 179)), ((376, 1241), (313, 1034)), ((1080, 1920), (900, 1600)),
+                                       ((97, 131), (41, 77)), ((50, 64), (40, 64)), ((19, 23), (9, 11))])
+def test_resize_band_stage(h, shape, dst, band_rows):
+    """The production pyramid kernel in isolation, both instantiations: band_rows 16 is resize_band_kernel<true>
+    (the batched throughput shape incl. the shared row tails), 8 / 4 resize_band_kernel<false> (latency shape)."""
+    rng = np.random.default_rng(shape[0] * 11 + dst[1] + band_rows)
+    src = rng.integers(0, 256, shape, dtype=np.uint8)
+    got = h.debug_resize_band(src, dst[1], dst[0], band_rows)
     assert np.array_equal(got, oracle.resize_linear_exact(src, dst[1], dst[0]))
 
 
@@ -457,6 +473,86 @@ def test_resident_passes_pipelined_and_repeatable():
                 assert np.array_equal(matches_as_rows(m), matches_as_rows(om))
 
 
+# ---- the batch shapes the benchmark times (batch >= 8 switches kernel instantiations) ------------------
+
+def _oracle_extract_many(frames, n_features=1000):
+    with ThreadPoolExecutor(max(1, len(os.sched_getaffinity(0)))) as ex:  # the C oracle releases the GIL
+        return list(ex.map(lambda f: oracle.orb_extract(f, n_features), frames))
+
+
+def _oracle_pairs(ext, radius, first_prev=None):
+    """Frame-to-frame matches of consecutive oracle extractions; first_prev = the carried frame before frame 0."""
+    out, prev = [], first_prev
+    for kp, desc in ext:
+        if prev is None:
+            out.append(np.zeros(0, oracle.MATCH_DTYPE))
+        else:
+            pk, pd = prev
+            win = radius > 0
+            out.append(oracle.match(pd, desc, 0.8, np.stack([pk["x"], pk["y"]], 1) if win else None,
+                                    np.stack([kp["x"], kp["y"]], 1) if win else None, radius))
+        prev = (kp, desc)
+    return out
+
+
+@pytest.mark.parametrize("batch", [16, 128])
+def test_bench_batch_shapes_vs_oracle(batch):
+    """Batches of 16 and 128 frames of 640x480 — the shapes bench.py times: resize_band_kernel<true>, describe with 16
+    keypoints per warp, FAST / blur / select over a batched grid — through extract_batch, track (window and brute
+    force) and the resident path, every frame's keypoints, descriptors and matches against the oracle bit for bit;
+    all 8 pyramid and blurred levels of the first, a middle and the last frame against the oracle's."""
+    frames = synth_sequence(640, 480, batch, seed=21)
+    ext = _oracle_extract_many(frames)
+    with vx.VxOrb(max_batch=batch) as hx:
+        outs = hx.extract_batch(frames)
+        for i, ((kp, desc), (okp, odesc)) in enumerate(zip(outs, ext)):
+            assert_kp_equal(kp, okp)
+            assert np.array_equal(desc, odesc), f"extract_batch frame {i}"
+        for f in (0, batch // 2 - 1, batch - 1):
+            levels = oracle.pyramid(frames[f])
+            for l in range(8):
+                assert np.array_equal(hx.debug_level(f, l, 640, 480), levels[l]), f"frame {f} level {l}"
+                assert np.array_equal(hx.debug_level(f, l, 640, 480, blurred=True), oracle.blur7(levels[l])), \
+                    f"frame {f} blurred level {l}"
+        for radius in (32.0, 0.0):
+            ref_m = _oracle_pairs(ext, radius)
+            hx.track_reset()
+            got = hx.track(frames, radius)
+            for i, ((kp, desc, m), (okp, odesc)) in enumerate(zip(got, ext)):
+                assert_kp_equal(kp, okp)
+                assert np.array_equal(desc, odesc)
+                assert np.array_equal(matches_as_rows(m), matches_as_rows(ref_m[i])), f"track r={radius} frame {i}"
+            # resident passes: from the second pass on, frame 0 is matched against the carried last frame
+            ref_c = _oracle_pairs(ext, radius, first_prev=ext[-1])
+            hx.resident_upload(frames)
+            for _ in range(4):  # rotates over all pipeline slots
+                hx.resident_run(radius)
+            res = hx.resident_fetch()
+            for i, ((kp, desc, m), (okp, odesc)) in enumerate(zip(res, ext)):
+                assert_kp_equal(kp, okp)
+                assert np.array_equal(desc, odesc)
+                assert np.array_equal(matches_as_rows(m), matches_as_rows(ref_c[i])), f"resident r={radius} frame {i}"
+
+
+def test_bench_batch_kitti_shape_vs_oracle():
+    """1241x376, 2000 keypoints, batch 8 (>= 8: the throughput instantiations on BASELINE config 3's geometry)."""
+    frames = synth_sequence(1241, 376, 8, seed=5)
+    ext = _oracle_extract_many(frames, 2000)
+    ref_m = _oracle_pairs(ext, 48.0)
+    with vx.VxOrb(n_features=2000, max_width=1241, max_height=376, max_batch=8, max_train=4096) as hx:
+        outs = hx.extract_batch(frames)
+        got = hx.track(frames, 48.0)
+        for i, ((kp, desc), (tkp, tdesc, m), (okp, odesc)) in enumerate(zip(outs, got, ext)):
+            assert_kp_equal(kp, okp)
+            assert np.array_equal(desc, odesc), f"frame {i}"
+            assert_kp_equal(tkp, okp)
+            assert np.array_equal(tdesc, odesc)
+            assert np.array_equal(matches_as_rows(m), matches_as_rows(ref_m[i])), f"frame {i}"
+        levels = oracle.pyramid(frames[7])
+        for l in range(8):
+            assert np.array_equal(hx.debug_level(7, l, 1241, 376), levels[l]), f"level {l}"
+
+
 # ---- the reference's interface, as the reference's caller uses it --------------------------------
 
 def test_reference_interface_flow(golden_c1):
@@ -479,6 +575,69 @@ def test_reference_interface_flow(golden_c1):
     blank = vx.Frame(2, 0.2, np.zeros((480, 640), np.uint8))
     extractor.Extract(blank)
     assert len(blank.Features()) == 0 and matcher.Match(last, blank, matches) == 0 and matches == []
+
+
+def test_reference_interface_flow_resident(golden_c1):
+    """The same flow with the matcher sharing the extractor's handle: Match runs on the descriptors Extract left
+    on the device (no re-upload); a frame that fell out of the 8-entry ring silently takes the upload path."""
+    g = golden_c1
+    extractor = vx.ORBExtractor()
+    matcher = vx.ORBMatcher(extractor=extractor)
+    last, curr = vx.Frame(0, 0.0, g["frame_a"]), vx.Frame(1, 0.1, g["frame_b"])
+    extractor.Extract(last)
+    extractor.Extract(curr)
+    matches = []
+    assert matcher.Match(last, curr, matches) == len(g["matches"])
+    rows = np.array([(m.queryIdx, m.trainIdx, int(m.distance)) for m in matches], np.int32)
+    assert np.array_equal(rows, g["matches"]) and (matcher.resident_calls, matcher.upload_calls) == (1, 0)
+    for i in range(8):  # push `last` out of the ring
+        extractor.Extract(vx.Frame(10 + i, 1.0, g["frame_b"]))
+    assert extractor.resident_id(last) == 0
+    assert matcher.Match(last, curr, matches) == len(g["matches"]) and matcher.upload_calls == 1
+    rows = np.array([(m.queryIdx, m.trainIdx, int(m.distance)) for m in matches], np.int32)
+    assert np.array_equal(rows, g["matches"])
+
+
+def test_match_ids_vs_oracle(golden_c1):
+    """vxorb_extract_id + vxorb_match_ids (ratio, post-filter, cross-check, window) and an uploaded map set."""
+    g = golden_c1
+    with vx.VxOrb(max_train=64) as hx:  # max_train is only a sizing hint: the scratch grows
+        ka, da, ia = hx.extract_id(g["frame_a"])
+        kb, db, ib, info = hx.extract_id(g["frame_b"], with_info=True)
+        assert_kp_equal(ka, g["kp_a"])
+        assert_kp_equal(kb, g["kp_b"])
+        assert np.array_equal(da, g["desc_a"]) and np.array_equal(db, g["desc_b"])
+        assert ib == ia + 1 and hx.set_size(ia) == len(da) and info["n_keypoints"] == len(kb)
+        assert np.array_equal(matches_as_rows(hx.match_ids(ia, ib)), g["matches"])
+        assert np.array_equal(matches_as_rows(hx.match_ids(ia, ib, mode=2)), g["crosscheck"])
+        assert np.array_equal(matches_as_rows(hx.match_ids(ia, ib, radius=32.0)), g["matches_win32"])
+        om = oracle.match(da, db, 0.8)
+        assert np.array_equal(matches_as_rows(hx.match_ids(ia, ib, mode=1)), matches_as_rows(oracle.postfilter(om)))
+        assert np.array_equal(matches_as_rows(hx.match_ids(ib, ia, nn_ratio=0.6)), matches_as_rows(oracle.match(db, da, 0.6)))
+        # a 16 384-row map kept on the device (BASELINE config 4's shape), matched against a frame id
+        rng = np.random.default_rng(4)
+        world = rng.integers(0, 256, (16384, 32), dtype=np.uint8)
+        world[::7][:len(da)] = da[:len(world[::7])]
+        sid = hx.set_upload(world)
+        assert hx.set_size(sid) == 16384
+        assert np.array_equal(matches_as_rows(hx.match_ids(ia, sid)), matches_as_rows(oracle.match(da, world, 0.8)))
+        with pytest.raises(vx.VxOrbError):
+            hx.match_ids(ia, sid, radius=16.0)  # the map has no positions
+        hx.set_free(sid)
+        with pytest.raises(vx.VxOrbError):
+            hx.match_ids(ia, sid)
+        for _ in range(8):
+            hx.extract_id(g["frame_b"])
+        with pytest.raises(vx.VxOrbError):  # overwritten: the caller falls back to the host-buffer call
+            hx.match_ids(ia, ib)
+        # a different geometry re-captures the per-entry graphs; ids of the old geometry stay valid (descriptors only)
+        small = synth_scene(320, 240, 3)
+        ks, ds, is_ = hx.extract_id(small)
+        okp, odesc = oracle.orb_extract(small)
+        assert_kp_equal(ks, okp)
+        assert np.array_equal(ds, odesc)
+        k2, d2, i2 = hx.extract_id(g["frame_b"])
+        assert np.array_equal(matches_as_rows(hx.match_ids(is_, i2)), matches_as_rows(oracle.match(odesc, g["desc_b"], 0.8)))
 
 
 # ---- caller-side per-frame quantities (SURVEY.md section 8f) ----------------------------------------

@@ -61,6 +61,11 @@ _SYMBOLS = [
     ("vxorb_extract", _i, [_vp, _vp, _i, _i, _sz, _i, _vp, _vp, _vp]),
     ("vxorb_extract_bgr", _i, [_vp, _vp, _i, _i, _sz, _i, _vp, _vp, _vp]),
     ("vxorb_extract_info", _i, [_vp, _vp, _i, _i, _i, _sz, _i, _vp, _vp, _vp, _vp]),
+    ("vxorb_extract_id", _i, [_vp, _vp, _i, _i, _i, _sz, _i, _vp, _vp, _vp, _vp, _vp]),
+    ("vxorb_set_upload", _i, [_vp, _vp, _vp, _i, _vp]),
+    ("vxorb_set_free", _i, [_vp, C.c_longlong]),
+    ("vxorb_set_size", _i, [_vp, C.c_longlong]),
+    ("vxorb_match_ids", _i, [_vp, C.c_longlong, C.c_longlong, _f, _f, _i, _i, _vp, _vp]),
     ("vxorb_extract_batch", _i, [_vp, _vp, _i, _i, _i, _sz, _i, _vp, _vp, _vp]),
     ("vxorb_knn2", _i, [_vp, _vp, _i, _vp, _i, _vp]),
     ("vxorb_match", _i, [_vp, _vp, _i, _vp, _i, _f, _i, _vp, _vp]),
@@ -91,6 +96,7 @@ _SYMBOLS = [
     ("vxorb_flush_l2", _i, [_vp]),
     ("vxorb_measure_popc_rate", _i, [_vp, _vp]),
     ("vxorb_debug_resize", _i, [_vp, _vp, _i, _i, _sz, _vp, _i, _i, _sz]),
+    ("vxorb_debug_resize_band", _i, [_vp, _vp, _i, _i, _sz, _vp, _i, _i, _sz, _i]),
     ("vxorb_debug_fast", _i, [_vp, _vp, _i, _i, _sz, _i, _i, _i, _vp, _vp]),
     ("vxorb_debug_blur", _i, [_vp, _vp, _i, _i, _sz, _vp, _sz]),
     ("vxorb_debug_level", _i, [_vp, _i, _i, _i, _vp, _sz]),
@@ -246,6 +252,71 @@ class VxOrb:
                                                  _ptr(kp), _ptr(desc), C.byref(n), _ptr(info)))
         m = min(n.value, cap)
         return kp[:m].copy(), desc[:m].copy(), info[0].copy()
+
+    def extract_into(self, img, kp, desc, want_id=False):
+        """Raw single-frame call into caller-owned arrays (no allocation: what the latency figures time).
+        Returns n, or (n, id) with the frame's descriptors kept resident on the device under id."""
+        n = C.c_int(0)
+        h, w = img.shape[:2]
+        ch = 3 if img.ndim == 3 else 1
+        if want_id:
+            fid = C.c_longlong(0)
+            self._check(self._lib.vxorb_extract_id(self._h, _ptr(img), ch, w, h, img.strides[0], len(kp), _ptr(kp), _ptr(desc),
+                                                   C.byref(n), None, C.byref(fid)))
+            return n.value, fid.value
+        fn = self._lib.vxorb_extract_bgr if ch == 3 else self._lib.vxorb_extract
+        self._check(fn(self._h, _ptr(img), w, h, img.strides[0], len(kp), _ptr(kp), _ptr(desc), C.byref(n)))
+        return n.value
+
+    def extract_id(self, img, with_info=False):
+        """extract() that also returns the id under which the descriptors stay on the device."""
+        img = np.asarray(img)
+        if not img.flags.c_contiguous:
+            img = np.ascontiguousarray(img)
+        kp = np.zeros(self.kp_cap, KEYPOINT_DTYPE)
+        desc = np.zeros((self.kp_cap, 32), np.uint8)
+        info = np.zeros(1, FRAME_INFO_DTYPE)
+        n, fid = C.c_int(0), C.c_longlong(0)
+        h, w = img.shape[:2]
+        self._check(self._lib.vxorb_extract_id(self._h, _ptr(img), 3 if img.ndim == 3 else 1, w, h, img.strides[0],
+                                               self.kp_cap, _ptr(kp), _ptr(desc), C.byref(n),
+                                               _ptr(info) if with_info else None, C.byref(fid)))
+        m = min(n.value, self.kp_cap)
+        out = (kp[:m].copy(), desc[:m].copy(), fid.value)
+        return out + (info[0].copy(),) if with_info else out
+
+    def set_upload(self, desc, xy=None):
+        """Keeps descriptor rows (and optional positions) resident on the device; returns the set id."""
+        desc = _desc(desc)
+        xy = _xy(xy) if xy is not None else None
+        sid = C.c_longlong(0)
+        self._check(self._lib.vxorb_set_upload(self._h, _ptr(desc), _ptr(xy), len(desc), C.byref(sid)))
+        return sid.value
+
+    def set_free(self, sid):
+        self._check(self._lib.vxorb_set_free(self._h, sid))
+
+    def set_size(self, sid):
+        return self._lib.vxorb_set_size(self._h, sid)
+
+    def match_ids_into(self, id_q, id_t, out, radius=0.0, nn_ratio=0.0, mode=0):
+        n = C.c_int(0)
+        self._check(self._lib.vxorb_match_ids(self._h, id_q, id_t, radius, nn_ratio, mode, len(out), _ptr(out), C.byref(n)))
+        return n.value
+
+    def match_ids(self, id_q, id_t, radius=0.0, nn_ratio=0.0, mode=0):
+        """vxorb_match / _filtered / _crosscheck (mode 0 / 1 / 2) on two device-resident sets."""
+        nq = self.set_size(id_q)
+        if nq < 0:
+            raise VxOrbError(E_INVALID, "unknown or overwritten set id")
+        out = np.zeros(max(nq, 1), MATCH_DTYPE)
+        return out[:self.match_ids_into(id_q, id_t, out, radius, nn_ratio, mode)].copy()
+
+    def match_into(self, q, t, out, nn_ratio=0.0):
+        """Raw vxorb_match into a caller-owned array (q, t: contiguous (n,32) uint8)."""
+        n = C.c_int(0)
+        self._check(self._lib.vxorb_match(self._h, _ptr(q), len(q), _ptr(t), len(t), nn_ratio, len(out), _ptr(out), C.byref(n)))
+        return n.value
 
     def extract_batch(self, frames, kp_cap=None):
         frames = [np.ascontiguousarray(f, dtype=np.uint8) for f in frames]
@@ -446,6 +517,14 @@ class VxOrb:
         self._check(self._lib.vxorb_debug_resize(self._h, _ptr(src), sw, sh, sw, _ptr(dst), dw, dh, dw))
         return dst
 
+    def debug_resize_band(self, src, dw, dh, band_rows):
+        """One level through the production band kernel: band_rows 16 = throughput shape, 8 / 4 = latency shape."""
+        src = np.ascontiguousarray(src, dtype=np.uint8)
+        sh, sw = src.shape
+        dst = np.zeros((dh, dw), np.uint8)
+        self._check(self._lib.vxorb_debug_resize_band(self._h, _ptr(src), sw, sh, sw, _ptr(dst), dw, dh, dw, band_rows))
+        return dst
+
     def debug_fast(self, img, threshold=20, border=3):
         img = np.ascontiguousarray(img, dtype=np.uint8)
         h, w = img.shape
@@ -524,12 +603,18 @@ class ORBExtractor:
         self._vx = VxOrb(n_features=n_features, scale_factor=scale_factor, n_levels=n_levels, **handle_kw)
 
     def Extract(self, frame):
-        kp, desc = self._vx.extract(frame.Image())
+        kp, desc, fid = self._vx.extract_id(frame.Image())
         feats = frame.Features()
         feats.clear()
         feats.extend(Feature(k["x"], k["y"], k["response"]) for k in kp)
         frame._descriptors = desc
         frame._keypoints = kp
+        frame._vx_id = fid  # the descriptors also stay on the device under this id (ring of 8 frames)
+
+    def resident_id(self, frame):
+        """Device-resident id of the frame's descriptors, or 0 when they are no longer (or never were) there."""
+        fid = getattr(frame, "_vx_id", 0)
+        return fid if fid and self._vx.set_size(fid) == len(frame.Descriptors()) else 0
 
 
 class ORBMatcher:
@@ -540,17 +625,29 @@ class ORBMatcher:
         def __init__(self, nn_ratio=0.8, min_matches=50):
             self.nn_ratio, self.min_matches = nn_ratio, min_matches
 
-    def __init__(self, options=None, **handle_kw):
+    def __init__(self, options=None, extractor=None, **handle_kw):
+        """extractor: an ORBExtractor whose handle is shared — frames it extracted are matched from the descriptors
+        it left on the device (vxorb_match_ids); other descriptor arrays are uploaded."""
         self.options_ = options or ORBMatcher.Options()
-        self._vx = VxOrb(nn_ratio=self.options_.nn_ratio, min_matches=self.options_.min_matches, **handle_kw)
+        self._extractor = extractor
+        self._vx = extractor._vx if extractor is not None else VxOrb(
+            nn_ratio=self.options_.nn_ratio, min_matches=self.options_.min_matches, **handle_kw)
         self.warnings = []
+        self.resident_calls = self.upload_calls = 0
 
     def Match(self, last, curr, matches):
         matches.clear()
         d1, d2 = last.Descriptors(), curr.Descriptors()
         if len(d1) == 0 or len(d2) == 0:  # orb_matcher.cpp:18-20
             return 0
-        m = self._vx.match(d1, d2, self.options_.nn_ratio)
+        i1 = self._extractor.resident_id(last) if self._extractor else 0
+        i2 = self._extractor.resident_id(curr) if self._extractor else 0
+        if i1 and i2:
+            m = self._vx.match_ids(i1, i2, 0.0, self.options_.nn_ratio)
+            self.resident_calls += 1
+        else:
+            m = self._vx.match(d1, d2, self.options_.nn_ratio)
+            self.upload_calls += 1
         matches.extend(DMatch(r["query_idx"], r["train_idx"], r["distance"]) for r in m)
         if len(matches) < self.options_.min_matches:  # orb_matcher.cpp:38-40 (warning only)
             self.warnings.append(f"[ORBMatcher] Too few matches: {len(matches)}")

@@ -4,6 +4,7 @@
 
 #include <glog/logging.h>
 
+#include <cstring>
 #include <stdexcept>
 
 namespace visionx {
@@ -27,6 +28,24 @@ CudaORBExtractor::CudaORBExtractor(int n_features, float scale_factor, int n_lev
 
 CudaORBExtractor::~CudaORBExtractor() { vxorb_destroy(handle_); }
 
+uint64_t CudaORBExtractor::Fingerprint(const cv::Mat& desc) {
+    if (desc.empty() || desc.cols != VXORB_DESC_BYTES) return 0;
+    uint64_t a[4], b[4], f = 0x9e3779b97f4a7c15ull ^ static_cast<uint64_t>(desc.rows);
+    std::memcpy(a, desc.data, 32);
+    std::memcpy(b, desc.data + static_cast<size_t>(desc.rows - 1) * desc.step, 32);
+    for (int i = 0; i < 4; ++i) f = (f ^ a[i]) * 0x100000001b3ull ^ (b[i] + (f << 7));
+    return f;
+}
+
+long long CudaORBExtractor::ResidentId(const Frame& frame) const {
+    const cv::Mat& d = frame.Descriptors();
+    for (const Resident& r : resident_)
+        if (r.vx_id != 0 && r.frame_id == frame.Id() && r.rows == d.rows && r.fingerprint == Fingerprint(d) &&
+            vxorb_set_size(handle_, r.vx_id) == d.rows)
+            return r.vx_id;
+    return 0;
+}
+
 void CudaORBExtractor::Extract(Frame& frame) {
     auto& features = frame.Features();
     features.clear();  // orb_extractor.cpp:16
@@ -34,10 +53,11 @@ void CudaORBExtractor::Extract(Frame& frame) {
     cv::Mat desc(kp_cap_, VXORB_DESC_BYTES, CV_8UC1);
     int n = 0;
     int rc = VXORB_E_INVALID;
+    long long vx_id = 0;
     if (!image.empty() && image.depth() == CV_8U && (image.channels() == 1 || image.channels() == 3)) {
         // cv::ORB converts 3-channel input to gray itself; system.cpp:46 feeds IMREAD_COLOR frames
-        rc = vxorb_extract_info(handle_, image.data, image.channels(), image.cols, image.rows,
-                                static_cast<size_t>(image.step), kp_cap_, kp_.data(), desc.data, &n, &info_);
+        rc = vxorb_extract_id(handle_, image.data, image.channels(), image.cols, image.rows,
+                              static_cast<size_t>(image.step), kp_cap_, kp_.data(), desc.data, &n, &info_, &vx_id);
     }
     if (rc != VXORB_OK && rc != VXORB_E_CAPACITY) info_ = vxorb_frame_info{};
     last_status_ = rc;
@@ -60,6 +80,14 @@ void CudaORBExtractor::Extract(Frame& frame) {
         features.emplace_back(f);
     }
     frame.Descriptors() = n > 0 ? desc.rowRange(0, n).clone() : cv::Mat();  // orb_extractor.cpp:26
+    if (rc == VXORB_OK && vx_id != 0 && n > 0) {  // remember where this frame's descriptors live on the device
+        Resident& r = resident_[resident_next_];
+        resident_next_ = (resident_next_ + 1) % 8;
+        r.frame_id = frame.Id();
+        r.vx_id = vx_id;
+        r.rows = n;
+        r.fingerprint = Fingerprint(frame.Descriptors());
+    }
 }
 
 }  // namespace visionx

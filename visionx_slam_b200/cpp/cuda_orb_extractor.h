@@ -45,10 +45,24 @@ public:
     // Last vxorb status / message (VXORB_OK after a successful Extract).
     int last_status() const { return last_status_; }
     const std::string& last_error() const { return last_error_; }
-    // The handle is shared with a CudaORBMatcher built from it so both use one device context.
+    // A CudaORBMatcher constructed with this extractor shares the handle (one device context, one set of
+    // streams) and matches the descriptors Extract left on the device instead of uploading them again.
     vxorb_handle* handle() const { return handle_; }
+    // Device-resident id of the descriptors Extract produced for `frame` (vxorb_extract_id), or 0 when the
+    // frame was not extracted here, has been overwritten (ring of 8 frames) or its descriptor matrix no longer
+    // is what Extract wrote (row count and a fingerprint of the first and last rows are compared).
+    long long ResidentId(const Frame& frame) const;
 
 private:
+    struct Resident {
+        uint64_t frame_id = 0;
+        long long vx_id = 0;
+        int rows = 0;
+        uint64_t fingerprint = 0;
+    };
+    static uint64_t Fingerprint(const cv::Mat& desc);
+    Resident resident_[8];
+    int resident_next_ = 0;
     vxorb_handle* handle_ = nullptr;
     int kp_cap_ = 0;
     std::vector<vxorb_keypoint> kp_;

@@ -20,7 +20,16 @@ CudaORBMatcher::CudaORBMatcher(const Options& options) : options_(options) {
         throw std::runtime_error(std::string("CudaORBMatcher: vxorb_create failed: ") + vxorb_last_error(nullptr));
 }
 
-CudaORBMatcher::~CudaORBMatcher() { vxorb_destroy(handle_); }
+CudaORBMatcher::CudaORBMatcher(std::shared_ptr<CudaORBExtractor> extractor, const Options& options)
+    : options_(options), extractor_(std::move(extractor)) {
+    if (!extractor_) throw std::runtime_error("CudaORBMatcher: null extractor");
+    handle_ = extractor_->handle();
+    owns_handle_ = false;
+}
+
+CudaORBMatcher::~CudaORBMatcher() {
+    if (owns_handle_) vxorb_destroy(handle_);
+}
 
 int CudaORBMatcher::Run(bool filtered, const Frame::Ptr& last, const Frame::Ptr& curr,
                         std::vector<cv::DMatch>& matches) {
@@ -33,10 +42,19 @@ int CudaORBMatcher::Run(bool filtered, const Frame::Ptr& last, const Frame::Ptr&
     const cv::Mat t = desc2.isContinuous() ? desc2 : desc2.clone();
     buf_.resize(static_cast<size_t>(q.rows));
     int n = 0;
-    auto fn = filtered ? vxorb_match_filtered : vxorb_match;
-    last_status_ = fn(handle_, q.data, q.rows, t.data, t.rows, options_.nn_ratio, q.rows, buf_.data(), &n);
+    const long long id_q = extractor_ ? extractor_->ResidentId(*last) : 0;
+    const long long id_t = extractor_ ? extractor_->ResidentId(*curr) : 0;
+    if (id_q != 0 && id_t != 0) {  // both descriptor sets are still on the device
+        last_status_ = vxorb_match_ids(handle_, id_q, id_t, 0.f, options_.nn_ratio, filtered ? 1 : 0, q.rows, buf_.data(), &n);
+        ++resident_calls_;
+    } else {
+        auto fn = filtered ? vxorb_match_filtered : vxorb_match;
+        last_status_ = fn(handle_, q.data, q.rows, t.data, t.rows, options_.nn_ratio, q.rows, buf_.data(), &n);
+        ++upload_calls_;
+    }
     if (last_status_ != VXORB_OK) {
-        LOG(ERROR) << "[CudaORBMatcher] " << vxorb_last_error(handle_);
+        // an error, not "no matches": the reference's matcher has no failure path, so say it loudly
+        LOG(ERROR) << "[CudaORBMatcher] vxorb status " << last_status_ << ": " << vxorb_last_error(handle_);
         return 0;
     }
     matches.reserve(static_cast<size_t>(n));

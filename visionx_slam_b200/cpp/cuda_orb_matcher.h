@@ -10,9 +10,11 @@
 // exactly as OpenCV's batchDistance.
 #pragma once
 
+#include <memory>
 #include <string>
 #include <vector>
 
+#include "cuda_orb_extractor.h"
 #include "feature/feature_matcher.h"
 #include "vxorb.h"
 
@@ -24,11 +26,16 @@ public:
         float nn_ratio = 0.8f;
         int min_matches = 50;
         int device_id = 0;
-        int max_descriptors = 16384;  // largest descriptor count per side
+        int max_descriptors = 16384;  // sizing hint; the device scratch grows with the descriptor counts it meets
     };
 
     CudaORBMatcher() : CudaORBMatcher(Options()) {}
     explicit CudaORBMatcher(const Options& options);
+    // Shares the extractor's handle: frames that extractor processed are matched from the descriptors it left on
+    // the device (vxorb_match_ids, only the matches cross the link); any other descriptor matrix is uploaded as
+    // before.  This is the constructor system.cpp:15-16 should use.
+    explicit CudaORBMatcher(std::shared_ptr<CudaORBExtractor> extractor) : CudaORBMatcher(std::move(extractor), Options()) {}
+    CudaORBMatcher(std::shared_ptr<CudaORBExtractor> extractor, const Options& options);
     ~CudaORBMatcher() override;
     CudaORBMatcher(const CudaORBMatcher&) = delete;
     CudaORBMatcher& operator=(const CudaORBMatcher&) = delete;
@@ -41,11 +48,17 @@ public:
     int MatchFiltered(const Frame::Ptr& last, const Frame::Ptr& curr, std::vector<cv::DMatch>& matches);
 
     int last_status() const { return last_status_; }
+    // Match calls served from device-resident descriptors / through the upload path since construction.
+    int resident_calls() const { return resident_calls_; }
+    int upload_calls() const { return upload_calls_; }
 
 private:
     int Run(bool filtered, const Frame::Ptr& last, const Frame::Ptr& curr, std::vector<cv::DMatch>& matches);
     Options options_;
+    std::shared_ptr<CudaORBExtractor> extractor_;  // keeps the shared handle alive
     vxorb_handle* handle_ = nullptr;
+    bool owns_handle_ = true;
+    int resident_calls_ = 0, upload_calls_ = 0;
     std::vector<vxorb_match_t> buf_;
     int last_status_ = VXORB_OK;
 };

@@ -11,6 +11,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <map>
 #include <mutex>
 #include <stdlib.h>
 #include <string>
@@ -53,6 +54,23 @@ struct Workspace {
     uint8_t* stage_bgr = nullptr;         // [max_batch][H][3 W] colour upload staging, allocated on the first BGR chunk
 };
 
+// A descriptor set that stays on the device under an id: the result of a single-frame extract call (ring of
+// kRing entries, overwritten in turn) or rows uploaded with vxorb_set_upload (a local map; freed by the caller).
+constexpr int kRing = 8;
+constexpr long long kFirstSetId = 1LL << 40;  // frame ids count up from 1, uploaded sets from here
+struct ResidentSet {
+    long long id = 0;             // 0 = empty
+    vxorb_keypoint* kp = nullptr; // ring entries only
+    uint8_t* desc = nullptr;
+    float* xy = nullptr;          // level-0 positions (nullptr for an uploaded set without positions)
+    int* n = nullptr;             // device: [0] rows written, [1] true count
+    int n_host = 0;
+    // single-frame extraction is launch bound: its launches, memsets and the side-stream fork/join are captured
+    // once per geometry and ring entry (the describe kernel writes straight into the entry) and replayed
+    cudaGraphExec_t graph = nullptr;
+    int graph_launches = 0;
+};
+
 }  // namespace
 
 struct vxorb_handle {
@@ -92,11 +110,12 @@ struct vxorb_handle {
     float stage_ms[VXORB_STAGE_COUNT] = {0};
     int stage_launches[VXORB_STAGE_COUNT] = {0};
     long long launches = 0;
-    // single-frame extraction (the per-frame call of the reference's front end) is launch bound: its 14
-    // launches, the two memsets and the side-stream fork/join are captured once per geometry into a CUDA
-    // graph on slot 0 and replayed
-    cudaGraphExec_t x_graph = nullptr;
-    int x_graph_launches = 0;
+    // device-resident descriptor sets (vxorb_extract_id / vxorb_set_upload / vxorb_match_ids)
+    ResidentSet ring[kRing];
+    bool ring_ready = false;
+    long long next_frame_id = 1, next_set_id = kFirstSetId;
+    std::map<long long, ResidentSet> sets;
+    bool no_graph = false, no_overlap = false, no_flat_upload = false;  // VXORB_NO_* switches, read once in vxorb_create
     uint8_t* x_stage = nullptr;  // pinned staging block of the synchronous extract calls
     size_t x_bytes = 0;
     uint8_t* flush_buf = nullptr;
@@ -154,8 +173,10 @@ void free_workspace(Workspace& w) {
 }
 
 void free_geometry(vxorb_handle* h) {
-    if (h->x_graph) cudaGraphExecDestroy(h->x_graph);  // its nodes point into the buffers freed below
-    h->x_graph = nullptr;
+    for (auto& r : h->ring) {  // graph nodes point into the buffers freed below
+        if (r.graph) cudaGraphExecDestroy(r.graph);
+        r.graph = nullptr;
+    }
     for (auto& w : h->ws) free_workspace(w);
     cudaFree(h->d_coef);
     cudaFree(h->carry_desc);
@@ -319,7 +340,7 @@ struct StageScope {
 
 // Queues the extraction kernels for `batch` frames whose level 0 already sits in ws.db.pyr.
 // Outputs go to frame slots 1..batch of kp/desc/xy/kp_n (slot 0 is the streaming carry).
-int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
+int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch, const ResidentSet* out = nullptr) {
     LevelTab lt = h->lt;
     // Frame strides inside a level plane do not depend on the batch, only the launch extent does.
     lt.batch = batch;
@@ -332,7 +353,7 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
     // instrumented (per-stage timed) mode the blur runs on the slot's side stream beside them and fills
     // the issue slots FAST's barriers and select's tails leave idle.  Instrumented runs stay serial so a
     // stage's events bracket that stage alone.
-    const bool overlap = !h->stage_enabled && ws.side != nullptr && !getenv("VXORB_NO_OVERLAP");
+    const bool overlap = !h->stage_enabled && ws.side != nullptr && !h->no_overlap;
     // Level 0's reflect apron is read by FAST and the blur, not by the resampling: for a few frames (where the
     // level chain is the critical path) it is built on the side stream while the chain already runs.  Large
     // batches keep it in line: there it only takes SMs from the first resize level (A/B: -0.7 % resident).
@@ -382,6 +403,13 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
         o.xy = d.xy + (size_t)h->kp_cap * 2;
         o.kp_n = d.kp_n + 1;
         o.kp_total = d.kp_total + 1;
+        if (out) {  // single frame: straight into the resident set
+            o.kp = out->kp;
+            o.desc = out->desc;
+            o.xy = out->xy;
+            o.kp_n = out->n;
+            o.kp_total = out->n + 1;
+        }
         const int n = launch_describe(lt, o, h->kp_cap, s);
         if (n < 0) return fail(h, VXORB_E_CUDA, "cuTensorMapEncodeTiled failed for the descriptor window maps");
         sc.end(n);
@@ -390,14 +418,15 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch) {
     return VXORB_OK;
 }
 
-// Single-frame extraction on slot 0 through a CUDA graph (captured on first use for the current geometry).
-int launch_extract_graph(vxorb_handle* h, Workspace& ws) {
-    if (!h->x_graph) {
+// Single-frame extraction on slot 0 through a CUDA graph (captured on first use for the current geometry and
+// ring entry).
+int launch_extract_graph(vxorb_handle* h, Workspace& ws, ResidentSet& rs) {
+    if (!rs.graph) {
         const long long before = h->launches;
         int stage_before[VXORB_STAGE_COUNT];
         for (int i = 0; i < VXORB_STAGE_COUNT; ++i) stage_before[i] = h->stage_launches[i];
         CK(cudaStreamBeginCapture(ws.stream, cudaStreamCaptureModeThreadLocal));
-        const int rc = enqueue_extract(h, ws, 1);
+        const int rc = enqueue_extract(h, ws, 1, &rs);
         cudaGraph_t graph = nullptr;
         const cudaError_t e = cudaStreamEndCapture(ws.stream, &graph);
         if (rc) {
@@ -405,19 +434,45 @@ int launch_extract_graph(vxorb_handle* h, Workspace& ws) {
             return rc;
         }
         if (e != cudaSuccess || !graph) return fail(h, VXORB_E_CUDA, std::string("graph capture: ") + cudaGetErrorString(e));
-        const cudaError_t ei = cudaGraphInstantiate(&h->x_graph, graph, 0);
+        const cudaError_t ei = cudaGraphInstantiate(&rs.graph, graph, 0);
         cudaGraphDestroy(graph);
         if (ei != cudaSuccess) {
-            h->x_graph = nullptr;
+            rs.graph = nullptr;
             return fail(h, VXORB_E_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(ei));
         }
-        h->x_graph_launches = (int)(h->launches - before);
+        rs.graph_launches = (int)(h->launches - before);
         h->launches = before;  // nothing ran during the capture; every replay below counts its kernels
         for (int i = 0; i < VXORB_STAGE_COUNT; ++i) h->stage_launches[i] = stage_before[i];
     }
-    CK(cudaGraphLaunch(h->x_graph, ws.stream));
-    h->launches += h->x_graph_launches;
+    CK(cudaGraphLaunch(rs.graph, ws.stream));
+    h->launches += rs.graph_launches;
     return VXORB_OK;
+}
+
+// Allocates the ring of resident frame sets (kp_cap rows each) on first use.
+int ensure_ring(vxorb_handle* h) {
+    if (h->ring_ready) return VXORB_OK;
+    const size_t cap = (size_t)h->kp_cap;
+    for (auto& r : h->ring) {
+        CK(cudaMalloc(&r.kp, sizeof(vxorb_keypoint) * cap));
+        CK(cudaMalloc(&r.desc, 32 * cap));
+        CK(cudaMalloc(&r.xy, 8 * cap));
+        CK(cudaMalloc(&r.n, sizeof(int) * 2));
+        CK(cudaMemset(r.n, 0, sizeof(int) * 2));
+    }
+    h->ring_ready = true;
+    return VXORB_OK;
+}
+
+// Looks an id up in the ring / the uploaded sets; nullptr when it is unknown or has been overwritten.
+const ResidentSet* find_set(const vxorb_handle* h, long long id) {
+    if (id <= 0) return nullptr;
+    if (id >= kFirstSetId) {
+        auto it = h->sets.find(id);
+        return it == h->sets.end() ? nullptr : &it->second;
+    }
+    const ResidentSet& r = h->ring[id % kRing];
+    return (h->ring_ready && r.id == id) ? &r : nullptr;
 }
 
 // Queues the frame-to-frame match of slots (p, p+1), p = 0..batch-1.
@@ -464,7 +519,7 @@ int upload_frames(vxorb_handle* h, Workspace& ws, const uint8_t* frames, int bat
     const LevelTab& lt = h->lt;
     uint8_t* dst = ws.db.pyr + lt.off[0];
     if (batch > 1 && stride == (size_t)W && frame_stride == (size_t)W * H && W % 16 == 0 && ws.stage_in &&
-        !getenv("VXORB_NO_FLAT_UPLOAD")) {
+        !h->no_flat_upload) {
         // densely packed chunk: one flat copy over the link, rows scattered into the planes on the device
         CK(cudaMemcpyAsync(ws.stage_in, frames, (size_t)W * H * batch, cudaMemcpyHostToDevice, ws.stream));
         h->launches += launch_unpack_frames(ws.stage_in, dst, W, H, lt.pitch[0], (size_t)lt.fstride[0], batch, ws.stream);
@@ -555,19 +610,88 @@ int ensure_host_stage(vxorb_handle* h, size_t need) {
     return VXORB_OK;
 }
 
-// Host-buffer knn: uploads both descriptor sets and runs the knn kernel into m_knn (and, for the
-// cross-check, the reverse direction into m_back).
+// A descriptor set on the device as the match kernels see it.
+struct DevSet {
+    const uint8_t* desc;
+    const float* xy;   // or nullptr
+    const int* n_dev;  // device row count
+    int n;             // the same count on the host (grid sizing)
+};
+
+// 2-NN of q against t on slot 0's stream into m_knn (and, for the cross-check, the reverse direction into m_back).
+int run_knn_device(vxorb_handle* h, const DevSet& q, const DevSet& t, float radius, bool reverse_too, const float* box) {
+    if (q.n >= (1 << 20) || t.n >= (1 << 20))
+        return fail(h, VXORB_E_INVALID, "descriptor count must stay below 2^20 (index field of the packed 2-NN key)");
+    int rc = ensure_match_scratch(h, std::max(std::max(q.n, t.n), 1));  // grows on demand: no fixed limit per side
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    const bool win = (radius > 0.f || box) && q.xy && t.xy;
+    if (box && !win) return fail(h, VXORB_E_INVALID, "box mask needs query and train positions");
+    StageScope sc(h, s, VXORB_STAGE_MATCH);
+    MatchArgs a;
+    a.q_desc = q.desc; a.t_desc = t.desc;
+    a.q_xy = win ? q.xy : nullptr; a.t_xy = win ? t.xy : nullptr;
+    a.q_n = q.n_dev; a.t_n = t.n_dev;
+    a.q_pair_stride = a.t_pair_stride = 0;
+    a.max_q = q.n; a.max_t = t.n; a.pairs = 1; a.radius = win ? radius : 0.f;
+    a.knn = h->m_knn; a.knn_stride = 0;
+    a.part = h->m_part;
+    if (box) {
+        a.boxed = 1;
+        for (int i = 0; i < 4; ++i) a.box[i] = box[i];
+    }
+    int launches = launch_knn2(a, s);
+    if (reverse_too) {
+        MatchArgs b = a;
+        b.q_desc = t.desc; b.t_desc = q.desc;
+        b.q_xy = a.t_xy; b.t_xy = a.q_xy;
+        b.q_n = t.n_dev; b.t_n = q.n_dev;
+        b.max_q = t.n; b.max_t = q.n; b.knn = h->m_back;
+        launches += launch_knn2(b, s);
+    }
+    sc.end(launches);
+    CK(cudaGetLastError());
+    return VXORB_OK;
+}
+
+// Compaction of m_knn into accepted matches (mode 0: ratio test, 1: + the caller's post-filter, 2: cross-check)
+// and the read-back: the count and the first min(out_cap, nq) rows reach the pinned staging block in one round trip.
+int finish_match(vxorb_handle* h, const DevSet& q, float nn_ratio, int mode, int out_cap, vxorb_match_t* out, int* n_out) {
+    cudaStream_t s = h->ws[0].stream;
+    if (nn_ratio <= 0.f) nn_ratio = h->p.nn_ratio;
+    h->launches += launch_match_compact(h->m_knn, mode == 2 ? h->m_back : nullptr, 0, 0, q.n_dev, 1, nn_ratio, mode,
+                                        h->m_out, h->m_cap, h->m_out_n, s);
+    h->stage_launches[VXORB_STAGE_MATCH] += 1;
+    CK(cudaGetLastError());
+    const int rows = std::min(out_cap, q.n);
+    const size_t need = 64 + sizeof(vxorb_match_t) * (size_t)rows;
+    int rc = ensure_host_stage(h, need);
+    if (rc) return rc;
+    int* n_st = reinterpret_cast<int*>(h->x_stage);
+    vxorb_match_t* out_st = reinterpret_cast<vxorb_match_t*>(h->x_stage + 64);
+    CK(cudaMemcpyAsync(n_st, h->m_out_n, sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (rows > 0) CK(cudaMemcpyAsync(out_st, h->m_out, sizeof(vxorb_match_t) * (size_t)rows, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    const int n = *n_st;
+    *n_out = n;
+    const int m = std::min(n, rows);
+    if (m > 0) memcpy(out, out_st, sizeof(vxorb_match_t) * (size_t)m);
+    if (n > out_cap) return fail(h, VXORB_E_CAPACITY, "match output buffer too small");
+    return VXORB_OK;
+}
+
+// Host-buffer knn: uploads both descriptor sets through the pinned staging block (pageable sources would make
+// every copy a blocking one) and runs the knn kernel.
 int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy,
                  int nt, float radius, bool reverse_too, const float* box = nullptr) {
     if (nq < 0 || nt < 0 || (nq > 0 && !q) || (nt > 0 && !t)) return fail(h, VXORB_E_INVALID, "bad descriptor arguments");
-    if (nq > h->p.max_train || nt > h->p.max_train || nt >= (1 << 20) || nq >= (1 << 20))
-        return fail(h, VXORB_E_INVALID, "descriptor count exceeds max_train");
+    if (nt >= (1 << 20) || nq >= (1 << 20))
+        return fail(h, VXORB_E_INVALID, "descriptor count must stay below 2^20 (index field of the packed 2-NN key)");
     int rc = ensure_match_scratch(h, std::max(std::max(nq, nt), 1));
     if (rc) return rc;
     cudaStream_t s = h->ws[0].stream;
     const bool win = (radius > 0.f || box) && qxy && txy;
     if (box && !win) return fail(h, VXORB_E_INVALID, "box mask needs query and train positions");
-    // inputs go through the pinned staging block (pageable sources would make every copy a blocking one);
     // the block is also large enough for the outputs the callers stage afterwards
     const size_t q_off = 64, t_off = q_off + (size_t)nq * 32, qxy_off = t_off + (size_t)nt * 32;
     const size_t txy_off = qxy_off + (size_t)nq * 8, in_end = txy_off + (size_t)nt * 8;
@@ -596,30 +720,8 @@ int run_knn_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, co
             CK(cudaMemcpyAsync(h->m_txy, h->x_stage + txy_off, (size_t)nt * 8, cudaMemcpyHostToDevice, s));
         }
     }
-    StageScope sc(h, s, VXORB_STAGE_MATCH);
-    MatchArgs a;
-    a.q_desc = h->m_q; a.t_desc = h->m_t;
-    a.q_xy = win ? h->m_qxy : nullptr; a.t_xy = win ? h->m_txy : nullptr;
-    a.q_n = h->m_n; a.t_n = h->m_n + 1;
-    a.q_pair_stride = a.t_pair_stride = 0;
-    a.max_q = nq; a.max_t = nt; a.pairs = 1; a.radius = win ? radius : 0.f;
-    a.knn = h->m_knn; a.knn_stride = 0;
-    a.part = h->m_part;
-    if (box) {
-        a.boxed = 1;
-        for (int i = 0; i < 4; ++i) a.box[i] = box[i];
-    }
-    int launches = launch_knn2(a, s);
-    if (reverse_too) {
-        MatchArgs b = a;
-        b.q_desc = h->m_t; b.t_desc = h->m_q;
-        b.q_n = h->m_n + 1; b.t_n = h->m_n;
-        b.max_q = nt; b.max_t = nq; b.knn = h->m_back;
-        launches += launch_knn2(b, s);
-    }
-    sc.end(launches);
-    CK(cudaGetLastError());
-    return VXORB_OK;
+    const DevSet dq{h->m_q, win ? h->m_qxy : nullptr, h->m_n, nq}, dt{h->m_t, win ? h->m_txy : nullptr, h->m_n + 1, nt};
+    return run_knn_device(h, dq, dt, radius, reverse_too, box);
 }
 
 int run_match_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy,
@@ -633,28 +735,8 @@ int run_match_host(vxorb_handle* h, const uint8_t* q, const float* qxy, int nq, 
     }
     int rc = run_knn_host(h, q, qxy, nq, t, txy, nt, radius, mode == 2, box);
     if (rc) return rc;
-    cudaStream_t s = h->ws[0].stream;
-    if (nn_ratio <= 0.f) nn_ratio = h->p.nn_ratio;
-    h->launches += launch_match_compact(h->m_knn, mode == 2 ? h->m_back : nullptr, 0, 0, h->m_n, 1, nn_ratio, mode,
-                                        h->m_out, h->m_cap, h->m_out_n, s);
-    h->stage_launches[VXORB_STAGE_MATCH] += 1;
-    CK(cudaGetLastError());
-    // one round trip: the count and the first min(out_cap, nq) rows go to the pinned staging block together
-    const int rows = std::min(out_cap, nq);
-    const size_t need = 64 + sizeof(vxorb_match_t) * (size_t)rows;
-    rc = ensure_host_stage(h, need);
-    if (rc) return rc;
-    int* n_st = reinterpret_cast<int*>(h->x_stage);
-    vxorb_match_t* out_st = reinterpret_cast<vxorb_match_t*>(h->x_stage + 64);
-    CK(cudaMemcpyAsync(n_st, h->m_out_n, sizeof(int), cudaMemcpyDeviceToHost, s));
-    if (rows > 0) CK(cudaMemcpyAsync(out_st, h->m_out, sizeof(vxorb_match_t) * (size_t)rows, cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
-    const int n = *n_st;
-    *n_out = n;
-    const int m = std::min(n, rows);
-    if (m > 0) memcpy(out, out_st, sizeof(vxorb_match_t) * (size_t)m);
-    if (n > out_cap) return fail(h, VXORB_E_CAPACITY, "match output buffer too small");
-    return VXORB_OK;
+    const DevSet dq{h->m_q, nullptr, h->m_n, nq};
+    return finish_match(h, dq, nn_ratio, mode, out_cap, out, n_out);
 }
 
 int ensure_stage_scratch(vxorb_handle* h, size_t bytes) {
@@ -725,6 +807,9 @@ int vxorb_create(const vxorb_params* p, vxorb_handle** out) {
         return VXORB_E_NOMEM;
     }
     h->p = *p;
+    h->no_graph = getenv("VXORB_NO_GRAPH") != nullptr;
+    h->no_overlap = getenv("VXORB_NO_OVERLAP") != nullptr;
+    h->no_flat_upload = getenv("VXORB_NO_FLAT_UPLOAD") != nullptr;
     h->kp_cap = p->max_keypoints > 0 ? p->max_keypoints : p->n_features + p->n_features / 4 + 64;
     auto bail = [&](cudaError_t err, const char* what) {
         g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
@@ -774,6 +859,12 @@ void vxorb_destroy(vxorb_handle* h) {
         if (w.ev_apron) cudaEventDestroy(w.ev_apron);
         if (w.h_status) cudaFreeHost(w.h_status);
     }
+    for (auto& r : h->ring) {
+        cudaFree(r.kp); cudaFree(r.desc); cudaFree(r.xy); cudaFree(r.n);
+    }
+    for (auto& kv : h->sets) {
+        cudaFree(kv.second.desc); cudaFree(kv.second.xy); cudaFree(kv.second.n);
+    }
     cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);
     cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n); cudaFree(h->m_part);
     cudaFree(h->s_a); cudaFree(h->s_b); cudaFree(h->flush_buf);
@@ -807,11 +898,12 @@ int vxorb_level_geometry(const vxorb_handle* h, int width, int height, int* leve
 
 static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const uint8_t* bgr, int batch, int W, int H,
                           size_t stride, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out,
-                          vxorb_frame_info* info_out = nullptr) {
+                          vxorb_frame_info* info_out = nullptr, long long* id_out = nullptr) {
     if (!h) return VXORB_E_INVALID;
     if (batch < 1 || batch > h->p.max_batch) return fail(h, VXORB_E_INVALID, "batch outside 1..max_batch");
     if (!n_out || kp_cap < 0 || (kp_cap > 0 && (!kp_out || !desc_out)))
         return fail(h, VXORB_E_INVALID, "null output pointer");
+    if (id_out) *id_out = 0;
     CK(cudaSetDevice(h->p.device_id));
     int rc = ensure_geometry(h, W, H);
     if (rc) return rc;
@@ -819,6 +911,16 @@ static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const u
     if (ws.in_flight) return fail(h, VXORB_E_INVALID, "slot 0 busy with a track submit; wait for it first");
     const LevelTab& lt = h->lt;
     uint8_t* l0 = ws.db.pyr + lt.off[0];
+    // a single frame goes straight into the next entry of the resident ring (its id stays valid until kRing
+    // more single-frame extractions have run); batches use the slot's frame-major buffers
+    ResidentSet* rs = nullptr;
+    if (batch == 1) {
+        rc = ensure_ring(h);
+        if (rc) return rc;
+        rs = &h->ring[h->next_frame_id % kRing];
+        rs->id = 0;  // invalid while it is being overwritten
+        rs->n_host = 0;
+    }
     if (bgr) {
         if (stride < (size_t)W * 3) return fail(h, VXORB_E_INVALID, "stride smaller than a BGR row");
         rc = ensure_stage_scratch(h, stride * (size_t)H);
@@ -834,16 +936,30 @@ static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const u
                                  cudaMemcpyHostToDevice, ws.stream));
         }
     }
-    if (batch == 1 && !h->stage_enabled && !getenv("VXORB_NO_GRAPH")) {
-        rc = launch_extract_graph(h, ws);
+    if (batch == 1 && !h->stage_enabled && !h->no_graph) {
+        rc = launch_extract_graph(h, ws, *rs);
     } else {
-        rc = enqueue_extract(h, ws, batch);
+        rc = enqueue_extract(h, ws, batch, rs);
     }
     if (rc) return rc;
+    // where the rows of frame 0 sit, and the stride to the next frame
+    const vxorb_keypoint* d_kp = rs ? rs->kp : ws.db.kp + h->kp_cap;
+    const uint8_t* d_desc = rs ? rs->desc : ws.db.desc + (size_t)h->kp_cap * 32;
+    const int* d_n = rs ? rs->n : ws.db.kp_n + 1;
+    const int* d_total = rs ? rs->n + 1 : ws.db.kp_total + 1;
     if (info_out) {  // no pairs here: zero match counts, then statistics + grid coverage of every frame
         CK(cudaMemsetAsync(ws.db.match_n, 0, sizeof(int) * batch, ws.stream));
-        rc = enqueue_frame_info(h, ws, batch, false);
-        if (rc) return rc;
+        LevelTab ltb = h->lt;
+        ltb.batch = batch;
+        DeviceBuffers dbi = ws.db;
+        if (rs) {  // the kernel reads frame f's positions / count at slot f + 1
+            dbi.xy = rs->xy - (size_t)h->kp_cap * 2;
+            dbi.kp_n = rs->n - 1;
+        }
+        const int nl = launch_frame_info(ltb, dbi, h->kp_cap, ws.sums, ws.info, nullptr, 5, 5, ws.stream);
+        h->launches += nl;
+        h->stage_launches[VXORB_STAGE_MATCH] += nl;
+        CK(cudaGetLastError());
         CK(cudaMemcpyAsync(info_out, ws.info, sizeof(vxorb_frame_info) * batch, cudaMemcpyDeviceToHost, ws.stream));
     }
     // One round trip: counts, status and the first min(kp_cap, capacity) rows of every frame land in the
@@ -858,15 +974,15 @@ static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const u
     int* counts = reinterpret_cast<int*>(h->x_stage);
     vxorb_keypoint* st_kp = reinterpret_cast<vxorb_keypoint*>(h->x_stage + kp_off);
     uint8_t* st_desc = h->x_stage + desc_off;
-    CK(cudaMemcpyAsync(counts, ws.db.kp_n + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
-    CK(cudaMemcpyAsync(counts + batch, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
+    CK(cudaMemcpyAsync(counts, d_n, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
+    CK(cudaMemcpyAsync(counts + batch, d_total, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
     CK(cudaMemcpyAsync(counts + 2 * batch, ws.db.status, sizeof(int) * 4, cudaMemcpyDeviceToHost, ws.stream));
     if (rows > 0) {
-        // frame f's rows sit at slot f + 1 with stride h->kp_cap on the device, stride `rows` in the staging block
-        CK(cudaMemcpy2DAsync(st_kp, sizeof(vxorb_keypoint) * (size_t)rows, ws.db.kp + h->kp_cap,
+        // frame f's rows sit h->kp_cap rows apart on the device, `rows` apart in the staging block
+        CK(cudaMemcpy2DAsync(st_kp, sizeof(vxorb_keypoint) * (size_t)rows, d_kp,
                              sizeof(vxorb_keypoint) * (size_t)h->kp_cap, sizeof(vxorb_keypoint) * (size_t)rows, batch,
                              cudaMemcpyDeviceToHost, ws.stream));
-        CK(cudaMemcpy2DAsync(st_desc, (size_t)32 * rows, ws.db.desc + (size_t)h->kp_cap * 32, (size_t)32 * h->kp_cap,
+        CK(cudaMemcpy2DAsync(st_desc, (size_t)32 * rows, d_desc, (size_t)32 * h->kp_cap,
                              (size_t)32 * rows, batch, cudaMemcpyDeviceToHost, ws.stream));
     }
     CK(cudaStreamSynchronize(ws.stream));
@@ -884,6 +1000,11 @@ static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const u
     h->last_slot = -1;  // the synchronous extract calls do not take part in a tracked sequence
     const int status = counts[2 * batch];
     if (status & 3) return check_status(h, status);
+    if (rs) {  // the set is complete: publish it
+        rs->n_host = counts[0];
+        rs->id = h->next_frame_id++;
+        if (id_out) *id_out = rs->id;
+    }
     if (truncated) return fail(h, VXORB_E_CAPACITY, "more keypoints than kp_cap / max_keypoints; output truncated");
     return VXORB_OK;
 }
@@ -903,6 +1024,16 @@ int vxorb_extract_info(vxorb_handle* h, const uint8_t* img, int channels, int wi
     if (channels == 3)
         return extract_common(h, nullptr, img, 1, width, height, stride, kp_cap, kp_out, desc_out, n_out, info_out);
     return extract_common(h, &img, nullptr, 1, width, height, stride, kp_cap, kp_out, desc_out, n_out, info_out);
+}
+
+int vxorb_extract_id(vxorb_handle* h, const uint8_t* img, int channels, int width, int height, size_t stride, int kp_cap,
+                     vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_out, vxorb_frame_info* info_out, long long* id_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!img || !id_out) return fail(h, VXORB_E_INVALID, "null image or id pointer");
+    if (channels != 1 && channels != 3) return fail(h, VXORB_E_INVALID, "channels must be 1 (gray) or 3 (BGR)");
+    if (channels == 3)
+        return extract_common(h, nullptr, img, 1, width, height, stride, kp_cap, kp_out, desc_out, n_out, info_out, id_out);
+    return extract_common(h, &img, nullptr, 1, width, height, stride, kp_cap, kp_out, desc_out, n_out, info_out, id_out);
 }
 
 int vxorb_extract_bgr(vxorb_handle* h, const uint8_t* bgr, int width, int height, size_t stride, int kp_cap,
@@ -996,6 +1127,71 @@ int vxorb_match_filtered(vxorb_handle* h, const uint8_t* query, int nq, const ui
     if (!h) return VXORB_E_INVALID;
     CK(cudaSetDevice(h->p.device_id));
     return run_match_host(h, query, nullptr, nq, train, nullptr, nt, 0.f, nn_ratio, 1, out_cap, out, n_out);
+}
+
+// ---- device-resident descriptor sets ---------------------------------------------------------------
+
+int vxorb_set_upload(vxorb_handle* h, const uint8_t* desc, const float* xy, int n, long long* id_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!id_out || n < 0 || (n > 0 && !desc) || n >= (1 << 20)) return fail(h, VXORB_E_INVALID, "bad set arguments");
+    *id_out = 0;
+    CK(cudaSetDevice(h->p.device_id));
+    ResidentSet rs;
+    const size_t rows = (size_t)std::max(n, 1);
+    auto bail = [&](const char* what) {
+        cudaFree(rs.desc); cudaFree(rs.xy); cudaFree(rs.n);
+        cudaGetLastError();
+        return fail(h, VXORB_E_NOMEM, what);
+    };
+    if (cudaMalloc(&rs.desc, rows * 32) != cudaSuccess) return bail("device allocation of the descriptor set failed");
+    if (xy && cudaMalloc(&rs.xy, rows * 8) != cudaSuccess) return bail("device allocation of the set positions failed");
+    if (cudaMalloc(&rs.n, sizeof(int) * 2) != cudaSuccess) return bail("device allocation of the set count failed");
+    const int counts[2] = {n, n};
+    CK(cudaMemcpy(rs.n, counts, sizeof(counts), cudaMemcpyHostToDevice));
+    if (n) {
+        CK(cudaMemcpy(rs.desc, desc, (size_t)n * 32, cudaMemcpyHostToDevice));
+        if (xy) CK(cudaMemcpy(rs.xy, xy, (size_t)n * 8, cudaMemcpyHostToDevice));
+    }
+    rs.n_host = n;
+    rs.id = h->next_set_id++;
+    h->sets[rs.id] = rs;
+    *id_out = rs.id;
+    return VXORB_OK;
+}
+
+int vxorb_set_free(vxorb_handle* h, long long id) {
+    if (!h) return VXORB_E_INVALID;
+    auto it = h->sets.find(id);
+    if (it == h->sets.end()) return fail(h, VXORB_E_INVALID, "unknown set id");
+    CK(cudaSetDevice(h->p.device_id));
+    CK(cudaStreamSynchronize(h->ws[0].stream));
+    cudaFree(it->second.desc); cudaFree(it->second.xy); cudaFree(it->second.n);
+    h->sets.erase(it);
+    return VXORB_OK;
+}
+
+int vxorb_set_size(const vxorb_handle* h, long long id) {
+    if (!h) return VXORB_E_INVALID;
+    const ResidentSet* s = find_set(h, id);
+    return s ? s->n_host : VXORB_E_INVALID;
+}
+
+int vxorb_match_ids(vxorb_handle* h, long long query_id, long long train_id, float radius, float nn_ratio, int mode,
+                    int out_cap, vxorb_match_t* out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!n_out || out_cap < 0 || (out_cap > 0 && !out) || mode < 0 || mode > 2)
+        return fail(h, VXORB_E_INVALID, "bad output arguments or mode");
+    *n_out = 0;
+    const ResidentSet* q = find_set(h, query_id);
+    const ResidentSet* t = find_set(h, train_id);
+    if (!q || !t) return fail(h, VXORB_E_INVALID, "unknown or overwritten set id (frame ids live for 8 single-frame extractions)");
+    if (radius > 0.f && (!q->xy || !t->xy)) return fail(h, VXORB_E_INVALID, "windowed match needs positions on both sets");
+    if (q->n_host <= 0 || t->n_host <= 0) return VXORB_OK;  // orb_matcher.cpp:18-20
+    CK(cudaSetDevice(h->p.device_id));
+    const DevSet dq{q->desc, q->xy, q->n, q->n_host}, dt{t->desc, t->xy, t->n, t->n_host};
+    int rc = run_knn_device(h, dq, dt, radius, mode == 2, nullptr);
+    if (rc) return rc;
+    return finish_match(h, dq, mode == 2 ? 1.f : nn_ratio, mode, out_cap, out, n_out);
 }
 
 // ---- streaming sequence path ---------------------------------------------------------------------
@@ -1358,6 +1554,50 @@ int vxorb_debug_resize(vxorb_handle* h, const uint8_t* src, int sw, int sh, size
     CK(cudaMemcpyAsync(d_taps, taps.data(), taps.size() * 4, cudaMemcpyHostToDevice, s));
     h->launches += launch_resize_single(s0, sw, sh, sp, d0, dw, dh, dp, d_taps, d_taps + dw,
                                         resize_taps_fit_fast_path(taps.data(), dw), s);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy2DAsync(dst, dstride, d0, dp, dw, dh, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return VXORB_OK;
+}
+
+// The production pyramid kernel (resize_band_kernel) on one image: band_rows 16 runs the throughput shape the
+// batched path uses, 8 / 4 the latency shape of small batches and of wide levels.
+int vxorb_debug_resize_band(vxorb_handle* h, const uint8_t* src, int sw, int sh, size_t sstride, uint8_t* dst, int dw,
+                            int dh, size_t dstride, int band_rows) {
+    if (!h) return VXORB_E_INVALID;
+    if (!src || !dst || sw < 1 || sh < 1 || dw < 8 || dh < 8 || sw >= 65536 || sh >= 65536 ||
+        (band_rows != 4 && band_rows != 8 && band_rows != 16))
+        return fail(h, VXORB_E_INVALID, "bad band-resize arguments (dw, dh >= 8; band_rows 4, 8 or 16)");
+    CK(cudaSetDevice(h->p.device_id));
+    const int sp = plane_pitch(sw), dp = plane_pitch(dw);
+    const int words = (dw + 3) / 4;
+    std::vector<uint32_t> taps((size_t)dw + dh);
+    build_resize_taps(sw, dw, taps.data());
+    build_resize_taps(sh, dh, taps.data() + dw);
+    if (!resize_taps_fit_fast_path(taps.data(), dw))
+        return fail(h, VXORB_E_INVALID, "scale too large for the band kernel (four output columns span more than 8 source bytes)");
+    int nb = 0;
+    long long smem = 0;
+    resize_band_extent(taps.data() + dw, dh, sh, sp, band_rows, &nb, &smem);
+    if (smem > 200 * 1024) return fail(h, VXORB_E_INVALID, "band does not fit shared memory");
+    // device tables: ytab[dh] | pad to 16 B | uint4 xw4[words] | uint2 xw2[words]
+    const size_t y_words = ((size_t)dh + 3) & ~(size_t)3;
+    std::vector<uint32_t> tab(y_words + (size_t)words * 6);
+    memcpy(tab.data(), taps.data() + dw, (size_t)dh * 4);
+    build_resize_words(taps.data(), dw, tab.data() + y_words);
+    const size_t sbytes = align_up(plane_bytes(sw, sh), 256), dbytes = align_up(plane_bytes(dw, dh), 256);
+    int rc = ensure_stage_scratch(h, std::max(sbytes, dbytes) + tab.size() * 4 + 256);
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    uint32_t* d_tab = reinterpret_cast<uint32_t*>(h->s_b + dbytes);
+    uint8_t* d0 = h->s_b + plane_origin(dw);
+    CK(cudaMemsetAsync(h->s_a, 0, sbytes, s));
+    CK(cudaMemsetAsync(h->s_b, 0, dbytes, s));
+    CK(cudaMemcpy2DAsync(h->s_a + plane_origin(sw), sp, src, sstride, sw, sh, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_tab, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, s));
+    launch_resize_band(h->s_a, sh, sp, 0, d0, dw, dh, dp, 0, d_tab, reinterpret_cast<const uint4*>(d_tab + y_words),
+                       reinterpret_cast<const uint2*>(d_tab + y_words + (size_t)words * 4), band_rows, nb, (int)smem, 1, s);
+    h->launches += 1;
     CK(cudaGetLastError());
     CK(cudaMemcpy2DAsync(dst, dstride, d0, dp, dw, dh, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));

@@ -502,17 +502,26 @@ int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t
 #ifndef VXORB_BAND_ROWS
 #define VXORB_BAND_ROWS 16
 #endif
+// Band count and the shared-memory bytes of the largest source chunk for bands of `rows` output rows (the last
+// band takes the remainder rows, so it is the largest).
+void resize_band_extent(const uint32_t* ytaps, int dh, int sh, int spitch, int rows, int* n_bands, long long* smem) {
+    const int nb = std::max(1, dh / rows);
+    int worst = 0;
+    for (int b = 0; b < nb; ++b) {
+        const int y0 = b * rows, y1 = (b == nb - 1) ? dh : y0 + rows;
+        const int jlo = (int)(ytaps[y0] & 0xffffu), jhi = std::min((int)(ytaps[y1 - 1] & 0xffffu) + 1, sh - 1);
+        worst = std::max(worst, jhi - jlo + 1);
+    }
+    *n_bands = nb;
+    *smem = (long long)worst * spitch;
+}
+
 bool plan_resize_bands(const uint32_t* ytaps, int dh, int sh, int spitch, int* band_rows, int* n_bands, int* smem) {
     if (dh < 8) return false;
     for (int rows = VXORB_BAND_ROWS; rows >= 4; rows >>= 1) {
-        const int nb = std::max(1, dh / rows);
-        int worst = 0;
-        for (int b = 0; b < nb; ++b) {
-            const int y0 = b * rows, y1 = (b == nb - 1) ? dh : y0 + rows;
-            const int jlo = (int)(ytaps[y0] & 0xffffu), jhi = std::min((int)(ytaps[y1 - 1] & 0xffffu) + 1, sh - 1);
-            worst = std::max(worst, jhi - jlo + 1);
-        }
-        const long long bytes = (long long)worst * spitch;
+        int nb;
+        long long bytes;
+        resize_band_extent(ytaps, dh, sh, spitch, rows, &nb, &bytes);
         if (bytes <= 40 * 1024 || (rows == 4 && bytes <= 200 * 1024)) {
             *band_rows = rows;
             *n_bands = nb;
@@ -521,6 +530,18 @@ bool plan_resize_bands(const uint32_t* ytaps, int dh, int sh, int spitch, int* b
         }
     }
     return false;
+}
+
+// One level through the production band kernel (launch_pyramid and the stage-isolation entry share this):
+// rows == 16 selects the throughput shape, 8 / 4 the latency shape.
+void launch_resize_band(const uint8_t* src_plane, int sh, int spitch, size_t sfstride, uint8_t* dst, int dw, int dh,
+                        int dpitch, size_t dfstride, const uint32_t* ytab, const uint4* xw4, const uint2* xw2, int rows,
+                        int n_bands, int smem, int batch, cudaStream_t s) {
+    const int words = (dw + 3) / 4;
+    dim3 grid(n_bands, batch);
+    auto kern = rows == 16 ? resize_band_kernel<true> : resize_band_kernel<false>;
+    kern<<<grid, 256, smem, s>>>(src_plane, sh, spitch, sfstride, dst, dw, dh, dpitch, dfstride, ytab, xw4, xw2, words, rows,
+                                 n_bands, rows / 2);
 }
 
 cudaError_t init_pyramid_kernels() {
@@ -548,11 +569,9 @@ int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, 
             const bool small = lt.batch < 8 && lt.band_rows[l] > 4;
             const int rows = small ? 4 : lt.band_rows[l];
             const int nb = small ? std::max(1, lt.h[l] / 4) : lt.n_bands[l];
-            dim3 grid(nb, lt.batch);
-            auto kern = rows == 16 ? resize_band_kernel<true> : resize_band_kernel<false>;
-            kern<<<grid, 256, lt.band_smem[l], s>>>(
-                src_plane, lt.h[l - 1], lt.pitch[l - 1], (size_t)lt.fstride[l - 1], db.pyr + lt.off[l], lt.w[l], lt.h[l],
-                lt.pitch[l], (size_t)lt.fstride[l], tab + lt.w[l], xw4, xw2, words, rows, nb, rows / 2);
+            launch_resize_band(src_plane, lt.h[l - 1], lt.pitch[l - 1], (size_t)lt.fstride[l - 1], db.pyr + lt.off[l], lt.w[l],
+                               lt.h[l], lt.pitch[l], (size_t)lt.fstride[l], tab + lt.w[l], xw4, xw2, rows, nb, lt.band_smem[l],
+                               lt.batch, s);
             ++launches;
         }
         return launches;

@@ -117,6 +117,11 @@ bool resize_taps_fit_fast_path(const uint32_t* xtaps, int dw);
 int launch_apron(const LevelTab& lt, const DeviceBuffers& db, int levels, cudaStream_t s);
 void build_resize_words(const uint32_t* xtaps, int dw, uint32_t* out);  // 6 words per output word
 bool plan_resize_bands(const uint32_t* ytaps, int dh, int sh, int spitch, int* band_rows, int* n_bands, int* smem);
+void resize_band_extent(const uint32_t* ytaps, int dh, int sh, int spitch, int rows, int* n_bands, long long* smem);
+// src_plane = start of the source plane allocation (apron included); rows 16 = throughput shape, 8 / 4 = latency shape
+void launch_resize_band(const uint8_t* src_plane, int sh, int spitch, size_t sfstride, uint8_t* dst, int dw, int dh,
+                        int dpitch, size_t dfstride, const uint32_t* ytab, const uint4* xw4, const uint2* xw2, int rows,
+                        int n_bands, int smem, int batch, cudaStream_t s);
 cudaError_t init_pyramid_kernels();
 int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s);
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);

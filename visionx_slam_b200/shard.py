@@ -1,8 +1,26 @@
 """Host-side sharding of independent sequences over ranks (replicas only, no
 data-path collective).  One process per GPU; a rank owns the sequences `shard_sequences` gives it and a
 handle on its own device.  torch.distributed is used for exactly two things: the barrier that brackets a
-timed region and the max-over-ranks of the device time (`max_over_ranks`) — NCCL on the GPU box, gloo in
-the CPU tests."""
+timed region and the max-over-ranks of the device time (`max_over_ranks`) — both on CPU tensors over gloo, on
+the GPU box as in the CPU tests: the path has no collective, so no NCCL communicator is ever created."""
+import os
+
+
+def init_host_group(world):
+    """gloo process group from the torchrun environment (RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT); a no-op
+    for a single rank."""
+    if world <= 1:
+        return
+    import torch.distributed as dist
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("gloo")
+
+
+def host_barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
 
 
 def shard_sequences(n_sequences, world, rank):
@@ -19,7 +37,7 @@ def sequence_seed(base_seed, sequence_id):
     return base_seed + sequence_id
 
 
-def max_over_ranks(values, world, device="cpu"):
+def max_over_ranks(values, world, device="cpu"):  # device stays "cpu": gloo
     """Element-wise MAX of a list of floats over all ranks (identity when world == 1)."""
     if world == 1:
         return [float(v) for v in values]
