@@ -547,7 +547,8 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     clocks = sampler.stop()
     h2d_chunk = int(B * W * H)
-    d2h_chunk = int(B * (cap * (20 + 32 + 12) + 8) + 16)
+    head = min(cap, NKP)  # rows per frame the streaming path copies back (tails beyond n_features only on demand)
+    d2h_chunk = int(B * (head * (20 + 32 + 12) + 16) + 16)
     e2e_nkp = float(np.mean(outs[0]["nk"].array))
     if rank == 0:  # the streamed result of the last chunk written to outs[k] is the same sequence: check it too
         k = (passes - 1) % inflight_max

@@ -1,12 +1,24 @@
 #!/bin/bash
-# one GPU visit: parity tests, bench (ours + reference), ncu launch list, ncu full capture
-set -x
-mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest.log
-tail -5 gpurun_out/pytest.log
-timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
-tail -c 600 gpurun_out/bench.json
-timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on --launch-skip 45 -c 16 -o gpurun_out/full -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
-ls -la gpurun_out
+# One gpurun call: gpu tests, bench line, ncu launch list of the bench command, ncu full set of one serial step.
+# usage: scratch/gpu_round.sh <tag> [skip_tests]
+set -u
+TAG=${1:-r2a}
+OUT=gpurun_out
+mkdir -p $OUT
+nvidia-smi --query-gpu=index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active --format=csv -lms 500 > $OUT/${TAG}_clocks.csv 2>/dev/null &
+SMI=$!
+if [ "${2:-}" != "skip_tests" ]; then
+  timeout 900 python -m pytest tests -m gpu -x -q > $OUT/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" >> $OUT/${TAG}_pytest.log
+  tail -5 $OUT/${TAG}_pytest.log
+fi
+timeout 600 python bench.py --steps 20 --warmup 3 > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench rc=$?"
+tail -c 600 $OUT/${TAG}_bench.json
+timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/${TAG}_bench_reference.json 2>> $OUT/${TAG}_bench.err; echo "ref rc=$?"
+timeout 300 python profiles/prof_step.py > $OUT/${TAG}_prof_plain.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -s 45 -c 28 -f -o $OUT/${TAG}_full python profiles/prof_step.py > $OUT/${TAG}_ncu_full.log 2>&1
+echo "ncu full rc=$?"; cat $OUT/${TAG}_prof_plain.log
+timeout 300 python bench.py --steps 2 --warmup 3 --no-configs --no-cpu-baseline > $OUT/${TAG}_bench_short.json 2>> $OUT/${TAG}_bench.err && \
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 100 -c 400 --csv --log-file $OUT/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 --no-configs --no-cpu-baseline > $OUT/${TAG}_ncu_launches.log 2>&1
+echo "ncu launches rc=$?"
+kill $SMI 2>/dev/null
+ls -la $OUT | head -30

@@ -46,6 +46,14 @@ struct Workspace {
     int batch = 0;          // frames of the chunk in flight / last processed
     bool in_flight = false;
     int* h_status = nullptr;  // pinned: status word copied back with every chunk
+    int* h_counts = nullptr;  // pinned: [max_batch] keypoint rows written, [max_batch] match rows of the chunk in flight
+    struct Tail {             // host destinations of the chunk in flight: rows beyond `head` are fetched on demand
+        vxorb_keypoint* kp;
+        uint8_t* desc;
+        vxorb_match_t* match;
+        float* pts;
+        size_t head;
+    } tail = {nullptr, nullptr, nullptr, nullptr, 0};
     // caller-side per-frame quantities (frame_info.cu)
     unsigned long long* sums = nullptr;   // [max_batch][2]
     vxorb_frame_info* info = nullptr;     // [max_batch]
@@ -834,6 +842,8 @@ int vxorb_create(const vxorb_params* p, vxorb_handle** out) {
         if ((e = cudaEventCreateWithFlags(&w.ev_apron, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
         if ((e = cudaHostAlloc(&w.h_status, sizeof(int) * 4, cudaHostAllocDefault)) != cudaSuccess) return bail(e, "pinned");
         w.h_status[0] = 0;
+        if ((e = cudaHostAlloc(&w.h_counts, sizeof(int) * 2 * (size_t)p->max_batch, cudaHostAllocDefault)) != cudaSuccess)
+            return bail(e, "pinned");
     }
     if ((e = cudaEventCreate(&h->t_begin)) != cudaSuccess) return bail(e, "event");
     if ((e = cudaEventCreate(&h->t_end)) != cudaSuccess) return bail(e, "event");
@@ -858,6 +868,7 @@ void vxorb_destroy(vxorb_handle* h) {
         if (w.ev_fork0) cudaEventDestroy(w.ev_fork0);
         if (w.ev_apron) cudaEventDestroy(w.ev_apron);
         if (w.h_status) cudaFreeHost(w.h_status);
+        if (w.h_counts) cudaFreeHost(w.h_counts);
     }
     for (auto& r : h->ring) {
         cudaFree(r.kp); cudaFree(r.desc); cudaFree(r.xy); cudaFree(r.n);
@@ -1277,26 +1288,54 @@ static int track_submit_common(vxorb_handle* h, const uint8_t* frames, int chann
     Workspace& ws = h->ws[slot];
     if (ws.in_flight) return fail(h, VXORB_E_INVALID, "all pipeline slots in flight; call vxorb_track_wait first");
     cudaStream_t s = ws.stream;
-    rc = channels == 3 ? upload_bgr_frames(h, ws, frames, batch, width, height, stride, frame_stride)
-                       : upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
-    if (rc) return rc;
-    rc = enqueue_chunk(h, ws, batch, radius);
-    if (rc) return rc;
-    if (info_out || pts_out) {
-        rc = enqueue_frame_info(h, ws, batch, pts_out != nullptr);
-        if (rc) return rc;
-    }
+    // Read-back: the first `head` rows of every frame (a strided copy into the caller's [batch][cap] arrays) —
+    // cv::ORB returns n_features keypoints unless response ties push a level over its quota, so the rows
+    // between n_features and the capacity are almost always padding and stay on the device; vxorb_track_wait
+    // fetches the tail of a frame that did overflow.
     const size_t cap = (size_t)h->kp_cap;
-    if (kp_out) CK(cudaMemcpyAsync(kp_out, ws.db.kp + cap, sizeof(vxorb_keypoint) * cap * batch, cudaMemcpyDeviceToHost, s));
-    if (desc_out) CK(cudaMemcpyAsync(desc_out, ws.db.desc + cap * 32, 32 * cap * batch, cudaMemcpyDeviceToHost, s));
-    if (n_kp_out) CK(cudaMemcpyAsync(n_kp_out, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
-    if (match_out) CK(cudaMemcpyAsync(match_out, ws.db.match, sizeof(vxorb_match_t) * cap * batch, cudaMemcpyDeviceToHost, s));
-    if (n_match_out) CK(cudaMemcpyAsync(n_match_out, ws.db.match_n, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
-    if (info_out) CK(cudaMemcpyAsync(info_out, ws.info, sizeof(vxorb_frame_info) * batch, cudaMemcpyDeviceToHost, s));
-    if (pts_out) CK(cudaMemcpyAsync(pts_out, ws.pts, sizeof(float4) * cap * batch, cudaMemcpyDeviceToHost, s));
-    CK(cudaMemcpyAsync(ws.h_status, ws.db.status, sizeof(int) * 4, cudaMemcpyDeviceToHost, s));
+    const size_t head = std::min<size_t>(cap, (size_t)h->p.n_features);
+    auto rows_d2h = [&](void* dst, const void* src, size_t row_bytes) {
+        return cudaMemcpy2DAsync(dst, cap * row_bytes, src, cap * row_bytes, head * row_bytes, (size_t)batch,
+                                 cudaMemcpyDeviceToHost, s);
+    };
+    auto queue = [&]() -> int {
+        int rc2 = channels == 3 ? upload_bgr_frames(h, ws, frames, batch, width, height, stride, frame_stride)
+                                : upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
+        if (rc2) return rc2;
+        rc2 = enqueue_chunk(h, ws, batch, radius);
+        if (rc2) return rc2;
+        if (info_out || pts_out) {
+            rc2 = enqueue_frame_info(h, ws, batch, pts_out != nullptr);
+            if (rc2) return rc2;
+        }
+        if (kp_out) CK(rows_d2h(kp_out, ws.db.kp + cap, sizeof(vxorb_keypoint)));
+        if (desc_out) CK(rows_d2h(desc_out, ws.db.desc + cap * 32, 32));
+        if (n_kp_out) CK(cudaMemcpyAsync(n_kp_out, ws.db.kp_total + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+        if (match_out) CK(rows_d2h(match_out, ws.db.match, sizeof(vxorb_match_t)));
+        if (n_match_out) CK(cudaMemcpyAsync(n_match_out, ws.db.match_n, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+        if (info_out) CK(cudaMemcpyAsync(info_out, ws.info, sizeof(vxorb_frame_info) * batch, cudaMemcpyDeviceToHost, s));
+        if (pts_out) CK(rows_d2h(pts_out, ws.pts, sizeof(float4)));
+        // counts of this chunk for the tail check in vxorb_track_wait (pinned, next to the status word)
+        CK(cudaMemcpyAsync(ws.h_counts, ws.db.kp_n + 1, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(ws.h_counts + h->p.max_batch, ws.db.match_n, sizeof(int) * batch, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(ws.h_status, ws.db.status, sizeof(int) * 4, cudaMemcpyDeviceToHost, s));
+        return VXORB_OK;
+    };
+    rc = queue();
+    if (rc) {
+        // part of the chunk may already be queued (possibly a carry-out that overwrote the handle's carry): drain the
+        // slot and restart the sequence, so the next submit neither races these buffers nor matches against a
+        // carry that belongs to no completed chunk
+        const std::string msg = h->err;
+        cudaStreamSynchronize(s);
+        cudaGetLastError();
+        h->last_slot = -1;
+        h->err = msg + " (chunk dropped; the tracked sequence was reset)";
+        return rc;
+    }
     ws.batch = batch;
     ws.in_flight = true;
+    ws.tail = {kp_out, desc_out, match_out, pts_out, head};
     h->last_slot = slot;
     h->next_slot = (slot + 1) % kSlots;
     *slot_out = slot;
@@ -1327,6 +1366,26 @@ int vxorb_track_wait(vxorb_handle* h, int slot) {
     CK(cudaSetDevice(h->p.device_id));
     CK(cudaStreamSynchronize(ws.stream));
     ws.in_flight = false;
+    // frames whose keypoint or match rows ran past the `head` rows copied with the chunk (response ties): fetch
+    // their tails now; the common case touches nothing
+    const size_t cap = (size_t)h->kp_cap, head = ws.tail.head;
+    bool extra = false;
+    for (int f = 0; f < ws.batch; ++f) {
+        const size_t nk = (size_t)std::min(ws.h_counts[f], h->kp_cap);
+        const size_t nm = (size_t)std::min(ws.h_counts[h->p.max_batch + f], h->kp_cap);
+        const size_t row = (size_t)f * cap + head;
+        if (nk > head) {
+            if (ws.tail.kp) CK(cudaMemcpyAsync(ws.tail.kp + row, ws.db.kp + cap + row, sizeof(vxorb_keypoint) * (nk - head), cudaMemcpyDeviceToHost, ws.stream));
+            if (ws.tail.desc) CK(cudaMemcpyAsync(ws.tail.desc + row * 32, ws.db.desc + (cap + row) * 32, 32 * (nk - head), cudaMemcpyDeviceToHost, ws.stream));
+            extra = true;
+        }
+        if (nm > head) {
+            if (ws.tail.match) CK(cudaMemcpyAsync(ws.tail.match + row, ws.db.match + row, sizeof(vxorb_match_t) * (nm - head), cudaMemcpyDeviceToHost, ws.stream));
+            if (ws.tail.pts) CK(cudaMemcpyAsync(ws.tail.pts + row * 4, reinterpret_cast<const float*>(ws.pts) + row * 4, sizeof(float4) * (nm - head), cudaMemcpyDeviceToHost, ws.stream));
+            extra = true;
+        }
+    }
+    if (extra) CK(cudaStreamSynchronize(ws.stream));
     return check_status(h, ws.h_status[0]);
 }
 

@@ -33,6 +33,9 @@
 // Roofline: HBM, algorithmic bytes = one read of every level pixel (950 532 B per 640x480 frame);
 // the kernel is integer-issue bound.
 #include <cuda.h>  // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
+#include <string.h>
+
+#include <mutex>
 
 #include "vxorb_internal.h"
 
@@ -351,11 +354,66 @@ bool build_plane_maps(const LevelTab& lt, const uint8_t* planes, int box_w, int 
     return true;
 }
 
+namespace {
+
+// The tensor maps of a launch depend only on the planes' base address, the level geometry and the batch: the
+// streaming path launches the same few combinations (one per pipeline slot) over and over, so the last encodings
+// are kept instead of calling the driver's encoder up to kMaxLevels times per launch.
+struct MapKey {
+    const uint8_t* planes;
+    int n_levels, batch;
+    int w[kMaxLevels], h[kMaxLevels], pitch[kMaxLevels], active[kMaxLevels];
+    unsigned long long off[kMaxLevels], fstride[kMaxLevels];
+};
+struct MapEntry {
+    MapKey key;
+    FastMaps maps;
+    unsigned long long stamp = 0;
+    bool used = false;
+};
+constexpr int kMapCache = 16;
+MapEntry g_map_cache[kMapCache];
+unsigned long long g_map_stamp = 0;
+std::mutex g_map_mutex;
+
+bool cached_fast_maps(const LevelTab& lt, const uint8_t* planes, FastMaps* out) {
+    MapKey key;
+    memset(&key, 0, sizeof(key));
+    key.planes = planes;
+    key.n_levels = lt.n_levels;
+    key.batch = lt.batch;
+    for (int l = 0; l < lt.n_levels; ++l) {
+        key.w[l] = lt.w[l]; key.h[l] = lt.h[l]; key.pitch[l] = lt.pitch[l]; key.active[l] = lt.active[l];
+        key.off[l] = lt.off[l]; key.fstride[l] = lt.fstride[l];
+    }
+    std::lock_guard<std::mutex> lock(g_map_mutex);
+    MapEntry* victim = nullptr;  // first unused entry, else the least recently used one
+    for (auto& e : g_map_cache) {
+        if (e.used && memcmp(&e.key, &key, sizeof(key)) == 0) {
+            e.stamp = ++g_map_stamp;
+            *out = e.maps;
+            return true;
+        }
+        if (!victim || (victim->used && (!e.used || e.stamp < victim->stamp))) victim = &e;
+    }
+    if (!build_plane_maps(lt, planes, TWORDS * 4, TROWS, true, victim->maps.m)) {
+        victim->used = false;
+        return false;
+    }
+    victim->key = key;
+    victim->used = true;
+    victim->stamp = ++g_map_stamp;
+    *out = victim->maps;
+    return true;
+}
+
+}  // namespace
+
 int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s) {
     const int tiles = lt.fast_tile_begin[lt.n_levels];
     if (tiles == 0 || lt.batch <= 0) return 0;
     FastMaps maps;
-    if (!build_plane_maps(lt, db.pyr, TWORDS * 4, TROWS, true, maps.m)) return -1;
+    if (!cached_fast_maps(lt, db.pyr, &maps)) return -1;
     const int total = tiles * lt.batch;
     const int grid = total < 148 * kFastCtasPerSm ? total : 148 * kFastCtasPerSm;  // persistent CTAs of 8 warps
     if (threshold >= 128)
