@@ -326,9 +326,12 @@ def bench_per_call(vx, peak):
         assert nm_ids == nm_host, "match by ids differs from match by host descriptors"
         out["match_ids_ms"], out["match_ids_ms_min"] = median_ms(lambda: h1.match_ids_into(ida, idb, mt), 300)
 
-        def frame():
+        state = {"last": idb}
+
+        def frame():  # what Tracking::ProcessFrame does per frame: Extract(curr), Match(last, curr); curr becomes last
             i = h1.extract_into(b, kp, desc, want_id=True)[1]
-            h1.match_ids_into(ida, i, mt)
+            h1.match_ids_into(state["last"], i, mt)
+            state["last"] = i
         out["extract_plus_match_ms"], _ = median_ms(frame, 300)
         out["keypoints"], out["matches"] = int(na), int(nm_host)
         ab = sum(v for k, v in algorithmic_bytes(na).items() if k in EXTRACT_STAGES)

@@ -48,7 +48,7 @@ def test_resize_stage(h, shape, dst):
 @pytest.mark.parametrize("band_rows", [16, 8, 4])
 @pytest.mark.parametrize("shape,dst", [((480, 640), (400, 533)), ((400, 533), (333, 444)), ((278, 370), (231, 309)),
                                        ((161, 214), (134, 179)), ((376, 1241), (313, 1034)), ((1080, 1920), (900, 1600)),
-                                       ((97, 131), (41, 77)), ((50, 64), (40, 64)), ((19, 23), (9, 11))])
+                                       ((97, 131), (49, 77)), ((50, 64), (40, 64)), ((19, 23), (16, 19))])
 def test_resize_band_stage(h, shape, dst, band_rows):
     """The production pyramid kernel in isolation, both instantiations: band_rows 16 is resize_band_kernel<true>
     (the batched throughput shape incl. the shared row tails), 8 / 4 resize_band_kernel<false> (latency shape)."""

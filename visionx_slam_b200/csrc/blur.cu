@@ -23,6 +23,7 @@
 // Packed fma.rn.f32x2 / add.f32x2 (FFMA2 / FADD2) were tried: 25 % fewer instructions, bit-identical
 // output, same time — the fma pipe spends two passes on a packed instruction.
 #include <math.h>
+#include <string.h>
 
 #include "vxorb_internal.h"
 
@@ -41,8 +42,21 @@ __device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t sel) {
 
 }  // namespace
 
+// cv::getGaussianKernel(7, 2, CV_32F) as literals: with the taps as immediates the row and column FMAs take the
+// FFMA-with-immediate form (one operand less to fetch from the register file per instruction); launch_blur
+// checks the literals against the kernel computed the way OpenCV computes it and falls back to the
+// parameter form if they ever differ.
+constexpr float kG0 = 0.0701593235f, kG1 = 0.131074876f, kG2 = 0.190712824f, kG3 = 0.216105938f;
+
+template <bool IMM>
 __global__ void __launch_bounds__(256, 3)
-blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, const GaussK gk) {
+blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, const GaussK gkp) {
+    GaussK gk;
+    if (IMM) {
+        gk.k[0] = kG0; gk.k[1] = kG1; gk.k[2] = kG2; gk.k[3] = kG3; gk.k[4] = kG2; gk.k[5] = kG1; gk.k[6] = kG0;
+    } else {
+        gk = gkp;
+    }
     int l = 0;
     while (l + 1 < lt.n_levels && (int)blockIdx.x >= lt.blur_tile_begin[l + 1]) ++l;
     const int w = lt.w[l], h = lt.h[l], pitch = lt.pitch[l];
@@ -146,7 +160,11 @@ int launch_blur(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
         for (int i = 0; i < 7; ++i) gk.k[i] = (float)(t[i] / sum);
     }
     dim3 grid(ctas, lt.batch);
-    blur_kernel<<<grid, 256, 0, s>>>(lt, db.pyr, db.blur, gk);
+    const float lit[7] = {kG0, kG1, kG2, kG3, kG2, kG1, kG0};
+    if (memcmp(lit, gk.k, sizeof(lit)) == 0)
+        blur_kernel<true><<<grid, 256, 0, s>>>(lt, db.pyr, db.blur, gk);
+    else
+        blur_kernel<false><<<grid, 256, 0, s>>>(lt, db.pyr, db.blur, gk);
     return 1;
 }
 

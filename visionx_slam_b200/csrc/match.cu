@@ -21,25 +21,32 @@ constexpr int kQPerBlock = 128;
 constexpr int kTrainTile = 256;
 constexpr uint32_t kNoKey = 0x7fffffffu;
 
-// 256-bit Hamming distance of a query held in registers against a train row read as two 16-byte vectors.
-// Harley-Seal: the eight XOR words go through a carry-save adder tree (LOP3 pairs) down to four words
-// of weight 1, 2, 4, 8, so a pair costs 4 POPC (the scarce unit: 16 lanes/clk/SM) instead of 8.
+// 256-bit Hamming distance of a query held in registers against a train row read as two 16-byte vectors, delivered
+// as the packed 2-NN key (distance << 20 | train index).  The integer (alu) pipe is what bounds the kernel (85 % busy
+// in the ncu capture, profiles/r2a_*), so the count is arranged to cost it as little as possible: the eight XOR words
+// go through four carry-save adders (2 LOP3 each) down to two words of weight 1, one of weight 2 and one of weight 4
+//     x0+x1+x2 = sa + 2 ca,  x3+x4+x5 = sb + 2 cb,  x6+x7+sa = sc + 2 cc,  ca+cb+cc = se + 2 ce
+//     popc(x0..x7) = popc(sb) + popc(sc) + 2 popc(se) + 4 popc(ce)
+// i.e. 16 LOP3 + 4 POPC per pair (8 LOP3 + 8 POPC + 7 IADD without the tree; the full Harley-Seal tree down to one word
+// per weight costs 22 LOP3 for the same 4 POPC), and the weighted sum and the index go into the key with four IMADs,
+// which run on the otherwise idle fma pipe.
 __device__ __forceinline__ void csa(uint32_t a, uint32_t b, uint32_t c, uint32_t& sum, uint32_t& carry) {
     sum = a ^ b ^ c;
     carry = (a & b) | (c & (a ^ b));
 }
-__device__ __forceinline__ int hamming256(const uint32_t (&q)[8], const uint4 lo, const uint4 hi) {
+__device__ __forceinline__ uint32_t hamming_key(const uint32_t (&q)[8], const uint4 lo, const uint4 hi, uint32_t idx) {
     const uint32_t x0 = q[0] ^ lo.x, x1 = q[1] ^ lo.y, x2 = q[2] ^ lo.z, x3 = q[3] ^ lo.w;
     const uint32_t x4 = q[4] ^ hi.x, x5 = q[5] ^ hi.y, x6 = q[6] ^ hi.z, x7 = q[7] ^ hi.w;
     uint32_t sa, ca, sb, cb, sc, cc, se, ce;
     csa(x0, x1, x2, sa, ca);
     csa(x3, x4, x5, sb, cb);
     csa(x6, x7, sa, sc, cc);
-    const uint32_t ones = sb ^ sc, cd = sb & sc;
     csa(ca, cb, cc, se, ce);
-    const uint32_t twos = se ^ cd, cf = se & cd;
-    const uint32_t fours = ce ^ cf, eights = ce & cf;
-    return __popc(ones) + 2 * __popc(twos) + 4 * __popc(fours) + 8 * __popc(eights);
+    uint32_t key = (uint32_t)__popc(sb) * (1u << 20) + idx;
+    key = (uint32_t)__popc(sc) * (1u << 20) + key;
+    key = (uint32_t)__popc(se) * (2u << 20) + key;
+    key = (uint32_t)__popc(ce) * (4u << 20) + key;
+    return key;
 }
 
 }  // namespace
@@ -112,8 +119,7 @@ knn2_kernel(const MatchArgs a) {
                 const uint4 hi = *reinterpret_cast<const uint4*>(&tdesc[j][4]);
 #pragma unroll
                 for (int u = 0; u < QPT; ++u) {
-                    const int d = hamming256(q[u], lo, hi);
-                    const uint32_t key = ((uint32_t)d << 20) | (uint32_t)(t0 + j);
+                    const uint32_t key = hamming_key(q[u], lo, hi, (uint32_t)(t0 + j));
                     k1[u] = min(k1[u], max(k0[u], key));
                     k0[u] = min(k0[u], key);
                 }
@@ -134,8 +140,7 @@ knn2_kernel(const MatchArgs a) {
                     const uint4 hi = *reinterpret_cast<const uint4*>(&tdesc[j][4]);
 #pragma unroll
                     for (int u = 0; u < QPT; ++u) {
-                        const int d = hamming256(q[u], lo, hi);
-                        const uint32_t key = in[u] ? (((uint32_t)d << 20) | (uint32_t)(t0 + j)) : kNoKey;
+                        const uint32_t key = in[u] ? hamming_key(q[u], lo, hi, (uint32_t)(t0 + j)) : kNoKey;
                         k1[u] = min(k1[u], max(k0[u], key));
                         k0[u] = min(k0[u], key);
                     }
