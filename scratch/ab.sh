@@ -1,14 +1,12 @@
 #!/bin/bash
-# A/B of library variants by the bench's resident value: scratch/ab.sh ROUNDS variant.so...  (default library first)
-R=${1:-3}; shift
-cp visionx_slam_b200/libvxorb.so /tmp/libvxorb_default.so
-for i in $(seq $R); do
-  for f in /tmp/libvxorb_default.so "$@"; do
-    cp $f visionx_slam_b200/libvxorb.so
-    timeout 300 python bench.py --no-cpu-baseline 2>/dev/null | python -c "
-import json,sys
-d=json.loads(sys.stdin.read())
-print('$f', 'value',round(d['value']),'e2e',round(d['e2e']['value']),'serial_ms',round(d['schedule']['ms_per_step_serial_instrumented'],4))"
-  done
+# Builds compile-time variants of libvxorb.so for A/B runs on the GPU box:
+#   scratch/ab.sh name1 "-DFLAG=1" name2 "-DOTHER=2 -DX=3" ...
+# -> visionx_slam_b200/variants/libvxorb_<name>.so (git-ignored *.so; travels with gpurun)
+set -e
+cd "$(dirname "$0")/../visionx_slam_b200/csrc"
+mkdir -p ../variants
+while [ $# -ge 2 ]; do
+  name=$1; flags=$2; shift 2
+  make -s BUILD=build_$name OUT=../variants/libvxorb_$name.so EXTRA="$flags" > /dev/null
+  echo "built variant $name ($flags)"
 done
-cp /tmp/libvxorb_default.so visionx_slam_b200/libvxorb.so

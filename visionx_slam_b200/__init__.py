@@ -21,7 +21,8 @@ import numpy as np
 from . import synth  # noqa: F401
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvxorb.so")
+# VXORB_LIB selects another build of the same library (A/B runs of compile-time variants, scratch/ab.sh)
+LIB_PATH = os.environ.get("VXORB_LIB") or os.path.join(_HERE, "libvxorb.so")
 
 KEYPOINT_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("response", "<f4"), ("angle", "<f4"),
                            ("octave", "<i4")])

@@ -44,8 +44,11 @@ namespace vxorb {
 namespace {
 
 constexpr int FW = kFastScoreW, FSR = kFastScoreH;   // score region of a tile
-constexpr int TROWS = FSR + 6, TWORDS = FW / 4 + 8;  // tile rows, 32-bit words per tile row: 160 B, because a TMA box must
-                                                     // START on a 16 B boundary of the plane row, so up to 12 B of slack precede the tile
+constexpr int TROWS = FSR + 6, TWORDS = FW / 4 + 12; // tile rows, 32-bit words per tile row: 136 B of pixels + up to 12 B of slack (a
+                                                     // TMA box must START on a 16 B boundary of the plane row) = 148 -> 160 B would do,
+                                                     // but 176 B = 44 words puts consecutive rows 12 banks apart, so the 8 rows of a
+                                                     // row group land in 8 different bank groups (40 words: only 4)
+constexpr int SCP = FW + 4;                          // score-map row pitch: 33 words, rows never share a bank at equal columns
 constexpr uint32_t kTileBytes = TROWS * TWORDS * 4;
 constexpr int TPITCH = TWORDS * 4;
 constexpr int RPW = FSR / 8;                          // score rows per warp
@@ -114,7 +117,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
         uint32_t w[TROWS][TWORDS];  // TMA destinations must be 128 B aligned: the struct alignment pads buffer 1
     };
     __shared__ TileBuf tiles[2];
-    __shared__ __align__(16) uint8_t score[2][FSR][FW];  // tile t uses map t & 1; a warp writes only its own rows
+    __shared__ __align__(16) uint8_t score[2][FSR][SCP];  // tile t uses map t & 1; a warp writes only its own rows
     __shared__ uint16_t wq[8][WQCAP];       // per-warp list: stage-1 survivors, then corners, then NMS survivors
     __shared__ __align__(8) unsigned long long mbar[2];
     __shared__ int4 info[4];                // tile descriptors (level, X, Y, frame), ring over 4 tiles
@@ -165,7 +168,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
 
         // this warp's rows of the score map (last read by the NMS of tile t - 2, two barriers ago)
 #pragma unroll
-        for (int i = 0; i < RPW; ++i) reinterpret_cast<uint32_t*>(sc + (i * 8 + warp) * FW)[lane] = 0u;
+        for (int i = 0; i < RPW; ++i) reinterpret_cast<uint32_t*>(sc + (i * 8 + (warp ^ i)) * SCP)[lane] = 0u;
 
         // score domain (global coordinates, inclusive)
         const int sx_min = max(3, border - 1), sx_max = min(w - 4, w - border);
@@ -188,7 +191,10 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
             const uint32_t yspan = sy_max >= sy_min ? (uint32_t)(sy_max - sy_min) : 0u;
 #pragma unroll
             for (int i = 0; i < RPW; ++i) {
-                const int r = i * 8 + warp;  // rows interleaved over warps: a corner cluster spreads over several warps
+                // rows interleaved over warps (a corner cluster spreads over several warps); within row group i the warp
+                // takes row warp ^ i, so its six rows sit in six different bank groups of the tile buffer: vertical
+                // structures, whose survivors share columns, then do not collide in the ring gathers of stage 2
+                const int r = i * 8 + (warp ^ i);
                 uint32_t q = 0;
                 if ((uint32_t)(r - ylo) <= yspan) {  // sy_min <= Y + r <= sy_max in one unsigned compare
                     const uint32_t* row = &tile[r + 3][lane + wo];
@@ -215,11 +221,12 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
             }
             nq = __shfl_sync(0xffffffffu, incl, 31);
             int pos = incl - cnt;
-            const int rowbase = warp * FW + 4 * lane;
+            const int colbase = 4 * lane;
             while (acc) {
                 const int b = __ffs(acc) - 1;
                 acc &= acc - 1;
-                q16[pos++] = (uint16_t)(rowbase + (b >> 2) * (8 * FW) + (b & 3));
+                const int i = b >> 2;
+                q16[pos++] = (uint16_t)(((i * 8 + (warp ^ i)) << 7) + colbase + (b & 3));
             }
         }
         __syncwarp();
@@ -256,7 +263,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                     best = __vmaxs2(best, m9[15]);
                     const int s = max((int)(best & 0xffffu), (int)(best >> 16)) - 257;
                     if (s >= threshold) {
-                        sc[idx] = (uint8_t)s;
+                        sc[idx + (idx >> 7) * (SCP - FW)] = (uint8_t)s;
                         corner = true;
                     }
                 }
@@ -288,11 +295,11 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                                         gy >= border && gx < ex_max && gy < ey_max;
                     // branch-free: strictly greater than all eight neighbours <=> greater than their maximum
                     // (lanes outside the emission domain read around a safe interior cell instead)
-                    const uint8_t* p = sc + (inside ? idx : FW + 1);
+                    const uint8_t* p = sc + (inside ? idx + r * (SCP - FW) : SCP + 1);
                     const int s = p[0];
-                    const int m0 = max(max((int)p[-FW - 1], (int)p[-FW]), (int)p[-FW + 1]);
-                    const int m1 = max(max((int)p[-1], (int)p[1]), (int)p[FW - 1]);
-                    const int m2 = max((int)p[FW], (int)p[FW + 1]);
+                    const int m0 = max(max((int)p[-SCP - 1], (int)p[-SCP]), (int)p[-SCP + 1]);
+                    const int m1 = max(max((int)p[-1], (int)p[1]), (int)p[SCP - 1]);
+                    const int m2 = max((int)p[SCP], (int)p[SCP + 1]);
                     keep = inside && s > max(max(m0, m1), m2);
                 }
                 __syncwarp();
@@ -309,7 +316,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                 uint32_t* out = cand + lt.cand_off[l] + (size_t)f * cap;
                 for (int e = lane; e < nk; e += 32) {
                     const int idx = q16[e];
-                    const uint32_t s = sc[idx];
+                    const uint32_t s = sc[idx + (idx >> 7) * (SCP - FW)];
                     if (obase + e < cap)
                         out[obase + e] = (s << 24) | ((uint32_t)(Y + (idx >> 7)) << 12) | (uint32_t)(X + (idx & 127));
                 }

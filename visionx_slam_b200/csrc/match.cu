@@ -20,6 +20,23 @@ namespace {
 constexpr int kQPerBlock = 128;
 constexpr int kTrainTile = 256;
 constexpr uint32_t kNoKey = 0x7fffffffu;
+// Packed 2-NN key of the brute-force kernels: distance * kKeyMul + train index, ordered like the pair (distance,
+// index), so ties go to the lowest index.  kKeyMul is 2^20 + 1 rather than 2^20: with a power of two ptxas turns
+// the multiply-adds that assemble the key into shift-adds (LEA) on the alu pipe, which is the pipe that bounds the
+// kernel; a non-power-of-two keeps them IMADs on the fma pipe.  Indices stay below 2^20.
+#ifndef VXORB_KNN_PAIRUPD
+#define VXORB_KNN_PAIRUPD 1
+#endif
+#ifndef VXORB_KEY_POW2
+#define VXORB_KEY_POW2 0
+#endif
+constexpr uint32_t kKeyMul = VXORB_KEY_POW2 ? (1u << 20) : (1u << 20) + 1u;
+__device__ __forceinline__ int key_dist(uint32_t k) { return (int)(k / kKeyMul); }
+__device__ __forceinline__ int key_idx(uint32_t k) { return (int)(k - (k / kKeyMul) * kKeyMul); }
+__device__ __forceinline__ int4 key_row(uint32_t k0, uint32_t k1) {
+    return make_int4(k0 == kNoKey ? -1 : key_idx(k0), k1 == kNoKey ? -1 : key_idx(k1), k0 == kNoKey ? 0 : key_dist(k0),
+                     k1 == kNoKey ? 0 : key_dist(k1));
+}
 
 // 256-bit Hamming distance of a query held in registers against a train row read as two 16-byte vectors, delivered
 // as the packed 2-NN key (distance << 20 | train index).  The integer (alu) pipe is what bounds the kernel (85 % busy
@@ -42,10 +59,10 @@ __device__ __forceinline__ uint32_t hamming_key(const uint32_t (&q)[8], const ui
     csa(x3, x4, x5, sb, cb);
     csa(x6, x7, sa, sc, cc);
     csa(ca, cb, cc, se, ce);
-    uint32_t key = (uint32_t)__popc(sb) * (1u << 20) + idx;
-    key = (uint32_t)__popc(sc) * (1u << 20) + key;
-    key = (uint32_t)__popc(se) * (2u << 20) + key;
-    key = (uint32_t)__popc(ce) * (4u << 20) + key;
+    uint32_t key = (uint32_t)__popc(sb) * kKeyMul + idx;
+    key = (uint32_t)__popc(sc) * kKeyMul + key;
+    key = (uint32_t)__popc(se) * (2u * kKeyMul) + key;
+    key = (uint32_t)__popc(ce) * (4u * kKeyMul) + key;
     return key;
 }
 
@@ -113,6 +130,35 @@ knn2_kernel(const MatchArgs a) {
                 txy[i] = __ldg(reinterpret_cast<const float2*>(a.t_xy + ((size_t)pair * a.t_pair_stride + t0) * 2) + i);
         __syncthreads();
         if (!windowed) {
+#if VXORB_KNN_PAIRUPD
+            // two train rows per step: the two smallest of {k0, k1, a, b} in five min/max operations instead of six
+            int j = 0;
+#pragma unroll 2
+            for (; j + 1 < tn; j += 2) {
+                const uint4 lo = *reinterpret_cast<const uint4*>(&tdesc[j][0]);
+                const uint4 hi = *reinterpret_cast<const uint4*>(&tdesc[j][4]);
+                const uint4 lo2 = *reinterpret_cast<const uint4*>(&tdesc[j + 1][0]);
+                const uint4 hi2 = *reinterpret_cast<const uint4*>(&tdesc[j + 1][4]);
+#pragma unroll
+                for (int u = 0; u < QPT; ++u) {
+                    const uint32_t ka = hamming_key(q[u], lo, hi, (uint32_t)(t0 + j));
+                    const uint32_t kb = hamming_key(q[u], lo2, hi2, (uint32_t)(t0 + j + 1));
+                    const uint32_t m = min(ka, kb), M = max(ka, kb);
+                    k1[u] = __vimin3_u32(max(k0[u], m), k1[u], M);
+                    k0[u] = min(k0[u], m);
+                }
+            }
+            if (j < tn) {
+                const uint4 lo = *reinterpret_cast<const uint4*>(&tdesc[j][0]);
+                const uint4 hi = *reinterpret_cast<const uint4*>(&tdesc[j][4]);
+#pragma unroll
+                for (int u = 0; u < QPT; ++u) {
+                    const uint32_t key = hamming_key(q[u], lo, hi, (uint32_t)(t0 + j));
+                    k1[u] = min(k1[u], max(k0[u], key));
+                    k0[u] = min(k0[u], key);
+                }
+            }
+#else
 #pragma unroll 4
             for (int j = 0; j < tn; ++j) {
                 const uint4 lo = *reinterpret_cast<const uint4*>(&tdesc[j][0]);
@@ -124,6 +170,7 @@ knn2_kernel(const MatchArgs a) {
                     k0[u] = min(k0[u], key);
                 }
             }
+#endif
         } else {
             for (int j = 0; j < tn; ++j) {
                 const float2 p = txy[j];
@@ -154,9 +201,7 @@ knn2_kernel(const MatchArgs a) {
         if (a.splits > 1) {
             a.part[((size_t)pair * a.splits + blockIdx.z) * a.max_q + qi[u]] = make_uint2(k0[u], k1[u]);
         } else {
-            reinterpret_cast<int4*>(a.knn + (size_t)pair * a.knn_stride)[qi[u]] =
-                make_int4(k0[u] == kNoKey ? -1 : (int)(k0[u] & 0xfffffu), k1[u] == kNoKey ? -1 : (int)(k1[u] & 0xfffffu),
-                          k0[u] == kNoKey ? 0 : (int)(k0[u] >> 20), k1[u] == kNoKey ? 0 : (int)(k1[u] >> 20));
+            reinterpret_cast<int4*>(a.knn + (size_t)pair * a.knn_stride)[qi[u]] = key_row(k0[u], k1[u]);
         }
     }
 }
@@ -176,9 +221,7 @@ knn2_merge_kernel(const MatchArgs a) {
         k0 = min(k0, p.x);
         k1 = min(k1, p.y);  // p.y >= p.x: it can only displace the second entry
     }
-    reinterpret_cast<int4*>(a.knn + (size_t)pair * a.knn_stride)[qi] =
-        make_int4(k0 == kNoKey ? -1 : (int)(k0 & 0xfffffu), k1 == kNoKey ? -1 : (int)(k1 & 0xfffffu),
-                  k0 == kNoKey ? 0 : (int)(k0 >> 20), k1 == kNoKey ? 0 : (int)(k1 >> 20));
+    reinterpret_cast<int4*>(a.knn + (size_t)pair * a.knn_stride)[qi] = key_row(k0, k1);
 }
 
 // ---- windowed 2-NN over a uniform cell grid ------------------------------------------------------
@@ -504,12 +547,18 @@ int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     const bool masked = (a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr;
     // two queries per thread pay off once a pair alone brings enough query blocks (measured: 4000 x 16384
     // 0.303 -> 0.242 ms; 128 pairs of 1000 x 1000 lose occupancy with it)
-    const int qpt = (masked || a.max_q < 2048) ? 1 : 2;
+#ifndef VXORB_KNN_QPT2_MIN
+#define VXORB_KNN_QPT2_MIN 2048
+#endif
+    const int qpt = (masked || a.max_q < VXORB_KNN_QPT2_MIN) ? 1 : 2;
     const int qblocks = (a.max_q + kQPerBlock * qpt - 1) / (kQPerBlock * qpt);
     const int tiles = (a.max_t + kTrainTile - 1) / kTrainTile;
     int splits = 1;
+#ifndef VXORB_KNN_CTA_TARGET
+#define VXORB_KNN_CTA_TARGET (2 * 148)
+#endif
     if (a.part && a.max_t > 0) {
-        splits = (2 * 148 + qblocks * a.pairs - 1) / (qblocks * a.pairs);
+        splits = (VXORB_KNN_CTA_TARGET + qblocks * a.pairs - 1) / (qblocks * a.pairs);
         splits = splits < 1 ? 1 : splits;
         splits = splits > tiles ? tiles : splits;
         splits = splits > kMaxTrainSplits ? kMaxTrainSplits : splits;
