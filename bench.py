@@ -436,6 +436,33 @@ def bench_c4(vx, peak, popc_peak):
     return out
 
 
+def fabric_probe(local_rank, world, h2d_bytes, d2h_bytes, host_barrier, iters=24):
+    """What this host can feed this rank's GPU while every other rank does the same: plain pinned cudaMemcpyAsync
+    loops through torch (no library code), the chunk's host->device bytes on one stream with its device->host
+    bytes on another.  Returns this rank's host->device GB/s.  The end-to-end figure cannot exceed it."""
+    import torch
+    torch.cuda.set_device(local_rank)
+    host = [torch.empty(h2d_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    dev = [torch.empty(h2d_bytes, dtype=torch.uint8, device="cuda") for _ in range(2)]
+    back_d = torch.empty(d2h_bytes, dtype=torch.uint8, device="cuda")
+    back_h = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory()
+    s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def run(n):
+        torch.cuda.synchronize()
+        host_barrier(world)
+        t0 = time.perf_counter()
+        for i in range(n):
+            with torch.cuda.stream(s_up):
+                dev[i % 2].copy_(host[i % 2], non_blocking=True)
+            with torch.cuda.stream(s_dn):
+                back_h.copy_(back_d, non_blocking=True)
+        torch.cuda.synchronize()
+        return h2d_bytes * n / (time.perf_counter() - t0) / 1e9
+    run(4)
+    return run(iters)
+
+
 def run_ours(args, rank, world, local_rank):
     import visionx_slam_b200 as vx
     from visionx_slam_b200.shard import (aggregate_throughput, host_barrier, init_host_group, max_over_ranks,
@@ -577,12 +604,15 @@ def run_ours(args, rank, world, local_rank):
     ms_e2e_win = max(win_dev, win_wall)
 
     popc_peak = h.measure_popc_rate()
+    link_gbs = fabric_probe(local_rank, world, h2d_chunk, d2h_chunk, host_barrier)
 
     # -------- max over ranks ----------------------------------------------------------------------
-    ms_resident_max, ms_e2e_max, ms_res_win_max, ms_e2e_win_max = max_over_ranks(
-        [ms_resident, ms_e2e, ms_res_win, ms_e2e_win], world)
+    ms_resident_max, ms_e2e_max, ms_res_win_max, ms_e2e_win_max, inv_link_max = max_over_ranks(
+        [ms_resident, ms_e2e, ms_res_win, ms_e2e_win, 1.0 / link_gbs], world)
     value = aggregate_throughput(B * passes, ms_resident_max, world)
     e2e_value = aggregate_throughput(B * passes, ms_e2e_max, world)
+    link_min_gbs = 1.0 / inv_link_max  # the slowest rank's link sets the step (max over ranks)
+    fabric_ceiling = world * link_min_gbs * 1e9 / (W * H)
 
     # -------- roofline of the dominant extraction kernel family, per-stage table ------------------
     peak, peak_src = peaks()
@@ -655,7 +685,11 @@ def run_ours(args, rank, world, local_rank):
                     # host->device link rate the streaming path sustained (this rank); a PCIe Gen5 x16 link tops
                     # out near 52-55 GB/s with the D2H running beside it (scratch/h2d_test.cu), which caps e2e
                     "h2d_gbs": h2d_chunk * passes / (ms_e2e * 1e-3) / 1e9,
-                    "d2h_gbs": d2h_chunk * passes / (ms_e2e * 1e-3) / 1e9},
+                    "d2h_gbs": d2h_chunk * passes / (ms_e2e * 1e-3) / 1e9,
+                    # host fabric probe in the same run: pinned copies of one chunk's bytes in both directions on every
+                    # rank at once, no library code; the slowest rank's host->device rate bounds the whole-job e2e rate
+                    "fabric_probe": {"h2d_gbs_slowest_rank_with_d2h": link_min_gbs, "ceiling_frames_per_s": fabric_ceiling,
+                                     "e2e_frac_of_ceiling": e2e_value / fabric_ceiling}},
             "gpu_launches": int(launches_timed),
             "parity_checked": True, "parity": parity,
             "windowed": {"note": "BASELINE config 2's matcher (square window r = 32 px, cv knnMatch(mask)) instead of brute force",

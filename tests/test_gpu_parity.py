@@ -534,6 +534,29 @@ def test_bench_batch_shapes_vs_oracle(batch):
                 assert np.array_equal(matches_as_rows(m), matches_as_rows(ref_c[i])), f"resident r={radius} frame {i}"
 
 
+def test_pipelined_passes_are_deterministic():
+    """Race check by repetition (compute-sanitizer racecheck is closed on this GPU pool): 60 resident passes of a
+    16-frame chunk, pipelined over the slots with the blur on side streams, windowed and brute-force matchers in
+    turn; every pass of the same matcher must produce the same bytes (FAST's double-buffered tiles and score maps,
+    describe's recycled cp.async windows and the carry between slots are the places a race would show)."""
+    import hashlib
+    frames = synth_sequence(640, 480, 16, seed=77)
+    with vx.VxOrb(max_batch=16) as hx:
+        hx.resident_upload(frames)
+        for radius in (32.0, 0.0):
+            hx.resident_run(radius)
+            digests = set()
+            for i in range(30):
+                hx.resident_run(radius)
+                if i % 3 == 2:  # fetch synchronises only every third pass, so passes really overlap
+                    res = hx.resident_fetch()
+                    digests.add(hashlib.sha256(b"".join(k.tobytes() + d.tobytes() + m.tobytes() for k, d, m in res)).hexdigest())
+            assert len(digests) == 1, f"radius {radius}: {len(digests)} different results over 10 fetches"
+        okp, odesc = oracle.orb_extract(frames[5])
+        assert_kp_equal(res[5][0], okp)
+        assert np.array_equal(res[5][1], odesc)
+
+
 def test_bench_batch_kitti_shape_vs_oracle():
     """1241x376, 2000 keypoints, batch 8 (>= 8: the throughput instantiations on BASELINE config 3's geometry)."""
     frames = synth_sequence(1241, 376, 8, seed=5)

@@ -195,6 +195,7 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
         const int kx = __shfl_sync(0xffffffffu, x, i), ky = __shfl_sync(0xffffffffu, y, i);
         const int kl = __shfl_sync(0xffffffffu, level, i);
         const int pitch = lt.pitch[kl];
+        VX_CHECK(kl >= 0 && kl < lt.n_levels && kx >= kEdge && ky >= kEdge && kx < lt.w[kl] - kEdge && ky < lt.h[kl] - kEdge);
         const uint8_t* g = pyr + lt.off[kl] + (size_t)f * lt.fstride[kl] + (ptrdiff_t)(ky - 15) * pitch + ((kx - 15) & ~15);
         const uint32_t d = win0 + (i % kDepthA) * kPaStride;
 #pragma unroll
@@ -208,6 +209,7 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
         const int kx = __shfl_sync(0xffffffffu, x, i), ky = __shfl_sync(0xffffffffu, y, i);
         const int kl = __shfl_sync(0xffffffffu, level, i);
         const int pitch = lt.pitch[kl];
+        VX_CHECK(kl >= 0 && kl < lt.n_levels && kx >= kEdge && ky >= kEdge && kx < lt.w[kl] - kEdge && ky < lt.h[kl] - kEdge);
         const uint8_t* g = blur + lt.off[kl] + (size_t)f * lt.fstride[kl] + (ptrdiff_t)(ky - 18) * pitch + ((kx - 18) & ~15);
         const uint32_t d = win0 + (i % kDepthB) * kPbStride;
 #pragma unroll
@@ -313,10 +315,13 @@ describe_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint8_
                 const float rx = __fsub_rn(__fmul_rn(xx, c), __fmul_rn(yy, s));
                 const float ry = __fadd_rn(__fmul_rn(xx, s), __fmul_rn(yy, c));
                 const uint32_t bx = __float_as_uint(__fadd_rn(rx, magic)), by = __float_as_uint(__fadd_rn(ry, magic));
+                VX_CHECK(bc + by * (uint32_t)kPbW + bx >= win0 + slot * kPbStride &&
+                         bc + by * (uint32_t)kPbW + bx < win0 + slot * kPbStride + kPbBytes);  // gather inside this keypoint's window
                 t[e] = lds_u8(bc + by * (uint32_t)kPbW + bx);
             }
             byte |= (t[0] < t[1] ? 1u : 0u) << k;
         }
+        VX_CHECK(g0 + i < kp_cap);
         desc_out[((size_t)f * kp_cap + g0 + i) * 32 + lane] = (uint8_t)byte;
         __syncwarp();  // every lane is done with this slot before it is refilled
         if (i + kDepthB < n_here) load_b(i + kDepthB);

@@ -226,6 +226,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                 const int b = __ffs(acc) - 1;
                 acc &= acc - 1;
                 const int i = b >> 2;
+                VX_CHECK(pos >= 0 && pos < WQCAP && i < RPW);
                 q16[pos++] = (uint16_t)(((i * 8 + (warp ^ i)) << 7) + colbase + (b & 3));
             }
         }
@@ -245,6 +246,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                 int idx = 0;
                 if (e < nq) {
                     idx = q16[e];
+                    VX_CHECK((idx >> 7) < FSR && 4 * wo + 4 + (idx & 127) + 3 < TPITCH);  // ring stays inside the tile buffer
                     const uint8_t* tp = t8 + (idx >> 7) * TPITCH + (idx & 127);
                     const uint32_t v = tp[0];
                     const uint32_t c0 = v * 0xFFFFu + 0x01000100u;  // (256 - v) | (256 + v) << 16
@@ -269,6 +271,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                 }
                 __syncwarp();  // every lane has read its entry before the front of the list is overwritten
                 const uint32_t m = __ballot_sync(0xffffffffu, corner);
+                VX_CHECK(nc + __popc(m) <= e0 + 32 && nc + __popc(m) <= WQCAP);  // compaction never overtakes the read cursor
                 if (corner) q16[nc + __popc(m & lt_mask)] = (uint16_t)idx;
                 nc += __popc(m);
             }
@@ -295,6 +298,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                                         gy >= border && gx < ex_max && gy < ey_max;
                     // branch-free: strictly greater than all eight neighbours <=> greater than their maximum
                     // (lanes outside the emission domain read around a safe interior cell instead)
+                    VX_CHECK(r < FSR && (!inside || (r >= 1 && r + 1 < FSR && c >= 1 && c + 1 < FW)));
                     const uint8_t* p = sc + (inside ? idx + r * (SCP - FW) : SCP + 1);
                     const int s = p[0];
                     const int m0 = max(max((int)p[-SCP - 1], (int)p[-SCP]), (int)p[-SCP + 1]);
@@ -317,6 +321,7 @@ fast_kernel(const LevelTab lt, const __grid_constant__ FastMaps maps, uint32_t* 
                 for (int e = lane; e < nk; e += 32) {
                     const int idx = q16[e];
                     const uint32_t s = sc[idx + (idx >> 7) * (SCP - FW)];
+                    VX_CHECK(Y + (idx >> 7) < h && X + (idx & 127) < w);
                     if (obase + e < cap)
                         out[obase + e] = (s << 24) | ((uint32_t)(Y + (idx >> 7)) << 12) | (uint32_t)(X + (idx & 127));
                 }

@@ -357,6 +357,7 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
         const float2 p = __ldg(txy_g + i);
         const int cell = cell_of(p.y, orgy, invy, kGridY) * kGridX + cell_of(p.x, orgx, invx, kGridX);
         const int pos = atomicAdd(&cursor[cell], 1);
+        VX_CHECK(cell >= 0 && cell < kCells && pos >= 0 && pos < nt);
         txy[pos] = p;
         tidx[pos] = i;
         tdesc[2 * pos] = __ldg(reinterpret_cast<const uint4*>(tbase + (size_t)i * 32));
@@ -411,6 +412,7 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
         uint32_t k0 = kNoKey, k1 = kNoKey;
         for (int cy = cy0; cy <= cy1; ++cy) {
             const int j0 = cell_start[cy * kGridX + cx0], j1 = cell_start[cy * kGridX + cx1 + 1];
+            VX_CHECK(j0 >= 0 && j1 <= nt && cy >= 0 && cy < kGridY && cx0 >= 0 && cx1 < kGridX);
             for (int j = j0; j < j1; ++j) {
                 const float2 p = txy[j];
                 if (fabsf(__fsub_rn(qx, p.x)) <= r && fabsf(__fsub_rn(qy, p.y)) <= r) {

@@ -336,6 +336,7 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
         uint8_t* const dcol = dst + 4 * k;  // a level plane is far below 4 GB: 32-bit row offsets from here
         // horizontal pass of one source row for this lane's output word: 4 x (p0 * c0 + p1 * c1), 8.8 fixed point
         auto hpass = [&](int j, uint32_t (&hv)[4]) {
+            VX_CHECK(j >= jlo && j <= jhi && wofs + 2 < spitch_w);  // inside the band's source chunk
             const uint32_t* p = sm_w + (j - jlo) * spitch_w + wofs;
             const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
             const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);

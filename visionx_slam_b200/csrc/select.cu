@@ -36,6 +36,7 @@ __device__ __forceinline__ uint32_t float_key(float v) {
 // Ix = d[y-1] + 2 d[y] + d[y+1], Iy = s[y+1] - s[y-1].  Integer sums are exact, so the grouping does
 // not matter; the float combine is un-fused in OpenCV's association.
 __device__ __forceinline__ float harris_thread(const uint8_t* __restrict__ img, int pitch, int x, int y) {
+    VX_CHECK(x >= 4 && y >= 4);  // the 9 x 9 window of a candidate (border 31) never leaves the plane
     const uint8_t* base = img + (ptrdiff_t)(y - 4) * pitch + (x - 4);
     const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(base) & 3u) * 8u;
     const uint32_t* wp = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(base) & ~(uintptr_t)3);
@@ -206,6 +207,7 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
             int base = 0;
             if (lane == 0 && m) base = atomicAdd(&s_nr, __popc(m));
             base = __shfl_sync(0xffffffffu, base, 0);
+            VX_CHECK(!keep || base + __popc(m & ((1u << lane) - 1u)) < kSortCap);
             if (keep) skey[base + __popc(m & ((1u << lane) - 1u))] = (uint32_t)i;
         }
         __syncthreads();
@@ -295,6 +297,7 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
 #pragma unroll
         for (int t = 0; t < kSortCap / kThreads; ++t)
             if (mypos[t] >= 0) {
+                VX_CHECK(mypos[t] < kSortCap);
                 skey[mypos[t]] = mykey[t];
                 sresp[mypos[t]] = myresp[t];
             }

@@ -12,11 +12,29 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include <string>
 #include <vector>
 
 #include "../../include/vxorb.h"
+
+// Checked build (make EXTRA=-DVXORB_CHECKED=1, scratch/ab.sh): every shared-memory / list / plane index the
+// kernels compute is range-checked on the device and a violation traps, which fails the launch loudly.  This
+// is the repo's own substitute for compute-sanitizer memcheck (closed on this GPU pool); the production build
+// compiles the checks away.
+#if defined(VXORB_CHECKED) && VXORB_CHECKED
+#define VX_CHECK(cond)                                                                                     \
+    do {                                                                                                   \
+        if (!(cond)) {                                                                                     \
+            printf("VX_CHECK failed: %s  (%s:%d, block %d,%d thread %d)\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, \
+                   (int)blockIdx.y, (int)threadIdx.x);                                                     \
+            __trap();                                                                                      \
+        }                                                                                                  \
+    } while (0)
+#else
+#define VX_CHECK(cond) ((void)0)
+#endif
 
 namespace vxorb {
 
