@@ -340,24 +340,26 @@ def bench_per_call(vx, peak):
     return out
 
 
-def bench_config(vx, peak, popc_peak, w, h, n_kp, batch, radius, steps, label, bytes_model):
-    """Resident-batch extraction + temporal matching throughput of another BASELINE geometry."""
-    from visionx_slam_b200.synth import synth_sequence
-    seq = synth_sequence(w, h, batch, seed=404)
+def bench_config(vx, peak, popc_peak, w, h, n_kp, batch, radius, steps, label, bytes_model, stereo_box=None):
+    """Resident-batch extraction + matching throughput of another BASELINE geometry (temporal frame-to-frame matching,
+    or, with stereo_box, chunks of (left, right) pairs: left -> right box-masked + left_(k-1) -> left_k windowed)."""
+    from visionx_slam_b200.synth import synth_sequence, synth_stereo_sequence
+    seq = synth_stereo_sequence(w, h, batch // 2, seed=404) if stereo_box is not None else synth_sequence(w, h, batch, seed=404)
     out = {"config": label, "batch": batch}
     with vx.VxOrb(n_features=n_kp, max_width=w, max_height=h, max_batch=batch, max_train=max(16384, 2 * n_kp)) as hc:
+        run = (lambda: hc.resident_run_stereo(stereo_box, radius)) if stereo_box is not None else (lambda: hc.resident_run(radius))
         hc.resident_upload(seq)
         for _ in range(3):
-            hc.resident_run(radius)
+            run()
         hc.sync()
         hc.timer_begin()
         for _ in range(steps):
-            hc.resident_run(radius)
+            run()
         ms = hc.timer_end()
         out["frames_per_s_resident"] = batch * steps / (ms * 1e-3)
         hc.stage_times_reset(True)
         for _ in range(steps):
-            hc.resident_run(radius)
+            run()
         st = hc.stage_times()
         hc.stage_times_reset(False)
         res = hc.resident_fetch()
@@ -368,28 +370,41 @@ def bench_config(vx, peak, popc_peak, w, h, n_kp, batch, radius, steps, label, b
         out["algorithmic_bytes_per_frame"] = bytes_model
         out["extraction_frac_of_hbm_peak"] = bytes_model * batch / (ext_ms * 1e-3) / 1e9 / peak
         out["stages_ms_per_batch"] = {s: st[s][0] / steps for s in st}
-        out["match"] = {"radius": radius, "ms_per_pair": st["match"][0] / steps / batch}
+        out["match"] = {"radius": radius, "ms_per_batch": st["match"][0] / steps}
     return out, seq, res
 
 
 def bench_c3(vx, peak, popc_peak):
-    """BASELINE config 3: 1241x376, 2000 kp — batched extraction with temporal windowed matching (resident), and
-    the left->right box-masked stereo match of one pair through the host-buffer call."""
-    from visionx_slam_b200.synth import synth_stereo_pair
-    out, _, _ = bench_config(vx, peak, popc_peak, 1241, 376, 2000, 32, 64.0, 5,
-                             "config3: KITTI-shape 1241x376, 2000 kp/frame, temporal windowed (r=64) matching, batch 32 resident",
-                             7853539)
-    left, right = synth_stereo_pair(1241, 376, 31)
+    """BASELINE config 3: KITTI-shape 1241x376 stereo pairs, 2000 kp per view, through the stereo chunk path
+    (vxorb_resident_run_stereo = the kernels of vxorb_track_submit_stereo): every view extracted, left -> right
+    through the box mask 0 <= xl - xr <= 128, |yl - yr| <= 2, and left_(k-1) -> left_k through a 64 px window."""
+    box = np.float32([0.0, 128.0, -2.0, 2.0])
+    out, seq, res = bench_config(vx, peak, popc_peak, 1241, 376, 2000, 32, 64.0, 5,
+                                 "config3: KITTI-shape 1241x376 stereo pairs, 2000 kp/view, left-right box-masked + temporal "
+                                 "windowed (r=64) matching, 16 pairs (32 frames) per resident chunk", 7853539, stereo_box=box)
+    pairs = 16
+    out["stereo_pairs_per_s_resident"] = out["frames_per_s_resident"] / 2
+    out["matches_per_pair"] = {"left_right": float(np.mean([len(res[k][2]) for k in range(pairs)])),
+                               "temporal": float(np.mean([len(res[pairs + k][2]) for k in range(1, pairs)]))}
+    # parity of the benchmarked chunk: pair 3's two views and both of its match legs against the oracle
+    import oracle
+    ext = {f: oracle.orb_extract(seq[f], 2000) for f in (4, 6, 7)}
+    xy = {f: np.stack([ext[f][0]["x"], ext[f][0]["y"]], 1) for f in ext}
+    ok = all(np.array_equal(res[f][0], ext[f][0]) and np.array_equal(res[f][1], ext[f][1]) for f in ext)
+    ok = ok and np.array_equal(res[3][2], oracle.match_boxed(ext[6][1], ext[7][1], xy[6], xy[7], box))
+    ok = ok and np.array_equal(res[pairs + 3][2], oracle.match(ext[4][1], ext[6][1], 0.8, xy[4], xy[6], 64.0))
+    if not ok:
+        raise SystemExit("bench.py: PARITY FAILURE in the config-3 stereo chunk")
+    out["parity_checked"] = True
+    # one pair through the host-buffer calls (what a per-frame caller pays)
+    left, right = seq[6], seq[7]
     with vx.VxOrb(n_features=2000, max_width=1241, max_height=376, max_batch=2, max_train=4096) as hs:
         (kl, dl), (kr, dr) = hs.extract_batch([left, right])
         qxy, txy = np.stack([kl["x"], kl["y"]], 1), np.stack([kr["x"], kr["y"]], 1)
-        box = np.float32([0.0, 128.0, -2.0, 2.0])
-        m = hs.match_boxed(dl, dr, qxy, txy, box)
         ms, ms_min = median_ms(lambda: hs.match_boxed(dl, dr, qxy, txy, box), 100)
         pair_ms, _ = median_ms(lambda: hs.extract_batch([left, right]), 50)
-        out["stereo"] = {"left_right_boxed_match_ms": ms, "left_right_boxed_match_ms_min": ms_min,
-                         "matches": int(len(m)), "extract_stereo_pair_ms": pair_ms,
-                         "box": "0 <= xl - xr <= 128, |yl - yr| <= 2", "path": "host buffers, synchronous calls"}
+        out["per_call"] = {"left_right_boxed_match_ms": ms, "left_right_boxed_match_ms_min": ms_min,
+                           "extract_stereo_pair_ms": pair_ms, "path": "host buffers, synchronous calls"}
     return out
 
 

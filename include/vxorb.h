@@ -249,6 +249,16 @@ int vxorb_track_submit_bgr(vxorb_handle* h, const uint8_t* bgr_frames, int batch
                            vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_kp_out, int match_cap,
                            vxorb_match_t* match_out, int* n_match_out, vxorb_frame_info* info_out,
                            float* pts_out, int* slot_out);
+/* Rectified stereo sequences (BASELINE config 3).  `frames` holds `pairs` (left, right) pairs: frame 2k = left_k,
+ * frame 2k + 1 = right_k (2 * pairs <= max_batch).  Every frame is extracted.  Match rows [0, pairs): left_k ->
+ * right_k through the box mask of vxorb_match_boxed ({0, max_disparity, -dy_tol, dy_tol} for a rectified pair);
+ * rows [pairs, 2 * pairs): the temporal leg left_(k-1) -> left_k through the square window `radius` (brute force
+ * when radius <= 0), left_(-1) being the last left frame of the previous chunk (none after vxorb_track_reset).
+ * kp_out / desc_out / n_kp_out have 2 * pairs frame rows, match_out / n_match_out 2 * pairs pair rows. */
+int vxorb_track_submit_stereo(vxorb_handle* h, const uint8_t* frames, int pairs, int width, int height,
+                              size_t stride, size_t frame_stride, const float* box, float radius, int kp_cap,
+                              vxorb_keypoint* kp_out, uint8_t* desc_out, int* n_kp_out, int match_cap,
+                              vxorb_match_t* match_out, int* n_match_out, int* slot_out);
 int vxorb_track_wait(vxorb_handle* h, int slot);
 int vxorb_keypoint_capacity(const vxorb_handle* h);
 
@@ -265,6 +275,8 @@ void vxorb_host_free(void* p);
 int vxorb_resident_upload(vxorb_handle* h, const uint8_t* frames, int batch, int width, int height,
                           size_t stride, size_t frame_stride);
 int vxorb_resident_run(vxorb_handle* h, float radius);
+/* The resident frames as (left, right) pairs with the matching of vxorb_track_submit_stereo. */
+int vxorb_resident_run_stereo(vxorb_handle* h, const float* box, float radius);
 int vxorb_resident_fetch(vxorb_handle* h, int kp_cap, vxorb_keypoint* kp_out, uint8_t* desc_out,
                          int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out);
 

@@ -14,7 +14,7 @@ import pytest
 import oracle
 import visionx_slam_b200 as vx
 from conftest import assert_kp_equal, load_golden, matches_as_rows
-from visionx_slam_b200.synth import sha256, synth_scene, synth_sequence
+from visionx_slam_b200.synth import sha256, synth_scene, synth_sequence, synth_stereo_sequence
 
 pytestmark = pytest.mark.gpu
 
@@ -736,6 +736,46 @@ def test_stereo_pair_boxed_golden():
         # temporal leg of the same config: square window against the oracle
         mt = hx.match(dl, dr, q_xy=qxy, t_xy=txy, radius=64.0)
         assert np.array_equal(matches_as_rows(mt), matches_as_rows(oracle.match(dl, dr, 0.8, qxy, txy, 64.0)))
+
+
+@pytest.mark.parametrize("size,n_features,pairs,radius", [((1241, 376), 2000, 4, 48.0), ((640, 480), 1000, 5, 0.0)])
+def test_track_stereo_vs_oracle(size, n_features, pairs, radius):
+    """BASELINE config 3 through the streaming path: chunks of (left, right) pairs, left -> right through the box
+    mask and left_(k-1) -> left_k through the window (or brute force), the last left frame carried across chunks;
+    the resident form of the same chunk gives the same bytes."""
+    w, hh = size
+    frames = synth_stereo_sequence(w, hh, pairs, seed=9)
+    box = np.float32([0.0, 64.0, -2.0, 2.0])
+    ext = _oracle_extract_many(frames, n_features)
+    xy = [np.stack([k["x"], k["y"]], 1) for k, _ in ext]
+    with vx.VxOrb(n_features=n_features, max_width=w, max_height=hh, max_batch=2 * pairs, max_train=4096) as hx:
+        first = 2 * (pairs // 2)
+        f1, m1 = hx.track_stereo(frames[:first], box, radius)           # two chunks: the carry crosses the boundary
+        f2, m2 = hx.track_stereo(frames[first:], box, radius)
+        got_f, got_m = f1 + f2, m1 + m2
+        for i, ((kp, desc), (okp, odesc)) in enumerate(zip(got_f, ext)):
+            assert_kp_equal(kp, okp)
+            assert np.array_equal(desc, odesc), f"frame {i}"
+        for k, (ms, mt) in enumerate(got_m):
+            l, r = 2 * k, 2 * k + 1
+            om = oracle.match_boxed(ext[l][1], ext[r][1], xy[l], xy[r], box)
+            assert np.array_equal(matches_as_rows(ms), matches_as_rows(om)), f"stereo pair {k}"
+            if k == 0:
+                assert len(mt) == 0
+            else:
+                p = 2 * (k - 1)
+                ot = oracle.match(ext[p][1], ext[l][1], 0.8, xy[p] if radius > 0 else None, xy[l] if radius > 0 else None, radius)
+                assert np.array_equal(matches_as_rows(mt), matches_as_rows(ot)), f"temporal pair {k}"
+        assert len(got_m[1][0]) > 100 and len(got_m[1][1]) > 100
+        # resident form of the whole sequence as one chunk
+        hx.track_reset()
+        hx.resident_upload(frames)
+        hx.resident_run_stereo(box, radius)
+        res = hx.resident_fetch()
+        for k in range(pairs):
+            assert np.array_equal(res[k][2], got_m[k][0]), f"resident stereo pair {k}"
+            if k > 0:
+                assert np.array_equal(res[pairs + k][2], got_m[k][1]), f"resident temporal pair {k}"
 
 
 @pytest.mark.parametrize("box", [(0.0, 128.0, -2.0, 2.0), (-5.5, 0.25, -100.0, 3.0), (10.0, 10.0, 0.0, 0.0)])

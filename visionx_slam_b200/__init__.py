@@ -81,12 +81,14 @@ _SYMBOLS = [
     ("vxorb_track_submit", _i, [_vp, _vp, _i, _i, _i, _sz, _sz, _f, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
     ("vxorb_track_submit_info", _i, [_vp, _vp, _i, _i, _i, _sz, _sz, _f, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
     ("vxorb_track_submit_bgr", _i, [_vp, _vp, _i, _i, _i, _sz, _sz, _f, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
+    ("vxorb_track_submit_stereo", _i, [_vp, _vp, _i, _i, _i, _sz, _sz, _vp, _f, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
     ("vxorb_track_wait", _i, [_vp, _i]),
     ("vxorb_keypoint_capacity", _i, [_vp]),
     ("vxorb_host_alloc", _vp, [_sz]),
     ("vxorb_host_free", None, [_vp]),
     ("vxorb_resident_upload", _i, [_vp, _vp, _i, _i, _i, _sz, _sz]),
     ("vxorb_resident_run", _i, [_vp, _f]),
+    ("vxorb_resident_run_stereo", _i, [_vp, _vp, _f]),
     ("vxorb_resident_fetch", _i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     ("vxorb_sync", _i, [_vp]),
     ("vxorb_timer_begin", _i, [_vp]),
@@ -456,6 +458,30 @@ class VxOrb:
         slot = self.track_submit(frames, radius, kp, desc, nk, mt, nm)
         self.track_wait(slot)
         return [(kp[i, :nk[i]].copy(), desc[i, :nk[i]].copy(), mt[i, :nm[i]].copy()) for i in range(b)]
+
+    def track_stereo(self, frames, box, radius):
+        """One chunk of (left, right) pairs: frames (2P,H,W).  Returns per frame (kp, desc) and per pair
+        (stereo matches left_k -> right_k, temporal matches left_(k-1) -> left_k)."""
+        frames = np.ascontiguousarray(frames, dtype=np.uint8)
+        b, h, w = frames.shape
+        box = np.ascontiguousarray(box, dtype=np.float32)
+        kp = np.zeros((b, self.kp_cap), KEYPOINT_DTYPE)
+        desc = np.zeros((b, self.kp_cap, 32), np.uint8)
+        nk = np.zeros(b, np.int32)
+        mt = np.zeros((b, self.kp_cap), MATCH_DTYPE)
+        nm = np.zeros(b, np.int32)
+        slot = C.c_int(-1)
+        self._check(self._lib.vxorb_track_submit_stereo(self._h, _ptr(frames), b // 2, w, h, frames.strides[1], frames.strides[0],
+                                                        _ptr(box), radius, self.kp_cap, _ptr(kp), _ptr(desc), _ptr(nk),
+                                                        self.kp_cap, _ptr(mt), _ptr(nm), C.byref(slot)))
+        self.track_wait(slot.value)
+        p = b // 2
+        return ([(kp[i, :nk[i]].copy(), desc[i, :nk[i]].copy()) for i in range(b)],
+                [(mt[k, :nm[k]].copy(), mt[p + k, :nm[p + k]].copy()) for k in range(p)])
+
+    def resident_run_stereo(self, box, radius):
+        box = np.ascontiguousarray(box, dtype=np.float32)
+        self._check(self._lib.vxorb_resident_run_stereo(self._h, _ptr(box), radius))
 
     def resident_upload(self, frames):
         frames = np.ascontiguousarray(frames, dtype=np.uint8)

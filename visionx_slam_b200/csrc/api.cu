@@ -510,6 +510,48 @@ int enqueue_track_match(vxorb_handle* h, Workspace& ws, int batch, float radius)
     return VXORB_OK;
 }
 
+// Stereo chunk (BASELINE config 3): frame slots 1..2P hold (left_0, right_0, left_1, right_1, ...).  Queues, into
+// knn / match / match_n rows [0, P): left_k -> right_k through the box mask, and into rows [P, 2P): the temporal
+// leg left_{k-1} -> left_k through the square window (brute force when radius <= 0); left_{-1} is the carry in
+// slot 0.
+int enqueue_stereo_match(vxorb_handle* h, Workspace& ws, int pairs, const float* box, float radius) {
+    cudaStream_t s = ws.stream;
+    DeviceBuffers& d = ws.db;
+    const size_t cap = (size_t)h->kp_cap;
+    StageScope sc(h, s, VXORB_STAGE_MATCH);
+    int n = 0;
+    auto leg = [&](int q_slot, int t_slot, int slot_stride, int n_pairs, int out_row, bool boxed) {
+        if (n_pairs <= 0) return;
+        MatchArgs a;
+        a.q_desc = d.desc + cap * 32 * q_slot;
+        a.t_desc = d.desc + cap * 32 * t_slot;
+        a.q_xy = d.xy + cap * 2 * q_slot;
+        a.t_xy = d.xy + cap * 2 * t_slot;
+        a.q_n = d.kp_n + q_slot;
+        a.t_n = d.kp_n + t_slot;
+        a.n_stride = slot_stride;
+        a.q_pair_stride = a.t_pair_stride = (long long)cap * slot_stride;
+        a.max_q = a.max_t = h->kp_cap;
+        a.pairs = n_pairs;
+        a.radius = boxed ? 0.f : radius;
+        if (boxed) {
+            a.boxed = 1;
+            for (int i = 0; i < 4; ++i) a.box[i] = box[i];
+        }
+        a.knn = d.knn + cap * out_row;
+        a.knn_stride = h->kp_cap;
+        n += launch_knn2(a, s);
+        n += launch_match_compact(a.knn, nullptr, h->kp_cap, 0, a.q_n, n_pairs, h->p.nn_ratio, 0, d.match + cap * out_row,
+                                  h->kp_cap, d.match_n + out_row, s, slot_stride);
+    };
+    leg(1, 2, 2, pairs, 0, true);              // left_k -> right_k
+    leg(0, 1, 1, 1, pairs, false);             // carry -> left_0
+    leg(1, 3, 2, pairs - 1, pairs + 1, false); // left_{k-1} -> left_k, k >= 1
+    sc.end(n);
+    CK(cudaGetLastError());
+    return VXORB_OK;
+}
+
 // Queues the caller-side per-frame quantities (image statistics, grid coverage, matched positions,
 // parallax) for frames 1..batch of the workspace; needs match / match_n of those pairs to be final.
 int enqueue_frame_info(vxorb_handle* h, Workspace& ws, int batch, bool want_pts) {
@@ -1250,14 +1292,15 @@ static int enqueue_carry_out(vxorb_handle* h, Workspace& ws, int batch) {
 // Extraction, carry and pair matching of one chunk whose level 0 is already in ws.  The carry leaves
 // as soon as the descriptors exist (the next chunk, on another slot, only needs this chunk's last
 // frame), so `done` is recorded before this chunk's own matching starts.
-static int enqueue_chunk(vxorb_handle* h, Workspace& ws, int batch, float radius) {
+static int enqueue_chunk(vxorb_handle* h, Workspace& ws, int batch, float radius, const float* stereo_box = nullptr) {
     int rc = enqueue_extract(h, ws, batch);
     if (rc) return rc;
     rc = enqueue_carry_in(h, ws);
     if (rc) return rc;
-    rc = enqueue_carry_out(h, ws, batch);
+    rc = enqueue_carry_out(h, ws, stereo_box ? batch - 1 : batch);  // stereo: the last LEFT frame carries
     if (rc) return rc;
     CK(cudaEventRecord(ws.done, ws.stream));  // descriptors and the carry of this chunk are final
+    if (stereo_box) return enqueue_stereo_match(h, ws, batch / 2, stereo_box, radius);
     return enqueue_track_match(h, ws, batch, radius);
 }
 
@@ -1271,10 +1314,13 @@ int vxorb_track_submit(vxorb_handle* h, const uint8_t* frames, int batch, int wi
 static int track_submit_common(vxorb_handle* h, const uint8_t* frames, int channels, int batch, int width, int height,
                                size_t stride, size_t frame_stride, float radius, int kp_cap, vxorb_keypoint* kp_out,
                                uint8_t* desc_out, int* n_kp_out, int match_cap, vxorb_match_t* match_out,
-                               int* n_match_out, vxorb_frame_info* info_out, float* pts_out, int* slot_out) {
+                               int* n_match_out, vxorb_frame_info* info_out, float* pts_out, int* slot_out,
+                               const float* stereo_box = nullptr) {
     if (!h) return VXORB_E_INVALID;
     if (!frames || !slot_out) return fail(h, VXORB_E_INVALID, "null argument");
     if (channels != 1 && channels != 3) return fail(h, VXORB_E_INVALID, "channels must be 1 (gray) or 3 (BGR)");
+    if (stereo_box && (batch % 2 != 0 || !(stereo_box[0] <= stereo_box[1]) || !(stereo_box[2] <= stereo_box[3])))
+        return fail(h, VXORB_E_INVALID, "stereo chunks hold (left, right) pairs and need box = {dx_min <= dx_max, dy_min <= dy_max}");
     if (batch < 1 || batch > h->p.max_batch) return fail(h, VXORB_E_INVALID, "batch outside 1..max_batch");
     if (width < 1 || height < 1 || stride < (size_t)width * channels) return fail(h, VXORB_E_INVALID, "stride smaller than a row");
     if ((kp_out || desc_out) && kp_cap != h->kp_cap)
@@ -1302,7 +1348,7 @@ static int track_submit_common(vxorb_handle* h, const uint8_t* frames, int chann
         int rc2 = channels == 3 ? upload_bgr_frames(h, ws, frames, batch, width, height, stride, frame_stride)
                                 : upload_frames(h, ws, frames, batch, width, height, stride, frame_stride);
         if (rc2) return rc2;
-        rc2 = enqueue_chunk(h, ws, batch, radius);
+        rc2 = enqueue_chunk(h, ws, batch, radius, stereo_box);
         if (rc2) return rc2;
         if (info_out || pts_out) {
             rc2 = enqueue_frame_info(h, ws, batch, pts_out != nullptr);
@@ -1356,6 +1402,16 @@ int vxorb_track_submit_bgr(vxorb_handle* h, const uint8_t* bgr_frames, int batch
                            vxorb_frame_info* info_out, float* pts_out, int* slot_out) {
     return track_submit_common(h, bgr_frames, 3, batch, width, height, stride, frame_stride, radius, kp_cap, kp_out,
                                desc_out, n_kp_out, match_cap, match_out, n_match_out, info_out, pts_out, slot_out);
+}
+
+int vxorb_track_submit_stereo(vxorb_handle* h, const uint8_t* frames, int pairs, int width, int height, size_t stride,
+                              size_t frame_stride, const float* box, float radius, int kp_cap, vxorb_keypoint* kp_out,
+                              uint8_t* desc_out, int* n_kp_out, int match_cap, vxorb_match_t* match_out, int* n_match_out,
+                              int* slot_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!box || pairs < 1) return fail(h, VXORB_E_INVALID, "stereo submit needs pairs >= 1 and a box");
+    return track_submit_common(h, frames, 1, 2 * pairs, width, height, stride, frame_stride, radius, kp_cap, kp_out, desc_out,
+                               n_kp_out, match_cap, match_out, n_match_out, nullptr, nullptr, slot_out, box);
 }
 
 int vxorb_track_wait(vxorb_handle* h, int slot) {
@@ -1417,7 +1473,18 @@ int vxorb_resident_upload(vxorb_handle* h, const uint8_t* frames, int batch, int
     return VXORB_OK;
 }
 
-int vxorb_resident_run(vxorb_handle* h, float radius) {
+static int resident_run_common(vxorb_handle* h, float radius, const float* stereo_box);
+
+int vxorb_resident_run(vxorb_handle* h, float radius) { return resident_run_common(h, radius, nullptr); }
+
+int vxorb_resident_run_stereo(vxorb_handle* h, const float* box, float radius) {
+    if (!h) return VXORB_E_INVALID;
+    if (!box || !(box[0] <= box[1]) || !(box[2] <= box[3]) || h->res_batch % 2 != 0)
+        return fail(h, VXORB_E_INVALID, "stereo pass needs an even number of resident frames and box = {dx_min <= dx_max, dy_min <= dy_max}");
+    return resident_run_common(h, radius, box);
+}
+
+static int resident_run_common(vxorb_handle* h, float radius, const float* stereo_box) {
     if (!h) return VXORB_E_INVALID;
     if (h->res_batch < 1 || h->geo_w == 0) return fail(h, VXORB_E_INVALID, "no resident frames; call vxorb_resident_upload");
     CK(cudaSetDevice(h->p.device_id));
@@ -1425,7 +1492,7 @@ int vxorb_resident_run(vxorb_handle* h, float radius) {
     const int slot = h->stage_enabled ? 0 : h->res_next;
     Workspace& ws = h->ws[slot];
     if (ws.in_flight) return fail(h, VXORB_E_INVALID, "slot busy with a track submit");
-    const int rc = enqueue_chunk(h, ws, h->res_batch, radius);
+    const int rc = enqueue_chunk(h, ws, h->res_batch, radius, stereo_box);
     if (rc) return rc;
     h->last_slot = slot;
     h->res_last = slot;

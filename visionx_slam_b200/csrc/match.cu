@@ -77,7 +77,7 @@ knn2_kernel(const MatchArgs a) {
     __shared__ float2 txy[kTrainTile];
 
     const int pair = blockIdx.y;
-    const int nq = a.q_n[pair], nt = a.t_n[pair];
+    const int nq = a.q_n[pair * a.n_stride], nt = a.t_n[pair * a.n_stride];
     const int q_first = blockIdx.x * (kQPerBlock * QPT);
     if (q_first >= nq) return;  // whole CTA idle
     const bool windowed = (a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr;
@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(256)
 knn2_merge_kernel(const MatchArgs a) {
     const int pair = blockIdx.y;
     const int qi = blockIdx.x * 256 + threadIdx.x;
-    if (qi >= a.q_n[pair]) return;
+    if (qi >= a.q_n[pair * a.n_stride]) return;
     uint32_t k0 = kNoKey, k1 = kNoKey;
     for (int sp = 0; sp < a.splits; ++sp) {
         const uint2 p = a.part[((size_t)pair * a.splits + sp) * a.max_q + qi];
@@ -274,7 +274,7 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
     __shared__ int warp_tot[kWinThreads / 32];
 
     const int pair = blockIdx.x;
-    const int nq = min(a.q_n[pair], max_q), nt = min(a.t_n[pair], max_t);
+    const int nq = min(a.q_n[pair * a.n_stride], max_q), nt = min(a.t_n[pair * a.n_stride], max_t);
     if (nq <= 0) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint8_t* qbase = a.q_desc + (size_t)pair * a.q_pair_stride * 32;
@@ -436,12 +436,12 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
 // the reference's loop over knn_matches (orb_matcher.cpp:27-36) produces them.
 __global__ void __launch_bounds__(256)
 match_compact_kernel(const vxorb_knn2_t* __restrict__ knn, const vxorb_knn2_t* __restrict__ back, int knn_stride,
-                     int back_stride, const int* __restrict__ q_n, float nn_ratio, int mode,
+                     int back_stride, const int* __restrict__ q_n, int n_stride, float nn_ratio, int mode,
                      vxorb_match_t* __restrict__ out, int out_stride, int* __restrict__ out_n) {
     __shared__ int warp_sum[8];
     __shared__ int s_base, s_min;
     const int pair = blockIdx.x;
-    const int nq = q_n[pair];
+    const int nq = q_n[pair * n_stride];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const vxorb_knn2_t* kp = knn + (size_t)pair * knn_stride;
     const vxorb_knn2_t* bp = back ? back + (size_t)pair * back_stride : nullptr;
@@ -580,9 +580,9 @@ int launch_knn2(const MatchArgs& a, cudaStream_t s) {
 
 int launch_match_compact(const vxorb_knn2_t* knn, const vxorb_knn2_t* back, int knn_stride, int back_stride,
                          const int* q_n, int pairs, float nn_ratio, int mode, vxorb_match_t* out, int out_stride,
-                         int* out_n, cudaStream_t s) {
+                         int* out_n, cudaStream_t s, int n_stride) {
     if (pairs <= 0) return 0;
-    match_compact_kernel<<<pairs, 256, 0, s>>>(knn, back, knn_stride, back_stride, q_n, nn_ratio, mode, out,
+    match_compact_kernel<<<pairs, 256, 0, s>>>(knn, back, knn_stride, back_stride, q_n, n_stride, nn_ratio, mode, out,
                                                out_stride, out_n);
     return 1;
 }

@@ -150,7 +150,8 @@ int launch_describe(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, cud
 struct MatchArgs {
     const uint8_t* q_desc; const uint8_t* t_desc;   // [pair][stride][32]
     const float* q_xy; const float* t_xy;           // [pair][stride][2] or nullptr
-    const int* q_n; const int* t_n;                 // [pair] row counts (device)
+    const int* q_n; const int* t_n;                 // row counts (device): pair p reads q_n[p * n_stride], t_n[p * n_stride]
+    int n_stride = 1;
     long long q_pair_stride, t_pair_stride;         // rows between consecutive pairs
     int max_q;                                      // upper bound of q_n (grid sizing)
     int max_t = 0;                                  // upper bound of t_n (shared-memory sizing of the windowed path)
@@ -172,7 +173,7 @@ int launch_knn2(const MatchArgs& a, cudaStream_t s);
 // mode 0: ratio test; mode 1: ratio test + caller's post-filter; mode 2: cross-check with `back`
 int launch_match_compact(const vxorb_knn2_t* knn, const vxorb_knn2_t* back, int knn_stride, int back_stride,
                          const int* q_n, int pairs, float nn_ratio, int mode, vxorb_match_t* out,
-                         int out_stride, int* out_n, cudaStream_t s);
+                         int out_stride, int* out_n, cudaStream_t s, int n_stride = 1);
 // frame_info.cu: image sums over level 0, grid coverage, matched positions and parallax (2 launches)
 int launch_frame_info(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, unsigned long long* sums,
                       vxorb_frame_info* info, float4* pts, int grid_cols, int grid_rows, cudaStream_t s);

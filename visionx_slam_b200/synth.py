@@ -79,5 +79,20 @@ def synth_stereo_pair(w=1241, h=376, seed=31):
     return left, right
 
 
+def synth_stereo_sequence(w, h, pairs, seed, max_disparity=48):
+    """(left_0, right_0, left_1, right_1, ...): the left views are a synth_sequence, every right view is its left
+    view shifted by a row-dependent disparity (8..max_disparity px) plus +-2 grey levels of noise."""
+    lefts = synth_sequence(w, h, pairs, seed=seed)
+    rng = np.random.default_rng(seed)
+    out = np.empty((2 * pairs, h, w), np.uint8)
+    for k in range(pairs):
+        right = np.empty_like(lefts[k])
+        for y in range(h):
+            right[y] = np.roll(lefts[k][y], -(8 + (y * (max_disparity - 8)) // h))
+        out[2 * k] = lefts[k]
+        out[2 * k + 1] = np.clip(right.astype(np.int16) + rng.integers(-2, 3, right.shape), 0, 255).astype(np.uint8)
+    return out
+
+
 def sha256(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
