@@ -379,10 +379,11 @@ def bench_c3(vx, peak, popc_peak):
     (vxorb_resident_run_stereo = the kernels of vxorb_track_submit_stereo): every view extracted, left -> right
     through the box mask 0 <= xl - xr <= 128, |yl - yr| <= 2, and left_(k-1) -> left_k through a 64 px window."""
     box = np.float32([0.0, 128.0, -2.0, 2.0])
-    out, seq, res = bench_config(vx, peak, popc_peak, 1241, 376, 2000, 32, 64.0, 5,
+    pairs = 48
+    out, seq, res = bench_config(vx, peak, popc_peak, 1241, 376, 2000, 2 * pairs, 64.0, 5,
                                  "config3: KITTI-shape 1241x376 stereo pairs, 2000 kp/view, left-right box-masked + temporal "
-                                 "windowed (r=64) matching, 16 pairs (32 frames) per resident chunk", 7853539, stereo_box=box)
-    pairs = 16
+                                 f"windowed (r=64) matching, {pairs} pairs ({2 * pairs} frames) per resident chunk", 7853539,
+                                 stereo_box=box)
     out["stereo_pairs_per_s_resident"] = out["frames_per_s_resident"] / 2
     out["matches_per_pair"] = {"left_right": float(np.mean([len(res[k][2]) for k in range(pairs)])),
                                "temporal": float(np.mean([len(res[pairs + k][2]) for k in range(1, pairs)]))}

@@ -11,6 +11,8 @@
 // vectors; per pair: 8 XOR + 8 POPC + 7 IADD, then the packed key (dist << 20 | idx) goes through a
 // 3-instruction min/max top-2 update.  Bound: integer/popcount issue rate, not HBM (64 KB of
 // descriptors per 1000x1000 pair).  compact kernel: one CTA per pair, ordered block scan.
+#include <algorithm>
+
 #include "vxorb_internal.h"
 
 namespace vxorb {
@@ -272,6 +274,7 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
     float* bounds = reinterpret_cast<float*>(cursor + kCells);                     // minx, miny, maxx, maxy
     uint16_t* qorder = reinterpret_cast<uint16_t*>(bounds + 16);                   // [max_q] query rows in cell order
     __shared__ int warp_tot[kWinThreads / 32];
+    __shared__ int s_rank_lo, s_rank_hi;
 
     const int pair = blockIdx.x;
     const int nq = min(a.q_n[pair * a.n_stride], max_q), nt = min(a.t_n[pair * a.n_stride], max_t);
@@ -280,7 +283,10 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
     const uint8_t* qbase = a.q_desc + (size_t)pair * a.q_pair_stride * 32;
     const uint8_t* tbase = a.t_desc + (size_t)pair * a.t_pair_stride * 32;
     const float2* txy_g = reinterpret_cast<const float2*>(a.t_xy + (size_t)pair * a.t_pair_stride * 2);
-    const float r = a.radius;
+    // the mask as a box on (query - train): the square window of radius r is {-r, r, -r, r} (|d| <= r <=> -r <= d <= r
+    // in float), a stereo / epipolar band is e.g. {0, max_disparity, -dy_tol, dy_tol}
+    const float bx0 = a.boxed ? a.box[0] : -a.radius, bx1 = a.boxed ? a.box[1] : a.radius;
+    const float by0 = a.boxed ? a.box[2] : -a.radius, by1 = a.boxed ? a.box[3] : a.radius;
 
     // ---- 1. bounding box of the train positions -> grid geometry ------------------------------
     {
@@ -313,9 +319,10 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
         __syncthreads();
     }
     const float orgx = bounds[0], orgy = bounds[1];
-    // cells at least r / 2 wide, and wide enough that kGridX x kGridY of them cover the bounding box
-    const float csx = fmaxf(r * kCellPerRadius, (bounds[2] - orgx) * (1.0f / kGridX) * 1.0001f);
-    const float csy = fmaxf(r * kCellPerRadius, (bounds[3] - orgy) * (1.0f / kGridY) * 1.0001f);
+    // cells at least a quarter of the box wide (= r / 2 for the square window), and wide enough that kGridX x kGridY
+    // of them cover the bounding box; never zero (a degenerate box over coincident points)
+    const float csx = fmaxf(fmaxf((bx1 - bx0) * (0.5f * kCellPerRadius), (bounds[2] - orgx) * (1.0f / kGridX) * 1.0001f), 1.0e-3f);
+    const float csy = fmaxf(fmaxf((by1 - by0) * (0.5f * kCellPerRadius), (bounds[3] - orgy) * (1.0f / kGridY) * 1.0001f), 1.0e-3f);
     const float invx = 1.0f / csx, invy = 1.0f / csy;
 
     // ---- 2. counting sort of the train rows by cell --------------------------------------------
@@ -384,9 +391,26 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
     }
     __syncthreads();
     scan_cells();
+    // gridDim.y CTAs share the queries of a pair (each bins the train rows itself: that part is a fraction of a
+    // CTA's time, and a pair with many more than kWinThreads queries would otherwise need several sequential rounds).
+    // The order of the queries INSIDE a cell depends on the order of the atomics and differs from CTA to CTA, so the
+    // split is made on whole cells: CTA s owns the cells whose first rank lies in [s, s + 1) * per_split — a range
+    // of ranks [rank_lo, rank_hi) that every CTA computes identically.
+    const int per_split = (nq + (int)gridDim.y - 1) / (int)gridDim.y;
+    const int own_lo = (int)blockIdx.y * per_split, own_hi = own_lo + per_split;
+    const bool split = gridDim.y > 1;
+    if (tid == 0) {
+        s_rank_lo = split ? nq : 0;
+        s_rank_hi = nq;
+    }
+    __syncthreads();
     for (int i = tid; i < nq; i += kWinThreads) {
         const float2 p = __ldg(qxy_g + i);
-        qorder[atomicAdd(&cursor[cell_of(p.y, orgy, invy, kGridY) * kGridX + cell_of(p.x, orgx, invx, kGridX)], 1)] = (uint16_t)i;
+        const int cell = cell_of(p.y, orgy, invy, kGridY) * kGridX + cell_of(p.x, orgx, invx, kGridX);
+        const int first = cell_start[cell];  // first rank of the cell (the scan of the query histogram)
+        if (split && first >= own_lo && first < s_rank_lo) atomicMin(&s_rank_lo, first);
+        if (split && first >= own_hi && first < s_rank_hi) atomicMin(&s_rank_hi, first);
+        qorder[atomicAdd(&cursor[cell], 1)] = (uint16_t)i;
     }
     __syncthreads();
 #pragma unroll
@@ -394,7 +418,8 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
     if (tid == 0) cell_start[kCells] = my_start[kCellsPerThread];
     __syncthreads();
 
-    for (int rank = tid; rank < nq; rank += kWinThreads) {
+    const int rank_end = s_rank_hi;
+    for (int rank = s_rank_lo + tid; rank < rank_end; rank += kWinThreads) {
         const int qi = qorder[rank];
         uint32_t q[8];
         {
@@ -405,17 +430,20 @@ knn2_window_kernel(const MatchArgs a, int max_t, int max_q) {
         }
         const float2 qp = __ldg(qxy_g + qi);
         const float qx = qp.x, qy = qp.y;
-        // widened radius for the cell range only (covers the rounding of qx - tx and of qx +- r)
-        const float rw = r + r * 1.0e-4f + fmaxf(fabsf(qx), fabsf(qy)) * 1.0e-6f;
-        const int cx0 = cell_of(qx - rw, orgx, invx, kGridX), cx1 = cell_of(qx + rw, orgx, invx, kGridX);
-        const int cy0 = cell_of(qy - rw, orgy, invy, kGridY), cy1 = cell_of(qy + rw, orgy, invy, kGridY);
+        // train rows that can pass have tx in [qx - bx1, qx - bx0] (ty alike); the cell range is taken from a slightly
+        // widened interval (covers the rounding of qx - tx and of qx - bound)
+        const float ew = (fmaxf(fabsf(bx0), fabsf(bx1)) + fmaxf(fabsf(by0), fabsf(by1))) * 1.0e-4f +
+                         fmaxf(fabsf(qx), fabsf(qy)) * 1.0e-6f + 1.0e-6f;
+        const int cx0 = cell_of(qx - bx1 - ew, orgx, invx, kGridX), cx1 = cell_of(qx - bx0 + ew, orgx, invx, kGridX);
+        const int cy0 = cell_of(qy - by1 - ew, orgy, invy, kGridY), cy1 = cell_of(qy - by0 + ew, orgy, invy, kGridY);
         uint32_t k0 = kNoKey, k1 = kNoKey;
         for (int cy = cy0; cy <= cy1; ++cy) {
             const int j0 = cell_start[cy * kGridX + cx0], j1 = cell_start[cy * kGridX + cx1 + 1];
             VX_CHECK(j0 >= 0 && j1 <= nt && cy >= 0 && cy < kGridY && cx0 >= 0 && cx1 < kGridX);
             for (int j = j0; j < j1; ++j) {
                 const float2 p = txy[j];
-                if (fabsf(__fsub_rn(qx, p.x)) <= r && fabsf(__fsub_rn(qy, p.y)) <= r) {
+                const float dx = __fsub_rn(qx, p.x), dy = __fsub_rn(qy, p.y);
+                if (dx >= bx0 && dx <= bx1 && dy >= by0 && dy <= by1) {
                     const uint4 lo = tdesc[2 * j], hi = tdesc[2 * j + 1];
                     const int d = __popc(q[0] ^ lo.x) + __popc(q[1] ^ lo.y) + __popc(q[2] ^ lo.z) + __popc(q[3] ^ lo.w) +
                                   __popc(q[4] ^ hi.x) + __popc(q[5] ^ hi.y) + __popc(q[6] ^ hi.z) + __popc(q[7] ^ hi.w);
@@ -537,10 +565,18 @@ cudaError_t init_match_kernels() {
 
 int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     if (a.pairs <= 0 || a.max_q <= 0) return 0;
-    const bool windowed = a.radius > 0.0f && !a.boxed && a.q_xy != nullptr && a.t_xy != nullptr;
-    if (windowed && a.max_t > 0 && a.max_q <= 65536 && window_smem_bytes(a.max_t, a.max_q) <= 224 * 1024) {
-        // cell-binned path: one CTA per pair, the whole train set sits in shared memory in cell order
-        knn2_window_kernel<<<a.pairs, kWinThreads, window_smem_bytes(a.max_t, a.max_q), s>>>(a, a.max_t, a.max_q);
+    const bool windowed = (a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr;
+    // a lone box-masked pair is served faster by the split brute-force launch below (32 CTAs instead of one)
+    const bool cells = windowed && !(a.boxed && a.pairs < 4);
+    if (cells && a.max_t > 0 && a.max_q <= 65536 && window_smem_bytes(a.max_t, a.max_q) <= 224 * 1024) {
+        // cell-binned path: the whole train set of a pair sits in shared memory in cell order; one CTA per pair and
+        // kWinThreads queries
+#ifndef VXORB_WIN_QSPLIT_MAX
+#define VXORB_WIN_QSPLIT_MAX 8
+#endif
+        const int qsplit = std::min(VXORB_WIN_QSPLIT_MAX, (a.max_q + 1535) / 1536);  // 1000 queries: one CTA is faster (0.049 vs 0.066 ms per 128 pairs); 2000: three CTAs 0.20 vs 0.35 ms per 96 pairs
+        dim3 grid(a.pairs, qsplit);
+        knn2_window_kernel<<<grid, kWinThreads, window_smem_bytes(a.max_t, a.max_q), s>>>(a, a.max_t, a.max_q);
         return 1;
     }
     // few pairs: split the train rows over gridDim.z so that the launch still covers the GPU (two CTAs of
