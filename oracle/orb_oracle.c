@@ -13,9 +13,10 @@
  * SURVEY.md Appendix A, stage by stage.
  *
  * Parity pin.  The reference holds no tests or golden vectors for this path ("parity unpinned"
- * by the reference itself).  The pin used instead is OpenCV itself: oracle/pin_cv2.py runs every
- * stage here against cv2 4.13.0 (the same OpenCV entry points the reference calls) and
- * tests/golden/ holds cv2-generated vectors that tests/test_oracle_golden.py replays.
+ * by the reference itself).  The pin used instead is OpenCV itself: tests/golden/make_golden.py
+ * (committed) runs cv2 4.13.0 — the same OpenCV entry points the reference calls, plus the per-stage
+ * primitives — and freezes the outputs as the .npz files under tests/golden/; tests/test_oracle_golden.py replays
+ * every one of them against the functions below, bit for bit.
  *
  * Build: gcc -O2 -ffp-contract=off (the float expressions below rely on un-fused rounding
  * except where fmaf is written out).
