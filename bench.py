@@ -9,7 +9,7 @@ rBRIEF, Hamming 2-NN + ratio test of every frame against its predecessor) over `
 chunks of `--batch` frames of a synthetic streaming sequence (default 8 x 128 = 1024 frames per step).
 
   value  frames/s with the chunk already resident in HBM (vxorb_resident_run), CUDA events on the library's
-         own streams, max over ranks.  Passes are pipelined over the handle's three slots exactly as the
+         own streams, max over ranks.  Passes are pipelined over the handle's pipeline slots exactly as the
          streaming path pipelines chunks; nothing crosses PCIe.  The working set of a chunk (pyramid + blurred
          pyramid + lists, ~2.3 MB/frame) is larger than the 126 MB L2.
   e2e    the same metric through the public streaming call (vxorb_track_submit/_wait) with pinned HOST frames
@@ -458,21 +458,23 @@ def fabric_probe(local_rank, world, h2d_bytes, d2h_bytes, host_barrier, iters=48
     bytes on another.  Returns this rank's host->device GB/s.  The end-to-end figure cannot exceed it."""
     import torch
     torch.cuda.set_device(local_rank)
-    host = [torch.empty(h2d_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
-    dev = [torch.empty(h2d_bytes, dtype=torch.uint8, device="cuda") for _ in range(2)]
-    back_d = torch.empty(d2h_bytes, dtype=torch.uint8, device="cuda")
-    back_h = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory()
-    s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+    k = 3  # copies in flight per direction, as the streaming path keeps three chunks in flight
+    host = [torch.empty(h2d_bytes, dtype=torch.uint8).pin_memory() for _ in range(k)]
+    dev = [torch.empty(h2d_bytes, dtype=torch.uint8, device="cuda") for _ in range(k)]
+    back_d = [torch.empty(d2h_bytes, dtype=torch.uint8, device="cuda") for _ in range(k)]
+    back_h = [torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory() for _ in range(k)]
+    s_up = [torch.cuda.Stream() for _ in range(k)]
+    s_dn = [torch.cuda.Stream() for _ in range(k)]
 
     def run(n):
         torch.cuda.synchronize()
         host_barrier(world)
         t0 = time.perf_counter()
         for i in range(n):
-            with torch.cuda.stream(s_up):
-                dev[i % 2].copy_(host[i % 2], non_blocking=True)
-            with torch.cuda.stream(s_dn):
-                back_h.copy_(back_d, non_blocking=True)
+            with torch.cuda.stream(s_up[i % k]):
+                dev[i % k].copy_(host[i % k], non_blocking=True)
+            with torch.cuda.stream(s_dn[i % k]):
+                back_h[i % k].copy_(back_d[i % k], non_blocking=True)
         torch.cuda.synchronize()
         return h2d_bytes * n / (time.perf_counter() - t0) / 1e9
     run(8)
@@ -713,7 +715,7 @@ def run_ours(args, rank, world, local_rank):
                          "e2e": aggregate_throughput(B * win_passes, ms_e2e_win_max, world),
                          "ms_per_chunk": ms_res_win_max / win_passes, "unit": "frames/s"},
             "schedule": {"ms_per_chunk_pipelined": ms_resident / passes, "ms_per_chunk_serial_instrumented": ms_serial / n_instr,
-                         "note": "value is timed on the production schedule: passes pipelined over the handle's 3 slots, the blur on "
+                         "note": "value is timed on the production schedule: passes pipelined over the handle's pipeline slots, the blur on "
                                  "a side stream beside FAST + select; the stage table and the roofline come from a serial "
                                  "pass on one stream with events around every stage"},
             "roofline": roofline, "stages": table, "cpu_baseline": cpu, "clocks": clocks,
