@@ -185,6 +185,15 @@ int vxorb_match_boxed(vxorb_handle* h, const uint8_t* query, const float* query_
                       const uint8_t* train, const float* train_xy, int nt, const float* box,
                       float nn_ratio, int out_cap, vxorb_match_t* out, int* n_out);
 
+/* Arbitrary mask = cv::BFMatcher::knnMatch(query, train, 2, mask): mask is an nq x nt byte matrix (mask_stride bytes
+ * per row), pair (i, j) is allowed iff mask[i][j] != 0.  The general (and slowest: the mask crosses the link) form of
+ * the window and box variants above. */
+int vxorb_knn2_masked(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt,
+                      const uint8_t* mask, size_t mask_stride, vxorb_knn2_t* knn_out);
+int vxorb_match_masked(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt,
+                       const uint8_t* mask, size_t mask_stride, float nn_ratio, int out_cap, vxorb_match_t* out,
+                       int* n_out);
+
 /* cv::BFMatcher(NORM_HAMMING, crossCheck=true).match: (i, j) kept iff j is i's nearest train
  * row and i is j's nearest query row, both with lowest-index tie-break. */
 int vxorb_match_crosscheck(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train,
@@ -208,6 +217,13 @@ int vxorb_set_free(vxorb_handle* h, long long id);
 int vxorb_set_size(const vxorb_handle* h, long long id);
 int vxorb_match_ids(vxorb_handle* h, long long query_id, long long train_id, float radius, float nn_ratio,
                     int mode, int out_cap, vxorb_match_t* out, int* n_out);
+
+/* Depth of every feature of a resident frame as Tracking::CreateLandmarksFromDepth reads it
+ * (tracking.cpp:606-637): u = (int)(x + 0.5), v = (int)(y + 0.5); depth_m_out[i] = depth in metres (16-bit / 5000,
+ * float or double image: depth_type 0 / 1 / 2), 0.0 where the reference skips the feature (outside the image,
+ * 16-bit depth 0, metres outside [0.1, 10]).  *n_out = number of features of the frame. */
+int vxorb_depth_lookup(vxorb_handle* h, long long frame_id, const void* depth, int depth_type, int width, int height,
+                       size_t stride, int cap, double* depth_m_out, int* n_out);
 
 /* ---- streaming sequence path (BASELINE config 2): batched extract + frame-to-frame match ---
  *

@@ -75,6 +75,10 @@ def lib():
         L.vxo_knn2_boxed.restype = None
         L.vxo_match_boxed.argtypes = [u8p, f32p, C.c_int, u8p, f32p, C.c_int, f32p, C.c_float, vp, C.c_int]
         L.vxo_match_boxed.restype = C.c_int
+        L.vxo_knn2_masked.argtypes = [u8p, C.c_int, u8p, C.c_int, u8p, sz, vp]
+        L.vxo_knn2_masked.restype = None
+        L.vxo_depth_lookup.argtypes = [f32p, C.c_int, vp, C.c_int, C.c_int, C.c_int, sz, vp]
+        L.vxo_depth_lookup.restype = None
         L.vxo_image_stats.argtypes = [u8p, C.c_int, C.c_int, sz, vp, vp]
         L.vxo_image_stats.restype = None
         L.vxo_grid_coverage.argtypes = [f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]
@@ -256,6 +260,36 @@ def correspondences(q_xy, t_xy, matches):
     pts = np.zeros((max(len(m), 1), 4), np.float32)
     par = lib().vxo_correspondences(_p(q_xy), _p(t_xy), _p(m), len(m), _p(pts))
     return pts[:len(m)].copy(), float(par)
+
+
+def knn2_masked(q, t, mask):
+    """cv knnMatch(k=2, mask): pair (i, j) allowed iff mask[i, j] != 0."""
+    q, t = _desc(q), _desc(t)
+    mask = np.ascontiguousarray(mask, dtype=np.uint8).reshape(len(q), len(t))
+    out = np.zeros(len(q), KNN2_DTYPE)
+    lib().vxo_knn2_masked(_p(q), len(q), _p(t), len(t), _p(mask), mask.shape[1], _p(out))
+    return out
+
+
+def match_from_knn(knn, nn_ratio=0.8):
+    """The ratio loop of ORBMatcher::Match (orb_matcher.cpp:27-36) over a 2-NN table."""
+    r = np.float32(nn_ratio)
+    rows = [(i, int(k["idx"][0]), int(k["dist"][0])) for i, k in enumerate(knn)
+            if k["idx"][1] >= 0 and np.float32(k["dist"][0]) < r * np.float32(k["dist"][1])]
+    return np.array(rows, MATCH_DTYPE) if rows else np.zeros(0, MATCH_DTYPE)
+
+
+DEPTH_TYPES = {np.dtype(np.uint16): 0, np.dtype(np.float32): 1, np.dtype(np.float64): 2}
+
+
+def depth_lookup(xy, depth):
+    """Tracking::CreateLandmarksFromDepth's per-feature depth in metres (tracking.cpp:606-637); 0 = skipped."""
+    xy = _xy(xy) if xy is not None and len(xy) else np.zeros((0, 2), np.float32)
+    depth = np.ascontiguousarray(depth)
+    out = np.zeros(max(len(xy), 1), np.float64)
+    lib().vxo_depth_lookup(_p(xy), len(xy), depth.ctypes.data, DEPTH_TYPES[depth.dtype], depth.shape[1], depth.shape[0],
+                           depth.strides[0], _p(out))
+    return out[:len(xy)].copy()
 
 
 def knn2_boxed(q, t, q_xy, t_xy, box):

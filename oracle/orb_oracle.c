@@ -614,7 +614,55 @@ int vxo_match_boxed(const uint8_t* q, const float* qxy, int nq, const uint8_t* t
     return n;
 }
 
+/* Arbitrary mask: cv::BFMatcher::knnMatch(q, t, 2, mask) with mask an nq x nt CV_8U matrix, pair (i, j) allowed
+ * iff mask[i][j] != 0 (the general form of the window / box masks above; SURVEY.md section 8b vxorb_match_masked). */
+void vxo_knn2_masked(const uint8_t* q, int nq, const uint8_t* t, int nt, const uint8_t* mask, size_t mask_stride,
+                     vxorb_knn2_t* out) {
+    for (int i = 0; i < nq; ++i) {
+        int d0 = 1 << 30, d1 = 1 << 30, i0 = -1, i1 = -1;
+        for (int j = 0; j < nt; ++j) {
+            if (!mask[(size_t)i * mask_stride + j]) continue;
+            int d = hamming256(q + (size_t)i * 32, t + (size_t)j * 32);
+            if (d < d0) {
+                d1 = d0; i1 = i0; d0 = d; i0 = j;
+            } else if (d < d1) {
+                d1 = d; i1 = j;
+            }
+        }
+        out[i].idx[0] = i0;
+        out[i].idx[1] = i1;
+        out[i].dist[0] = i0 >= 0 ? d0 : 0;
+        out[i].dist[1] = i1 >= 0 ? d1 : 0;
+    }
+}
+
 /* ---- caller-side per-frame quantities --------------------------------- */
+
+/* Depth of every feature as Tracking::CreateLandmarksFromDepth reads it (core/frontend/tracking.cpp:606-637):
+ * u = (int)(x + 0.5), v = (int)(y + 0.5) on the double position; skipped when outside the image, when a 16-bit
+ * depth is 0, or when the depth in metres (u16 / 5000, float, double) is outside [0.1, 10].  depth_type: 0 = CV_16U,
+ * 1 = CV_32F, 2 = CV_64F.  out[i] = depth in metres, 0 where the reference skips the feature. */
+void vxo_depth_lookup(const float* xy, int n, const void* depth, int depth_type, int cols, int rows, size_t stride,
+                      double* out) {
+    for (int i = 0; i < n; ++i) {
+        out[i] = 0.0;
+        const int u = (int)((double)xy[2 * i] + 0.5), v = (int)((double)xy[2 * i + 1] + 0.5);
+        if (u < 0 || u >= cols || v < 0 || v >= rows) continue;
+        const uint8_t* row = (const uint8_t*)depth + (size_t)v * stride;
+        double m;
+        if (depth_type == 0) {
+            const uint16_t d = ((const uint16_t*)row)[u];
+            if (d == 0) continue;
+            m = (double)d / 5000.0;
+        } else if (depth_type == 1) {
+            m = (double)((const float*)row)[u];
+        } else {
+            m = ((const double*)row)[u];
+        }
+        if (m < 0.1 || m > 10.0) continue;
+        out[i] = m;
+    }
+}
 
 /* cv::meanStdDev of an 8-bit single-channel image, as Tracking::CheckImageQuality calls it
  * (core/frontend/tracking.cpp:126-127).  OpenCV accumulates integer sums, then evaluates

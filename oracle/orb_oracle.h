@@ -39,6 +39,10 @@ void vxo_knn2_boxed(const uint8_t* q, const float* qxy, int nq, const uint8_t* t
                     const float* box, vxorb_knn2_t* out);
 int vxo_match_boxed(const uint8_t* q, const float* qxy, int nq, const uint8_t* t, const float* txy, int nt,
                     const float* box, float nn_ratio, vxorb_match_t* out, int cap);
+void vxo_knn2_masked(const uint8_t* q, int nq, const uint8_t* t, int nt, const uint8_t* mask, size_t mask_stride,
+                     vxorb_knn2_t* out);
+void vxo_depth_lookup(const float* xy, int n, const void* depth, int depth_type, int cols, int rows, size_t stride,
+                      double* out);
 void vxo_image_stats(const uint8_t* img, int w, int h, size_t stride, double* mean, double* sd);
 int vxo_grid_coverage(const float* xy, int n, int width, int height, int cols, int rows, uint32_t* mask);
 double vxo_correspondences(const float* q_xy, const float* t_xy, const vxorb_match_t* m, int n, float* pts);

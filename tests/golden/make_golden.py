@@ -261,8 +261,35 @@ def stereo_kat():
     print("stereo", len(kl), len(kr), "matches", len(m))
 
 
+def masked_kat():
+    """cv knnMatch(k=2, mask) with an arbitrary nq x nt CV_8U mask (SURVEY.md 8b vxorb_match_masked): few distinct
+    descriptors (heavy distance ties -> lowest allowed train index), rows with no / one / all pairs allowed
+    -> masked_kat.npz."""
+    rng = np.random.default_rng(77)
+    base = rng.integers(0, 256, (12, 32), dtype=np.uint8)
+    t = base[rng.integers(0, 12, 700)].copy()
+    q = base[rng.integers(0, 12, 300)].copy()
+    t[::4, 5] ^= 0x33
+    q[::3, 9] ^= 0x0c
+    t[600:] = rng.integers(0, 256, (100, 32), dtype=np.uint8)      # distinct rows with near-copies among the queries
+    q[200:] = t[600:]
+    q[200:, 3] ^= 0x41
+    mask = (rng.random((300, 700)) < 0.15).astype(np.uint8)
+    mask[np.arange(200, 300), np.arange(600, 700)] = (np.arange(100) % 3 != 0)  # a third of the true partners masked out
+    mask[5] = 0                      # no neighbour at all
+    mask[6] = 0
+    mask[6, 123] = 1                 # exactly one neighbour -> knn row of size 1 -> never a ratio match
+    mask[7] = 255                    # everything allowed, any non-zero value counts
+    knn = cv_knn2(q, t, mask)
+    m = ratio_matches(knn)
+    np.savez_compressed(os.path.join(HERE, "masked_kat.npz"), q=q, t=t, mask=mask, knn=knn, matches=m)
+    print("masked", len(q), len(t), "allowed", int(mask.astype(bool).sum()), "matches", len(m))
+
+
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
+    if which in ("all", "masked"):
+        masked_kat()
     if which in ("all",):
         main()
     if which in ("all", "caller"):

@@ -298,6 +298,47 @@ def test_match_windowed_vs_oracle(h, nq, nt, radius, kind):
                           matches_as_rows(oracle.match(q, t, 0.8, qxy, txy, radius)))
 
 
+def test_match_masked_golden(h):
+    """Arbitrary byte mask = cv knnMatch(k=2, mask) (masked_kat.npz: ties, empty and single-entry rows), then larger
+    random masks against the oracle, and the window mask written out as bytes against the windowed kernel."""
+    g = load_golden("masked_kat.npz")
+    assert _knn_equal(h.knn2_masked(g["q"], g["t"], g["mask"]), g["knn"])
+    assert np.array_equal(matches_as_rows(h.match_masked(g["q"], g["t"], g["mask"])), g["matches"])
+    rng = np.random.default_rng(31)
+    for nq, nt, density in ((1000, 1000, 0.05), (257, 3000, 0.5), (3, 5, 1.0), (700, 129, 0.002)):
+        t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+        q = t[rng.integers(0, nt, nq)].copy()
+        q[:, 7] ^= rng.integers(0, 8, nq).astype(np.uint8)
+        mask = (rng.random((nq, nt)) < density).astype(np.uint8) * 3
+        assert _knn_equal(h.knn2_masked(q, t, mask), oracle.knn2_masked(q, t, mask)), (nq, nt)
+        assert np.array_equal(matches_as_rows(h.match_masked(q, t, mask, 0.7)),
+                              matches_as_rows(oracle.match_from_knn(oracle.knn2_masked(q, t, mask), 0.7)))
+    qxy = (rng.random((700, 2)) * 300).astype(np.float32)
+    txy = (rng.random((129, 2)) * 300).astype(np.float32)
+    win = ((np.abs(qxy[:, None, 0] - txy[None, :, 0]) <= 40) & (np.abs(qxy[:, None, 1] - txy[None, :, 1]) <= 40)).astype(np.uint8)
+    assert _knn_equal(h.knn2_masked(q, t, win), h.knn2(q, t, qxy, txy, 40.0))
+
+
+def test_depth_lookup_vs_oracle(golden_c1):
+    """Tracking::CreateLandmarksFromDepth's per-feature depth (tracking.cpp:606-637) for a resident frame, all three
+    depth image types, against the oracle."""
+    rng = np.random.default_rng(5)
+    with vx.VxOrb() as hx:
+        kp, desc, fid = hx.extract_id(golden_c1["frame_a"])
+        xy = np.stack([kp["x"], kp["y"]], 1)
+        d16 = rng.integers(0, 60000, (480, 640)).astype(np.uint16)
+        d16[rng.random(d16.shape) < 0.2] = 0
+        for depth in (d16, (rng.random((480, 640)) * 12).astype(np.float32), rng.random((480, 640)) * 12):
+            got = hx.depth_lookup(fid, depth)
+            assert np.array_equal(got, oracle.depth_lookup(xy, depth)), depth.dtype
+            assert (got > 0).sum() > 300
+        small = np.full((100, 100), 5000, np.uint16)  # a depth image smaller than the frame: features outside are skipped
+        got = hx.depth_lookup(fid, small)
+        assert np.array_equal(got, oracle.depth_lookup(xy, small)) and 0 < (got > 0).sum() < len(kp)
+        with pytest.raises(vx.VxOrbError):
+            hx.depth_lookup(fid + 100, d16)
+
+
 def test_match_empty_sides(h):
     z = np.zeros((0, 32), np.uint8)
     q = np.zeros((5, 32), np.uint8)

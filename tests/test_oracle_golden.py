@@ -209,7 +209,8 @@ def test_stereo_boxed_golden():
     assert sha256(left) == str(g["left_sha"]) and sha256(right) == str(g["right_sha"])
     kl, dl = oracle.orb_extract(left, n_features=2000)
     kr, dr = oracle.orb_extract(right, n_features=2000)
-    assert_kp_equal(kl, g["kp_left"]) and assert_kp_equal(kr, g["kp_right"])
+    assert_kp_equal(kl, g["kp_left"])
+    assert_kp_equal(kr, g["kp_right"])
     assert np.array_equal(dl, g["desc_left"]) and np.array_equal(dr, g["desc_right"])
     qxy, txy = np.stack([kl["x"], kl["y"]], 1), np.stack([kr["x"], kr["y"]], 1)
     knn = oracle.knn2_boxed(dl, dr, qxy, txy, g["box"])
@@ -221,3 +222,46 @@ def test_stereo_boxed_golden():
     # the square window is the box {-r, r, -r, r}
     assert np.array_equal(oracle.knn2_boxed(dl, dr, qxy, txy, [-40, 40, -40, 40])["idx"],
                           oracle.knn2(dl, dr, qxy, txy, 40.0)["idx"])
+
+
+# ---- arbitrary mask (cv knnMatch(mask)) and the depth look-up of the landmark creation ------------------
+
+def test_masked_knn_golden():
+    """oracle.knn2_masked against cv2's knnMatch(k=2, mask) (masked_kat.npz): ties, empty and single-entry rows."""
+    g = load_golden("masked_kat.npz")
+    knn = oracle.knn2_masked(g["q"], g["t"], g["mask"])
+    assert np.array_equal(knn["idx"], g["knn"]["idx"])
+    assert np.array_equal(np.where(knn["idx"] >= 0, knn["dist"], 0), np.where(g["knn"]["idx"] >= 0, g["knn"]["dist"], 0))
+    assert list(knn["idx"][5]) == [-1, -1] and list(knn["idx"][6]) == [123, -1]
+    assert np.array_equal(matches_as_rows(oracle.match_from_knn(knn)), g["matches"])
+    # the window and box masks are special cases of it
+    rng = np.random.default_rng(3)
+    qxy = (rng.random((300, 2)) * 200).astype(np.float32)
+    txy = (rng.random((700, 2)) * 200).astype(np.float32)
+    win = ((np.abs(qxy[:, None, 0] - txy[None, :, 0]) <= 30) & (np.abs(qxy[:, None, 1] - txy[None, :, 1]) <= 30)).astype(np.uint8)
+    assert np.array_equal(oracle.knn2_masked(g["q"], g["t"], win), oracle.knn2(g["q"], g["t"], qxy, txy, 30.0))
+
+
+def test_depth_lookup_restatement():
+    """oracle.depth_lookup against an independent numpy statement of tracking.cpp:606-637."""
+    rng = np.random.default_rng(8)
+    xy = (rng.random((500, 2)) * np.float32([660, 500]) - 10).astype(np.float32)  # some outside the image
+    xy[:4] = [[0.49, 0.5], [639.5, 479.49], [639.49, 479.5], [-0.5, 10.0]]
+    for dt, img in ((np.uint16, rng.integers(0, 60000, (480, 640)).astype(np.uint16)),
+                    (np.float32, (rng.random((480, 640)) * 12).astype(np.float32)),
+                    (np.float64, rng.random((480, 640)) * 12)):
+        if dt is np.uint16:
+            img[rng.random(img.shape) < 0.2] = 0
+        got = oracle.depth_lookup(xy, img)
+        want = np.zeros(len(xy))
+        for i, (x, y) in enumerate(xy.astype(np.float64)):
+            u, v = int(x + 0.5), int(y + 0.5)  # C truncation toward zero, like static_cast<int>
+            if not (0 <= u < 640 and 0 <= v < 480):
+                continue
+            m = float(img[v, u]) / 5000.0 if dt is np.uint16 else float(img[v, u])
+            if dt is np.uint16 and img[v, u] == 0:
+                continue
+            if 0.1 <= m <= 10.0:
+                want[i] = m
+        assert np.array_equal(got, want), dt
+        assert (got > 0).sum() > 100

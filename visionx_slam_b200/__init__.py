@@ -74,6 +74,9 @@ _SYMBOLS = [
     ("vxorb_match_windowed", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _i, _vp, _vp]),
     ("vxorb_knn2_boxed", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp]),
     ("vxorb_match_boxed", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _f, _i, _vp, _vp]),
+    ("vxorb_knn2_masked", _i, [_vp, _vp, _i, _vp, _i, _vp, _sz, _vp]),
+    ("vxorb_match_masked", _i, [_vp, _vp, _i, _vp, _i, _vp, _sz, _f, _i, _vp, _vp]),
+    ("vxorb_depth_lookup", _i, [_vp, C.c_longlong, _vp, _i, _i, _i, _sz, _i, _vp, _vp]),
     ("vxorb_match_crosscheck", _i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp]),
     ("vxorb_match_filtered", _i, [_vp, _vp, _i, _vp, _i, _f, _i, _vp, _vp]),
     ("vxorb_track_slots", _i, [_vp]),
@@ -377,6 +380,33 @@ class VxOrb:
         n = C.c_int(0)
         self._check(self._lib.vxorb_match_boxed(self._h, _ptr(q), _ptr(q_xy), len(q), _ptr(t), _ptr(t_xy), len(t), _ptr(b),
                                                 nn_ratio, len(out), _ptr(out), C.byref(n)))
+        return out[:n.value].copy()
+
+    def knn2_masked(self, q, t, mask):
+        """cv knnMatch(k=2, mask): mask (nq, nt) uint8, pair allowed iff non-zero."""
+        q, t = _desc(q), _desc(t)
+        mask = np.ascontiguousarray(mask, dtype=np.uint8).reshape(len(q), len(t))
+        out = np.zeros(len(q), KNN2_DTYPE)
+        self._check(self._lib.vxorb_knn2_masked(self._h, _ptr(q), len(q), _ptr(t), len(t), _ptr(mask), mask.strides[0], _ptr(out)))
+        return out
+
+    def match_masked(self, q, t, mask, nn_ratio=0.0):
+        q, t = _desc(q), _desc(t)
+        mask = np.ascontiguousarray(mask, dtype=np.uint8).reshape(len(q), len(t))
+        out = np.zeros(max(len(q), 1), MATCH_DTYPE)
+        n = C.c_int(0)
+        self._check(self._lib.vxorb_match_masked(self._h, _ptr(q), len(q), _ptr(t), len(t), _ptr(mask), mask.strides[0],
+                                                 nn_ratio, len(out), _ptr(out), C.byref(n)))
+        return out[:n.value].copy()
+
+    def depth_lookup(self, frame_id, depth):
+        """Per-feature depth in metres of a resident frame (Tracking::CreateLandmarksFromDepth); 0 = skipped."""
+        depth = np.ascontiguousarray(depth)
+        dt = {np.dtype(np.uint16): 0, np.dtype(np.float32): 1, np.dtype(np.float64): 2}[depth.dtype]
+        out = np.zeros(self.kp_cap, np.float64)
+        n = C.c_int(0)
+        self._check(self._lib.vxorb_depth_lookup(self._h, frame_id, _ptr(depth), dt, depth.shape[1], depth.shape[0],
+                                                 depth.strides[0], len(out), _ptr(out), C.byref(n)))
         return out[:n.value].copy()
 
     def match_crosscheck(self, q, t):

@@ -105,6 +105,9 @@ struct vxorb_handle {
     vxorb_knn2_t *m_knn = nullptr, *m_back = nullptr;
     vxorb_match_t* m_out = nullptr;
     uint2* m_part = nullptr;  // per-split partial top-2 keys of the single-pair brute-force launch
+    uint8_t* m_mask = nullptr;  // nq x nt byte mask of vxorb_knn2_masked / vxorb_match_masked
+    size_t m_mask_bytes = 0;
+    const uint8_t* pending_mask = nullptr;
     int* m_out_n = nullptr;
     int m_cap = 0;
     // single-image stage scratch
@@ -686,6 +689,10 @@ int run_knn_device(vxorb_handle* h, const DevSet& q, const DevSet& t, float radi
     a.max_q = q.n; a.max_t = t.n; a.pairs = 1; a.radius = win ? radius : 0.f;
     a.knn = h->m_knn; a.knn_stride = 0;
     a.part = h->m_part;
+    if (h->pending_mask) {  // set by the masked entry points around their run_knn_host call
+        a.mask = h->pending_mask;
+        a.mask_stride = t.n;
+    }
     if (box) {
         a.boxed = 1;
         for (int i = 0; i < 4; ++i) a.box[i] = box[i];
@@ -920,7 +927,7 @@ void vxorb_destroy(vxorb_handle* h) {
     }
     cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);
     cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n); cudaFree(h->m_part);
-    cudaFree(h->s_a); cudaFree(h->s_b); cudaFree(h->flush_buf);
+    cudaFree(h->s_a); cudaFree(h->s_b); cudaFree(h->flush_buf); cudaFree(h->m_mask);
     if (h->x_stage) cudaFreeHost(h->x_stage);
     for (auto& sp : h->spans) {
         cudaEventDestroy(sp.a);
@@ -1149,6 +1156,86 @@ int vxorb_match_boxed(vxorb_handle* h, const uint8_t* query, const float* query_
         return fail(h, VXORB_E_INVALID, "boxed match needs positions and box = {dx_min <= dx_max, dy_min <= dy_max}");
     CK(cudaSetDevice(h->p.device_id));
     return run_match_host(h, query, query_xy, nq, train, train_xy, nt, 0.f, nn_ratio, 0, out_cap, out, n_out, box);
+}
+
+// Arbitrary mask = cv::BFMatcher::knnMatch(q, t, 2, mask): uploads the nq x nt byte mask next to the descriptors.
+static int masked_common(vxorb_handle* h, const uint8_t* q, int nq, const uint8_t* t, int nt, const uint8_t* mask,
+                         size_t mask_stride) {
+    if (!mask || mask_stride < (size_t)nt) return fail(h, VXORB_E_INVALID, "masked match needs an nq x nt mask (stride >= nt)");
+    CK(cudaSetDevice(h->p.device_id));
+    const size_t bytes = (size_t)nq * nt;
+    if (bytes > h->m_mask_bytes) {
+        cudaFree(h->m_mask);
+        h->m_mask = nullptr;
+        h->m_mask_bytes = 0;
+        CK(cudaMalloc(&h->m_mask, bytes));
+        h->m_mask_bytes = bytes;
+    }
+    cudaStream_t s = h->ws[0].stream;
+    CK(cudaMemcpy2DAsync(h->m_mask, (size_t)nt, mask, mask_stride, (size_t)nt, (size_t)nq, cudaMemcpyHostToDevice, s));
+    h->pending_mask = h->m_mask;
+    const int rc = run_knn_host(h, q, nullptr, nq, t, nullptr, nt, 0.f, false);
+    h->pending_mask = nullptr;
+    return rc;
+}
+
+int vxorb_knn2_masked(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, const uint8_t* mask,
+                      size_t mask_stride, vxorb_knn2_t* knn_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (nq > 0 && !knn_out) return fail(h, VXORB_E_INVALID, "null output");
+    if (nq <= 0) return nq < 0 ? fail(h, VXORB_E_INVALID, "negative count") : VXORB_OK;
+    if (nt <= 0) {  // no train rows: every knn row is empty
+        if (nt < 0) return fail(h, VXORB_E_INVALID, "negative count");
+        for (int i = 0; i < nq; ++i) knn_out[i] = vxorb_knn2_t{{-1, -1}, {0, 0}};
+        return VXORB_OK;
+    }
+    int rc = masked_common(h, query, nq, train, nt, mask, mask_stride);
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    CK(cudaMemcpyAsync(knn_out, h->m_knn, sizeof(vxorb_knn2_t) * (size_t)nq, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return VXORB_OK;
+}
+
+int vxorb_match_masked(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, const uint8_t* mask,
+                       size_t mask_stride, float nn_ratio, int out_cap, vxorb_match_t* out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    if (!n_out || out_cap < 0 || (out_cap > 0 && !out)) return fail(h, VXORB_E_INVALID, "bad output arguments");
+    *n_out = 0;
+    if (nq <= 0 || nt <= 0) return (nq < 0 || nt < 0) ? fail(h, VXORB_E_INVALID, "negative descriptor count") : VXORB_OK;
+    int rc = masked_common(h, query, nq, train, nt, mask, mask_stride);
+    if (rc) return rc;
+    const DevSet dq{h->m_q, nullptr, h->m_n, nq};
+    return finish_match(h, dq, nn_ratio, 0, out_cap, out, n_out);
+}
+
+// Tracking::CreateLandmarksFromDepth's look-up (tracking.cpp:606-637) for a frame whose positions are still on the
+// device: only the depth image goes up and one double per feature comes back.
+int vxorb_depth_lookup(vxorb_handle* h, long long frame_id, const void* depth, int depth_type, int width, int height,
+                       size_t stride, int cap, double* depth_m_out, int* n_out) {
+    if (!h) return VXORB_E_INVALID;
+    const size_t elem = depth_type == 0 ? 2 : depth_type == 1 ? 4 : 8;
+    if (!depth || !n_out || depth_type < 0 || depth_type > 2 || width < 1 || height < 1 || stride < elem * (size_t)width ||
+        cap < 0 || (cap > 0 && !depth_m_out))
+        return fail(h, VXORB_E_INVALID, "bad depth arguments (depth_type 0 = u16, 1 = f32, 2 = f64)");
+    *n_out = 0;
+    const ResidentSet* fs = find_set(h, frame_id);
+    if (!fs || !fs->xy) return fail(h, VXORB_E_INVALID, "unknown or overwritten frame id (or a set without positions)");
+    CK(cudaSetDevice(h->p.device_id));
+    const int n = fs->n_host;
+    *n_out = n;
+    if (n == 0) return VXORB_OK;
+    const size_t img = stride * (size_t)height, out_off = align_up(img, 256);
+    int rc = ensure_stage_scratch(h, out_off + sizeof(double) * (size_t)n);
+    if (rc) return rc;
+    cudaStream_t s = h->ws[0].stream;
+    CK(cudaMemcpyAsync(h->s_a, depth, img, cudaMemcpyHostToDevice, s));
+    double* d_out = reinterpret_cast<double*>(h->s_a + out_off);
+    h->launches += launch_depth_lookup(fs->xy, fs->n, n, h->s_a, depth_type, width, height, stride, d_out, s);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(depth_m_out, d_out, sizeof(double) * (size_t)std::min(n, cap), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return n > cap ? fail(h, VXORB_E_CAPACITY, "depth output buffer too small") : VXORB_OK;
 }
 
 int vxorb_match(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train, int nt, float nn_ratio,

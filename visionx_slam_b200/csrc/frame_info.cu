@@ -138,6 +138,44 @@ frame_info_kernel(const unsigned long long* __restrict__ sums, int w, int h, con
     }
 }
 
+// Depth of every feature as Tracking::CreateLandmarksFromDepth reads it (tracking.cpp:606-637): u = (int)(x + 0.5),
+// v = (int)(y + 0.5) on the position widened to double; 0 where the reference skips the feature (outside the image,
+// 16-bit depth 0, depth in metres outside [0.1, 10]).
+__global__ void __launch_bounds__(256)
+depth_lookup_kernel(const float2* __restrict__ xy, const int* __restrict__ n_dev, int max_n, const uint8_t* __restrict__ depth,
+                    int depth_type, int cols, int rows, size_t stride, double* __restrict__ out) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= max_n) return;
+    double m = 0.0;
+    if (i < *n_dev) {
+        const float2 p = __ldg(xy + i);
+        const int u = (int)__dadd_rn((double)p.x, 0.5), v = (int)__dadd_rn((double)p.y, 0.5);
+        if (u >= 0 && u < cols && v >= 0 && v < rows) {
+            const uint8_t* row = depth + (size_t)v * stride;
+            bool ok = true;
+            if (depth_type == 0) {
+                const unsigned short d = __ldg(reinterpret_cast<const unsigned short*>(row) + u);
+                ok = d != 0;
+                m = __ddiv_rn((double)d, 5000.0);
+            } else if (depth_type == 1) {
+                m = (double)__ldg(reinterpret_cast<const float*>(row) + u);
+            } else {
+                m = __ldg(reinterpret_cast<const double*>(row) + u);
+            }
+            if (!ok || m < 0.1 || m > 10.0) m = 0.0;  // the reference's two comparisons (a NaN depth passes both, as there)
+        }
+    }
+    out[i] = m;
+}
+
+int launch_depth_lookup(const float* xy, const int* n_dev, int max_n, const void* depth, int depth_type, int cols, int rows,
+                        size_t stride, double* out, cudaStream_t s) {
+    if (max_n <= 0) return 0;
+    depth_lookup_kernel<<<(max_n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float2*>(xy), n_dev, max_n,
+                                                            static_cast<const uint8_t*>(depth), depth_type, cols, rows, stride, out);
+    return 1;
+}
+
 int launch_frame_info(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, unsigned long long* sums,
                       vxorb_frame_info* info, float4* pts, int grid_cols, int grid_rows, cudaStream_t s) {
     if (lt.batch <= 0) return 0;

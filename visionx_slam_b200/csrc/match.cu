@@ -82,7 +82,8 @@ knn2_kernel(const MatchArgs a) {
     const int nq = a.q_n[pair * a.n_stride], nt = a.t_n[pair * a.n_stride];
     const int q_first = blockIdx.x * (kQPerBlock * QPT);
     if (q_first >= nq) return;  // whole CTA idle
-    const bool windowed = (a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr;
+    const bool bytemask = a.mask != nullptr;
+    const bool windowed = bytemask || ((a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr);
     // square window = the box [-r, r] x [-r, r] on (xq - xt, yq - yt): |d| <= r <=> -r <= d <= r in float
     const float bx0 = a.boxed ? a.box[0] : -a.radius, bx1 = a.boxed ? a.box[1] : a.radius;
     const float by0 = a.boxed ? a.box[2] : -a.radius, by1 = a.boxed ? a.box[3] : a.radius;
@@ -105,7 +106,7 @@ knn2_kernel(const MatchArgs a) {
             const uint4 hi = __ldg(reinterpret_cast<const uint4*>(qbase + (size_t)qi[u] * 32 + 16));
             q[u][0] = lo.x; q[u][1] = lo.y; q[u][2] = lo.z; q[u][3] = lo.w;
             q[u][4] = hi.x; q[u][5] = hi.y; q[u][6] = hi.z; q[u][7] = hi.w;
-            if (windowed) {
+            if (windowed && !bytemask) {
                 const float2 p = __ldg(reinterpret_cast<const float2*>(a.q_xy + ((size_t)pair * a.q_pair_stride + qi[u]) * 2));
                 qx[u] = p.x;
                 qy[u] = p.y;
@@ -127,7 +128,7 @@ knn2_kernel(const MatchArgs a) {
         for (int i = threadIdx.x; i < tn * 2; i += kQPerBlock)
             reinterpret_cast<uint4*>(&tdesc[0][0])[i] =
                 __ldg(reinterpret_cast<const uint4*>(tbase + (size_t)t0 * 32) + i);
-        if (windowed)
+        if (windowed && !bytemask)
             for (int i = threadIdx.x; i < tn; i += kQPerBlock)
                 txy[i] = __ldg(reinterpret_cast<const float2*>(a.t_xy + ((size_t)pair * a.t_pair_stride + t0) * 2) + i);
         __syncthreads();
@@ -175,13 +176,17 @@ knn2_kernel(const MatchArgs a) {
 #endif
         } else {
             for (int j = 0; j < tn; ++j) {
-                const float2 p = txy[j];
+                const float2 p = bytemask ? make_float2(0.f, 0.f) : txy[j];
                 bool in[QPT];
                 bool any = false;
 #pragma unroll
                 for (int u = 0; u < QPT; ++u) {
-                    const float dx = __fsub_rn(qx[u], p.x), dy = __fsub_rn(qy[u], p.y);
-                    in[u] = dx >= bx0 && dx <= bx1 && dy >= by0 && dy <= by1;
+                    if (bytemask) {  // a thread walks along its own mask row: consecutive bytes, cached lines
+                        in[u] = live[u] && __ldg(a.mask + (size_t)qi[u] * a.mask_stride + (t0 + j)) != 0;
+                    } else {
+                        const float dx = __fsub_rn(qx[u], p.x), dy = __fsub_rn(qy[u], p.y);
+                        in[u] = dx >= bx0 && dx <= bx1 && dy >= by0 && dy <= by1;
+                    }
                     any = any || in[u];
                 }
                 if (__any_sync(0xffffffffu, any)) {
@@ -565,7 +570,7 @@ cudaError_t init_match_kernels() {
 
 int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     if (a.pairs <= 0 || a.max_q <= 0) return 0;
-    const bool windowed = (a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr;
+    const bool windowed = a.mask == nullptr && (a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr;
     // a lone box-masked pair is served faster by the split brute-force launch below (32 CTAs instead of one)
     const bool cells = windowed && !(a.boxed && a.pairs < 4);
     if (cells && a.max_t > 0 && a.max_q <= 65536 && window_smem_bytes(a.max_t, a.max_q) <= 224 * 1024) {
@@ -582,7 +587,7 @@ int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     // few pairs: split the train rows over gridDim.z so that the launch still covers the GPU (two CTAs of
     // 4 warps per SM at least), then merge the partial top-2 keys
     MatchArgs b = a;
-    const bool masked = (a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr;
+    const bool masked = a.mask != nullptr || ((a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr);
     // two queries per thread pay off once a pair alone brings enough query blocks (measured: 4000 x 16384
     // 0.303 -> 0.242 ms; 128 pairs of 1000 x 1000 lose occupancy with it)
 #ifndef VXORB_KNN_QPT2_MIN

@@ -161,6 +161,9 @@ struct MatchArgs {
     // box[2] <= yq - yt <= box[3]; used instead of the square window when boxed != 0
     int boxed = 0;
     float box[4] = {0.f, 0.f, 0.f, 0.f};
+    // arbitrary mask (cv knnMatch(mask)): row-major [max_q][mask_stride] bytes of ONE pair, pair (i, j) allowed iff != 0
+    const uint8_t* mask = nullptr;
+    long long mask_stride = 0;
     vxorb_knn2_t* knn;                              // [pair][knn_stride]
     int knn_stride;
     // brute-force path with few pairs: the train set is split over gridDim.z CTAs per query block, each
@@ -177,6 +180,9 @@ int launch_match_compact(const vxorb_knn2_t* knn, const vxorb_knn2_t* back, int 
 // frame_info.cu: image sums over level 0, grid coverage, matched positions and parallax (2 launches)
 int launch_frame_info(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, unsigned long long* sums,
                       vxorb_frame_info* info, float4* pts, int grid_cols, int grid_rows, cudaStream_t s);
+// Tracking::CreateLandmarksFromDepth's per-feature depth (tracking.cpp:606-637): depth_type 0 = u16 (/5000), 1 = f32, 2 = f64
+int launch_depth_lookup(const float* xy, const int* n_dev, int max_n, const void* depth, int depth_type, int cols, int rows,
+                        size_t stride, double* out, cudaStream_t s);
 int launch_flush(uint8_t* buf, size_t bytes, cudaStream_t s);
 int launch_popc_peak(uint32_t* out, int blocks, int iters, cudaStream_t s);
 
