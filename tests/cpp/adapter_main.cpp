@@ -39,6 +39,22 @@ int main(int argc, char** argv) {
         const vxorb_frame_info& fi_ = ce->last_frame_info();
         fprintf(stderr, "FRAMEINFO %d %.17g %.17g %d %d %d\n", i, fi_.mean, fi_.stddev, fi_.grid_occupied,
                 ce->ImageQualityOk() ? 1 : 0, ce->FeatureDistributionOk() ? 1 : 0);
+        // the depth look-up of CreateLandmarksFromDepth (tracking.cpp:586-650) on a synthetic 16-bit depth image
+        if (ch == 1) {
+            std::vector<uint16_t> dep((size_t)w * h);
+            for (int y = 0; y < h; ++y)
+                for (int x = 0; x < w; ++x) dep[(size_t)y * w + x] = (uint16_t)((x * 37 + y * 101 + i * 977) % 60000);
+            cv::Mat depth(h, w, CV_MAKETYPE(CV_16U, 1), dep.data(), (size_t)w * 2);
+            std::vector<double> dm;
+            const bool ok = ce->FeatureDepths(*f, depth, dm);
+            double sum = 0.0;
+            int valid = 0;
+            for (double d : dm) {
+                sum += d;
+                valid += d > 0.0 ? 1 : 0;
+            }
+            fprintf(stderr, "DEPTH %d %d %d %.17g\n", i, ok ? 1 : 0, valid, sum);
+        }
         frames.push_back(f);
     }
     fclose(fi);

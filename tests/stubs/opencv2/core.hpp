@@ -7,6 +7,9 @@
 #include <vector>
 
 #define CV_8U 0
+#define CV_16U 2
+#define CV_32F 5
+#define CV_64F 6
 #define CV_MAKETYPE(depth, cn) ((depth) + (((cn) - 1) << 3))
 #define CV_8UC1 CV_MAKETYPE(CV_8U, 1)
 #define CV_8UC3 CV_MAKETYPE(CV_8U, 3)

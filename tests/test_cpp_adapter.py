@@ -102,6 +102,17 @@ def test_cpp_adapter_matches_oracle(tmp_path):
         assert int(occ) == oocc
         assert int(q_ok) == int(30 <= om <= 225 and osd >= 20) and int(d_ok) == int(oocc >= 12.5)
     assert infos[3][4] == "0" and infos[3][5] == "0"  # blank frame fails both checks
+    # the depth look-up of CreateLandmarksFromDepth served from the positions Extract left on the device
+    deps = [l.split()[1:] for l in log.splitlines() if l.startswith("DEPTH")]
+    assert len(deps) == len(frames)
+    yy, xx = np.mgrid[0:480, 0:640]
+    for (i, ok, valid, total), (okp, _) in zip(deps, ref):
+        depth = ((xx * 37 + yy * 101 + int(i) * 977) % 60000).astype(np.uint16)
+        if len(okp) == 0:
+            assert ok == "0"  # the blank frame has no resident descriptors: the caller keeps its own loop
+            continue
+        want = oracle.depth_lookup(np.stack([okp["x"], okp["y"]], 1), depth)
+        assert ok == "1" and int(valid) == int((want > 0).sum()) and float(total) == sum(want.tolist())  # sequential double sum, as the C++ loop
     # the shared-handle matcher served the non-empty pairs from the descriptors Extract left on the device
     path = [l for l in log.splitlines() if l.startswith("MATCHPATH")][0]
     assert "resident=4 upload=0" in path, path  # 2 pairs x (Match + MatchFiltered); the blank pair returns early

@@ -46,6 +46,23 @@ long long CudaORBExtractor::ResidentId(const Frame& frame) const {
     return 0;
 }
 
+bool CudaORBExtractor::FeatureDepths(const Frame& frame, const cv::Mat& depth, std::vector<double>& depth_m) {
+    depth_m.clear();
+    const long long id = ResidentId(frame);
+    const int type = depth.depth() == CV_16U ? 0 : depth.depth() == CV_32F ? 1 : depth.depth() == CV_64F ? 2 : -1;
+    if (id == 0 || type < 0 || depth.empty() || depth.channels() != 1) return false;
+    depth_m.resize(frame.Features().size());
+    int n = 0;
+    const int rc = vxorb_depth_lookup(handle_, id, depth.data, type, depth.cols, depth.rows, static_cast<size_t>(depth.step),
+                                      static_cast<int>(depth_m.size()), depth_m.data(), &n);
+    if (rc != VXORB_OK || n != static_cast<int>(depth_m.size())) {
+        LOG(ERROR) << "[CudaORBExtractor] depth look-up: " << vxorb_last_error(handle_);
+        depth_m.clear();
+        return false;
+    }
+    return true;
+}
+
 void CudaORBExtractor::Extract(Frame& frame) {
     auto& features = frame.Features();
     features.clear();  // orb_extractor.cpp:16

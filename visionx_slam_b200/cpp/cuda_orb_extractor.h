@@ -52,6 +52,12 @@ public:
     // frame was not extracted here, has been overwritten (ring of 8 frames) or its descriptor matrix no longer
     // is what Extract wrote (row count and a fingerprint of the first and last rows are compared).
     long long ResidentId(const Frame& frame) const;
+    // The per-feature depth Tracking::CreateLandmarksFromDepth (tracking.cpp:586-650) reads from frame.Depth():
+    // depth_m[i] in metres for feature i, 0 where the reference skips it (outside the image, 16-bit depth 0, outside
+    // [0.1, 10] m).  Uses the positions Extract left on the device (only the depth image goes up); returns false
+    // when the frame is no longer resident or the depth type is not CV_16U / CV_32F / CV_64F — the caller then runs
+    // its own loop.
+    bool FeatureDepths(const Frame& frame, const cv::Mat& depth, std::vector<double>& depth_m);
 
 private:
     struct Resident {
