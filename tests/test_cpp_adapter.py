@@ -112,7 +112,10 @@ def test_cpp_adapter_matches_oracle(tmp_path):
             assert ok == "0"  # the blank frame has no resident descriptors: the caller keeps its own loop
             continue
         want = oracle.depth_lookup(np.stack([okp["x"], okp["y"]], 1), depth)
-        assert ok == "1" and int(valid) == int((want > 0).sum()) and float(total) == sum(want.tolist())  # sequential double sum, as the C++ loop
+        acc = 0.0
+        for v in want.tolist():  # plain sequential double adds like the C++ loop (Python's sum() compensates)
+            acc += v
+        assert ok == "1" and int(valid) == int((want > 0).sum()) and float(total) == acc
     # the shared-handle matcher served the non-empty pairs from the descriptors Extract left on the device
     path = [l for l in log.splitlines() if l.startswith("MATCHPATH")][0]
     assert "resident=4 upload=0" in path, path  # 2 pairs x (Match + MatchFiltered); the blank pair returns early
