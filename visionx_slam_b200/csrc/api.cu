@@ -547,9 +547,22 @@ int enqueue_stereo_match(vxorb_handle* h, Workspace& ws, int pairs, const float*
         n += launch_match_compact(a.knn, nullptr, h->kp_cap, 0, a.q_n, n_pairs, h->p.nn_ratio, 0, d.match + cap * out_row,
                                   h->kp_cap, d.match_n + out_row, s, slot_stride);
     };
+    // the two legs are independent (different output rows) and each is latency bound at one CTA per pair and query
+    // split: outside the instrumented mode the temporal leg runs on the slot's side stream beside the stereo leg
+    const bool aside = !h->stage_enabled && ws.side != nullptr && !h->no_overlap;
+    if (aside) {
+        CK(cudaEventRecord(ws.ev_fork, s));
+        CK(cudaStreamWaitEvent(ws.side, ws.ev_fork, 0));
+    }
     leg(1, 2, 2, pairs, 0, true);              // left_k -> right_k
+    if (aside) s = ws.side;
     leg(0, 1, 1, 1, pairs, false);             // carry -> left_0
     leg(1, 3, 2, pairs - 1, pairs + 1, false); // left_{k-1} -> left_k, k >= 1
+    if (aside) {
+        CK(cudaEventRecord(ws.ev_join, ws.side));
+        s = ws.stream;
+        CK(cudaStreamWaitEvent(s, ws.ev_join, 0));
+    }
     sc.end(n);
     CK(cudaGetLastError());
     return VXORB_OK;
