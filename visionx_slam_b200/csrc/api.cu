@@ -242,7 +242,7 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
         lt.fast_tiles_x[l] = lt.active[l] ? fast_tiles_x(lt.w[l], kEdge) : 0;
         const int fty = lt.active[l] ? fast_tiles_y(lt.h[l], kEdge) : 0;
         lt.fast_tile_begin[l + 1] = lt.fast_tile_begin[l] + lt.fast_tiles_x[l] * fty;
-        lt.blur_tiles_x[l] = (lt.w[l] + 3) / 4;
+        lt.blur_tiles_x[l] = (lt.w[l] + kBlurCols - 1) / kBlurCols;
         lt.blur_tile_begin[l + 1] =
             lt.blur_tile_begin[l] + (lt.blur_tiles_x[l] * ((lt.h[l] + kBlurRows - 1) / kBlurRows) + 255) / 256;
         lt.coef_off[l] = coef_off;
@@ -1847,7 +1847,7 @@ static int single_level_tab(vxorb_handle* h, int W, int H, int border, LevelTab*
     lt.cand_cap[0] = lt.active[0] ? ((ew + 1) / 2 + 1) * ((eh + 1) / 2 + 1) : 0;
     lt.fast_tiles_x[0] = lt.active[0] ? fast_tiles_x(W, border) : 0;
     lt.fast_tile_begin[1] = lt.active[0] ? lt.fast_tiles_x[0] * fast_tiles_y(H, border) : 0;
-    lt.blur_tiles_x[0] = (W + 3) / 4;
+    lt.blur_tiles_x[0] = (W + kBlurCols - 1) / kBlurCols;
     lt.blur_tile_begin[1] = (lt.blur_tiles_x[0] * ((H + kBlurRows - 1) / kBlurRows) + 255) / 256;
     for (int l = 1; l < kMaxLevels; ++l) {
         lt.fast_tile_begin[l + 1] = lt.fast_tile_begin[1];

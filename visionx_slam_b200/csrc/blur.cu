@@ -58,8 +58,12 @@ __device__ __forceinline__ float byte_to_float(uint32_t word, uint32_t sel) {
 // parameter form if they ever differ.
 constexpr float kG0 = 0.0701593235f, kG1 = 0.131074876f, kG2 = 0.190712824f, kG3 = 0.216105938f;
 
+constexpr int kBC = kBlurCols;            // columns per thread (4 or 8)
+constexpr int kBW = (kBC + 8) / 4;        // aligned source words per row: columns x0-4 .. x0+kBC+3
+constexpr int kBF = kBC + 6;              // source pixels per row: x0-3 .. x0+kBC+2
+
 template <bool IMM>
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, kBC == 8 ? 2 : 3)
 blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, const GaussK gkp) {
     GaussK gk;
     if (IMM) {
@@ -69,38 +73,36 @@ blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restr
     }
     int l = 0;
     while (l + 1 < lt.n_levels && (int)blockIdx.x >= lt.blur_tile_begin[l + 1]) ++l;
-    const int w = lt.w[l], h = lt.h[l], pitch = lt.pitch[l];
+    const int h = lt.h[l], pitch = lt.pitch[l];
     const int words = lt.blur_tiles_x[l];
     const int item = ((int)blockIdx.x - lt.blur_tile_begin[l]) * 256 + (int)threadIdx.x;
     const int band = item / words;
     const int y0 = band * kBlurRows;
     if (y0 >= h) return;
-    const int x0 = (item - band * words) * 4;
-    (void)w;
+    const int x0 = (item - band * words) * kBC;
     const int rows_out = min(kBlurRows, h - y0);
     const size_t plane = lt.off[l] + (size_t)blockIdx.y * lt.fstride[l];
-    // source row r (0-based in the strip) is image row y0 - 3 + r; word c-1 starts at x0 - 4
+    // source row r (0-based in the strip) is image row y0 - 3 + r; the first word starts at x0 - 4
     const uint8_t* src = pyr + plane + (ptrdiff_t)(y0 - kApronY) * pitch + (x0 - 4);
     uint8_t* dst = blur + plane + (size_t)y0 * pitch + x0;
     const int last_src = rows_out + 2 * kApronY - 1;
     const int groups = (rows_out + 2 * kApronY + 6) / 7;
 
-    float win[7][4];
+    float win[7][kBC];
 #pragma unroll
     for (int i = 0; i < 7; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) win[i][j] = 0.f;
+        for (int j = 0; j < kBC; ++j) win[i][j] = 0.f;
 
     const uint32_t* p = reinterpret_cast<const uint32_t*>(src);
     const int pitch_w = pitch >> 2;  // pitch is a multiple of 32
     // software pipeline: the words of source rows r+1 and r+2 are in flight while row r is filtered
     // (the pointer stops at the last apron row, so the tail re-reads that row instead of running on)
-    uint32_t qa[2], qb[2], qc[2];
+    uint32_t q[2][kBW];
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
-        qa[i] = __ldg(p);
-        qb[i] = __ldg(p + 1);
-        qc[i] = __ldg(p + 2);
+#pragma unroll
+        for (int k = 0; k < kBW; ++k) q[i][k] = __ldg(p + k);
         if (i < last_src) p += pitch_w;
     }
     int r = 0;
@@ -108,27 +110,19 @@ blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restr
     for (int g = 0; g < groups; ++g) {
 #pragma unroll
         for (int s = 0; s < 7; ++s, ++r) {
-            const uint32_t wa = qa[0], wb = qb[0], wc = qc[0];
-            qa[0] = qa[1];
-            qb[0] = qb[1];
-            qc[0] = qc[1];
-            qa[1] = __ldg(p);
-            qb[1] = __ldg(p + 1);
-            qc[1] = __ldg(p + 2);
-            if (r + 2 < last_src) p += pitch_w;  // never read below the apron
-            float f[10];
-            f[0] = byte_to_float(wa, 0x7541u);
-            f[1] = byte_to_float(wa, 0x7542u);
-            f[2] = byte_to_float(wa, 0x7543u);
-            f[3] = byte_to_float(wb, 0x7540u);
-            f[4] = byte_to_float(wb, 0x7541u);
-            f[5] = byte_to_float(wb, 0x7542u);
-            f[6] = byte_to_float(wb, 0x7543u);
-            f[7] = byte_to_float(wc, 0x7540u);
-            f[8] = byte_to_float(wc, 0x7541u);
-            f[9] = byte_to_float(wc, 0x7542u);
+            uint32_t w[kBW];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int k = 0; k < kBW; ++k) {
+                w[k] = q[0][k];
+                q[0][k] = q[1][k];
+                q[1][k] = __ldg(p + k);
+            }
+            if (r + 2 < last_src) p += pitch_w;  // never read below the apron
+            float f[kBF];
+#pragma unroll
+            for (int i = 0; i < kBF; ++i) f[i] = byte_to_float(w[(i + 1) >> 2], 0x7540u + (uint32_t)((i + 1) & 3));
+#pragma unroll
+            for (int j = 0; j < kBC; ++j) {
                 float acc = __fmul_rn(gk.k[0], f[j]);
 #pragma unroll
                 for (int t = 1; t < 7; ++t) acc = __fmaf_rn(f[j + t], gk.k[t], acc);
@@ -137,9 +131,9 @@ blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restr
             // rows r-6 .. r are in win[(s+1)%7] .. win[s]; the output row is r - 6
             const int o = r - 6;
             if (o >= 0 && o < rows_out) {
-                uint32_t t4[4];
+                uint32_t t4[kBC];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < kBC; ++j) {
                     float acc = __fmul_rn(gk.k[3], win[(s + 4) % 7][j]);
                     acc = __fmaf_rn(__fadd_rn(win[(s + 3) % 7][j], win[(s + 5) % 7][j]), gk.k[4], acc);
                     acc = __fmaf_rn(__fadd_rn(win[(s + 2) % 7][j], win[(s + 6) % 7][j]), gk.k[5], acc);
@@ -147,8 +141,17 @@ blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restr
                     // 0 <= acc <= 255.001: adding 1.5 * 2^23 leaves round-half-even(acc) in the low byte
                     t4[j] = __float_as_uint(__fadd_rn(acc, 12582912.0f));
                 }
-                const uint32_t lo = __byte_perm(t4[0], t4[1], 0x0040u), hi = __byte_perm(t4[2], t4[3], 0x0040u);
-                *reinterpret_cast<uint32_t*>(dst) = __byte_perm(lo, hi, 0x5410u);
+                uint32_t outw[kBC / 4];
+#pragma unroll
+                for (int k = 0; k < kBC / 4; ++k) {
+                    const uint32_t lo = __byte_perm(t4[4 * k], t4[4 * k + 1], 0x0040u);
+                    const uint32_t hi = __byte_perm(t4[4 * k + 2], t4[4 * k + 3], 0x0040u);
+                    outw[k] = __byte_perm(lo, hi, 0x5410u);
+                }
+                if (kBC == 8)
+                    *reinterpret_cast<uint2*>(dst) = make_uint2(outw[0], outw[kBC / 4 - 1]);
+                else
+                    *reinterpret_cast<uint32_t*>(dst) = outw[0];
             }
             dst += pitch;
         }

@@ -52,6 +52,11 @@ constexpr int kApronRight = 12;
 #define VXORB_BLUR_ROWS 64
 #endif
 constexpr int kBlurRows = VXORB_BLUR_ROWS;    // output rows per blur strip
+#ifndef VXORB_BLUR_COLS
+#define VXORB_BLUR_COLS 4
+#endif
+constexpr int kBlurCols = VXORB_BLUR_COLS;    // columns per blur strip (one thread): 4 or 8
+static_assert(kBlurCols == 4 || kBlurCols == 8, "blur strips are 4 or 8 columns wide");
 
 // FAST tiling (fast.cu): a CTA computes scores for kFastScoreW x kFastScoreH pixels and emits corners
 // from the inner kFastEmitW x kFastEmitH; tile origins are multiples of 4 px in x.
@@ -90,7 +95,7 @@ struct LevelTab {
     unsigned long long fin_off[kMaxLevels];
     // tile bookkeeping: tiles of level l are [tile_begin[l], tile_begin[l+1]) in blockIdx.x
     int fast_tiles_x[kMaxLevels], fast_tile_begin[kMaxLevels + 1];
-    // blur strips: blur_tiles_x = 4-px words per row; CTAs of level l are [blur_tile_begin[l], [l+1])
+    // blur strips: blur_tiles_x = strips of kBlurCols px per row; CTAs of level l are [blur_tile_begin[l], [l+1])
     int blur_tiles_x[kMaxLevels], blur_tile_begin[kMaxLevels + 1];
     int coef_off[kMaxLevels];        // offset (in u32) of level l's resize tables: x[w_l] then y[h_l]
     int resize_fast[kMaxLevels];     // level l's x taps fit the register-resident resize kernel
