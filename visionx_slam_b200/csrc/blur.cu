@@ -11,15 +11,15 @@
 // columns x kBlurRows output rows and walks down the source rows:
 //   * per source row: three aligned 32-bit loads (columns x0-4 .. x0+7; the reflect-101 apron
 //     written by apron_kernel makes the border a plain read), ten byte->float conversions
-//     (PRMT into 0x4B0000bb, then subtract 2^23: exact), 4 x 7 row-pass FMAs;
+//     (I2F.U8 with a byte selector, on the conversion unit), 4 x 7 row-pass FMAs with the taps as immediates;
 //   * the last seven row-pass rows live in registers (window rotated by unrolling x7);
 //   * per output row: 4 x 7 column-pass ops, round-half-even by adding 1.5*2^23, pack, one
 //     32-bit store.  Consecutive lanes own consecutive words, so loads and stores coalesce.
 // Strips are enumerated per level (band-major, then word) and dealt to threads linearly, so lane
 // utilisation does not depend on the level width.
 // Roofline: HBM, algorithmic bytes = read + write of every level pixel (1 901 064 B per 640x480);
-// the kernel is bound by the FP32 (fma) pipe: 17.5 FP operations per pixel (2.5 conversions, 7 row, 8
-// column) at 16 lanes x 4 SMSPs per SM put the floor at 0.114 ms per 128 frames; measured 0.146.
+// the kernel is bound by instruction issue (79 % of the issue slots, fma pipe 47 %): 15 FP operations, 2.5
+// conversions and ~5.5 load / store / address / predicate instructions per pixel; 0.131 ms per 128 frames.
 // Packed fma.rn.f32x2 / add.f32x2 (FFMA2 / FADD2) were tried: 25 % fewer instructions, bit-identical
 // output, same time — the fma pipe spends two passes on a packed instruction.
 #include <math.h>

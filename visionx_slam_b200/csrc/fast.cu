@@ -9,11 +9,12 @@
 //
 // Persistent CTAs (8 warps) walk over tiles whose score region is 128 x 48 px (emission region: the
 // inner 124 x 46); the level pixels a tile needs sit in shared memory as 32-bit words and the score
-// map never leaves shared memory.  Warp w owns score rows w, w + 8, ... of the tile from the first
+// map never leaves shared memory.  Warp w owns one row of every group of eight score rows (row w ^ i of group i,
+// so its six rows sit in six different bank groups of the 176-byte-pitch tile buffer) from the first
 // test to the emission, so a tile costs ONE CTA barrier (between scoring and NMS, which reads the
 // neighbouring rows other warps scored); score maps and tile buffers are double buffered.
 //   load    one TMA box per tile (cp.async.bulk.tensor.3d over a per-level {pitch, rows, frame}
-//           tensor map: 54 rows x 160 B = 3-row ring halo, halo words left and right, 16 B aligned start),
+//           tensor map: 54 rows x 176 B = 3-row ring halo, halo words left and right, 16 B aligned start),
 //           issued two tiles ahead right after the barrier that frees the buffer and completed
 //           through an mbarrier; pixels outside the plane are zero-filled by the TMA unit and are
 //           never part of a valid ring

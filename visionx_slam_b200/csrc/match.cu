@@ -1,4 +1,4 @@
-// match.cu — Hamming 2-NN (brute force or square-window masked), ratio test, cross-check and the
+// match.cu — Hamming 2-NN (brute force, square-window, box or byte masked), ratio test, cross-check and the
 // caller's post-filter, for a batch of independent (query, train) descriptor sets.
 //
 // Replaces cv::BFMatcher(cv::NORM_HAMMING).knnMatch(desc_last, desc_curr, knn, 2)
@@ -8,9 +8,10 @@
 //
 // knn kernel: one thread owns one query descriptor (8 x u32 in registers); the CTA streams the
 // train set through shared memory in 256-row tiles which every thread reads as broadcast 16-byte
-// vectors; per pair: 8 XOR + 8 POPC + 7 IADD, then the packed key (dist << 20 | idx) goes through a
-// 3-instruction min/max top-2 update.  Bound: integer/popcount issue rate, not HBM (64 KB of
-// descriptors per 1000x1000 pair).  compact kernel: one CTA per pair, ordered block scan.
+// vectors; per pair: 8 XOR + 4 carry-save adders (8 LOP3) + 4 POPC + 4 IMAD that assemble the packed key
+// (dist * kKeyMul + idx), then a top-2 update of 2.5 min/max operations (two rows at a time).  Bound: the integer
+// (alu) pipe, 80 % busy — not HBM (64 KB of descriptors per 1000x1000 pair).  Windowed / box masks over more than a
+// few pairs go through the cell-binned kernel below.  compact kernel: one CTA per pair, ordered block scan.
 #include <algorithm>
 
 #include "vxorb_internal.h"
