@@ -411,6 +411,39 @@ def test_track_sequence_chunks(radius):
         assert np.array_equal(matches_as_rows(again[1][2]), matches_as_rows(ref[5][2]))
 
 
+def test_track_tie_tails():
+    """Response ties push the keypoint count above n_features (cv::ORB keeps every tie): the streaming path copies
+    only the first n_features rows of every frame with the chunk and fetches such tails in vxorb_track_wait —
+    keypoints, descriptors, matches and matched points beyond row n_features must still arrive."""
+    rng = np.random.default_rng(5)
+    patch = rng.integers(0, 256, (14, 14)).astype(np.uint8)
+    img = np.full((240, 320), 128, np.uint8)
+    for y in range(36, 190, 24):
+        for x in range(36, 270, 24):
+            img[y:y + 14, x:x + 14] = patch        # identical copies: identical scores and responses
+    frames = np.stack([img, np.roll(img, 2, axis=1), np.roll(img, 4, axis=1)])
+    for n_features, n_levels in ((50, 1), (100, 2)):
+        ext = [oracle.orb_extract(f, n_features, 1.2, n_levels) for f in frames]
+        assert min(len(k) for k, _ in ext) > n_features  # the tails exist
+        with vx.VxOrb(n_features=n_features, n_levels=n_levels, max_width=320, max_height=240, max_batch=3) as hx:
+            assert hx.kp_cap >= max(len(k) for k, _ in ext)
+            for radius in (0.0, 16.0):
+                hx.track_reset()
+                got = hx.track_info(frames, radius)
+                prev = None
+                for i, ((kp, desc, m, info, pts), (okp, odesc)) in enumerate(zip(got, ext)):
+                    assert_kp_equal(kp, okp)
+                    assert np.array_equal(desc, odesc)
+                    if prev is not None:
+                        pk, pd = prev
+                        qxy, txy = np.stack([pk["x"], pk["y"]], 1), np.stack([okp["x"], okp["y"]], 1)
+                        om = oracle.match(pd, odesc, 0.8, qxy if radius > 0 else None, txy if radius > 0 else None, radius)
+                        assert np.array_equal(matches_as_rows(m), matches_as_rows(om)), f"frame {i} radius {radius}"
+                        opts, _ = oracle.correspondences(qxy, txy, om)
+                        assert np.array_equal(pts, opts)
+                    prev = (okp, odesc)
+
+
 def test_track_bgr_chunks():
     """Colour chunks through the streaming path (what System::Run feeds, system.cpp:46): converted on the device,
     then identical to streaming the oracle's gray conversion; a strided (padded-row) chunk gives the same."""
