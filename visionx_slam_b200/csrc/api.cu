@@ -68,6 +68,7 @@ constexpr int kRing = 8;
 constexpr long long kFirstSetId = 1LL << 40;  // frame ids count up from 1, uploaded sets from here
 struct ResidentSet {
     long long id = 0;             // 0 = empty
+    uint8_t* block = nullptr;     // ring entries: header | kp rows | desc rows in one allocation (n, kp, desc point into it)
     vxorb_keypoint* kp = nullptr; // ring entries only
     uint8_t* desc = nullptr;
     float* xy = nullptr;          // level-0 positions (nullptr for an uploaded set without positions)
@@ -103,6 +104,7 @@ struct vxorb_handle {
     float *m_qxy = nullptr, *m_txy = nullptr;
     int* m_n = nullptr;  // [0] = nq, [1] = nt
     vxorb_knn2_t *m_knn = nullptr, *m_back = nullptr;
+    uint8_t* m_out_blk = nullptr;  // m_out_n (header) and m_out (rows) live in this allocation
     vxorb_match_t* m_out = nullptr;
     uint2* m_part = nullptr;  // per-split partial top-2 keys of the single-pair brute-force launch
     uint8_t* m_mask = nullptr;  // nq x nt byte mask of vxorb_knn2_masked / vxorb_match_masked
@@ -464,12 +466,16 @@ int launch_extract_graph(vxorb_handle* h, Workspace& ws, ResidentSet& rs) {
 int ensure_ring(vxorb_handle* h) {
     if (h->ring_ready) return VXORB_OK;
     const size_t cap = (size_t)h->kp_cap;
+    // one block per entry, laid out like the pinned staging block of the synchronous extract call — 64-byte header
+    // (rows written, true count), keypoint rows, descriptor rows — so the whole result is ONE device-to-host copy
+    const size_t kp_bytes = align_up(sizeof(vxorb_keypoint) * cap, 64);
     for (auto& r : h->ring) {
-        CK(cudaMalloc(&r.kp, sizeof(vxorb_keypoint) * cap));
-        CK(cudaMalloc(&r.desc, 32 * cap));
+        CK(cudaMalloc(&r.block, 64 + kp_bytes + 32 * cap));
+        CK(cudaMemset(r.block, 0, 64));
+        r.n = reinterpret_cast<int*>(r.block);
+        r.kp = reinterpret_cast<vxorb_keypoint*>(r.block + 64);
+        r.desc = r.block + 64 + kp_bytes;
         CK(cudaMalloc(&r.xy, 8 * cap));
-        CK(cudaMalloc(&r.n, sizeof(int) * 2));
-        CK(cudaMemset(r.n, 0, sizeof(int) * 2));
     }
     h->ring_ready = true;
     return VXORB_OK;
@@ -646,7 +652,14 @@ int check_status(vxorb_handle* h, int status) {
 int ensure_match_scratch(vxorb_handle* h, int rows) {
     if (rows <= h->m_cap) return VXORB_OK;
     cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);
-    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n); cudaFree(h->m_part);
+    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out_blk); cudaFree(h->m_part);
+    h->m_q = h->m_t = nullptr;
+    h->m_qxy = h->m_txy = nullptr;
+    h->m_n = nullptr;
+    h->m_knn = h->m_back = nullptr;
+    h->m_out_blk = nullptr;
+    h->m_out = nullptr;
+    h->m_out_n = nullptr;
     h->m_part = nullptr;
     h->m_cap = 0;
     const size_t r = (size_t)rows;
@@ -657,8 +670,10 @@ int ensure_match_scratch(vxorb_handle* h, int rows) {
     CK(cudaMalloc(&h->m_n, sizeof(int) * 4));
     CK(cudaMalloc(&h->m_knn, sizeof(vxorb_knn2_t) * r));
     CK(cudaMalloc(&h->m_back, sizeof(vxorb_knn2_t) * r));
-    CK(cudaMalloc(&h->m_out, sizeof(vxorb_match_t) * r));
-    CK(cudaMalloc(&h->m_out_n, sizeof(int) * 4));
+    // count (64-byte header) and rows in one block: the read-back of a match call is one copy
+    CK(cudaMalloc(&h->m_out_blk, 64 + sizeof(vxorb_match_t) * r));
+    h->m_out_n = reinterpret_cast<int*>(h->m_out_blk);
+    h->m_out = reinterpret_cast<vxorb_match_t*>(h->m_out_blk + 64);
     CK(cudaMalloc(&h->m_part, sizeof(uint2) * r * kMaxTrainSplits));
     h->m_cap = rows;
     return VXORB_OK;
@@ -739,8 +754,7 @@ int finish_match(vxorb_handle* h, const DevSet& q, float nn_ratio, int mode, int
     if (rc) return rc;
     int* n_st = reinterpret_cast<int*>(h->x_stage);
     vxorb_match_t* out_st = reinterpret_cast<vxorb_match_t*>(h->x_stage + 64);
-    CK(cudaMemcpyAsync(n_st, h->m_out_n, sizeof(int), cudaMemcpyDeviceToHost, s));
-    if (rows > 0) CK(cudaMemcpyAsync(out_st, h->m_out, sizeof(vxorb_match_t) * (size_t)rows, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(n_st, h->m_out_blk, need, cudaMemcpyDeviceToHost, s));  // header + rows, one copy
     CK(cudaStreamSynchronize(s));
     const int n = *n_st;
     *n_out = n;
@@ -933,13 +947,13 @@ void vxorb_destroy(vxorb_handle* h) {
         if (w.h_counts) cudaFreeHost(w.h_counts);
     }
     for (auto& r : h->ring) {
-        cudaFree(r.kp); cudaFree(r.desc); cudaFree(r.xy); cudaFree(r.n);
+        cudaFree(r.block); cudaFree(r.xy);
     }
     for (auto& kv : h->sets) {
         cudaFree(kv.second.desc); cudaFree(kv.second.xy); cudaFree(kv.second.n);
     }
     cudaFree(h->m_q); cudaFree(h->m_t); cudaFree(h->m_qxy); cudaFree(h->m_txy); cudaFree(h->m_n);
-    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out); cudaFree(h->m_out_n); cudaFree(h->m_part);
+    cudaFree(h->m_knn); cudaFree(h->m_back); cudaFree(h->m_out_blk); cudaFree(h->m_part);
     cudaFree(h->s_a); cudaFree(h->s_b); cudaFree(h->flush_buf); cudaFree(h->m_mask);
     if (h->x_stage) cudaFreeHost(h->x_stage);
     for (auto& sp : h->spans) {
@@ -1047,10 +1061,15 @@ static int extract_common(vxorb_handle* h, const uint8_t* const* frames, const u
     int* counts = reinterpret_cast<int*>(h->x_stage);
     vxorb_keypoint* st_kp = reinterpret_cast<vxorb_keypoint*>(h->x_stage + kp_off);
     uint8_t* st_desc = h->x_stage + desc_off;
-    CK(cudaMemcpyAsync(counts, d_n, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
-    CK(cudaMemcpyAsync(counts + batch, d_total, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
+    const bool one_copy = rs != nullptr && rows == h->kp_cap;  // the ring entry has the staging block's layout
+    if (one_copy) {
+        CK(cudaMemcpyAsync(h->x_stage, rs->block, need, cudaMemcpyDeviceToHost, ws.stream));
+    } else {
+        CK(cudaMemcpyAsync(counts, d_n, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
+        CK(cudaMemcpyAsync(counts + batch, d_total, sizeof(int) * batch, cudaMemcpyDeviceToHost, ws.stream));
+    }
     CK(cudaMemcpyAsync(counts + 2 * batch, ws.db.status, sizeof(int) * 4, cudaMemcpyDeviceToHost, ws.stream));
-    if (rows > 0) {
+    if (rows > 0 && !one_copy) {
         // frame f's rows sit h->kp_cap rows apart on the device, `rows` apart in the staging block
         CK(cudaMemcpy2DAsync(st_kp, sizeof(vxorb_keypoint) * (size_t)rows, d_kp,
                              sizeof(vxorb_keypoint) * (size_t)h->kp_cap, sizeof(vxorb_keypoint) * (size_t)rows, batch,
