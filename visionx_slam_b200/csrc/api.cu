@@ -367,26 +367,24 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch, const ResidentSet
     // the issue slots FAST's barriers and select's tails leave idle.  Instrumented runs stay serial so a
     // stage's events bracket that stage alone.
     const bool overlap = !h->stage_enabled && ws.side != nullptr && !h->no_overlap;
-    // Level 0's reflect apron is read by FAST and the blur, not by the resampling: for a few frames (where the
-    // level chain is the critical path) it is built on the side stream while the chain already runs.  Large
-    // batches keep it in line: there it only takes SMs from the first resize level (A/B: -0.7 % resident).
+    // The reflect apron of the planes is read by the blur alone (FAST's tiles take it in but never score a ring that
+    // touches it; the resampling, Harris and the descriptor windows stay inside the image).  For a few frames, where
+    // the level chain is the critical path of the call, the level kernels therefore skip their apron phase and the
+    // aprons of all levels are built on the side stream just before the blur, beside FAST + select.  Large batches
+    // keep them in the band kernels (a separate pass over the planes costs more than it hides there).
     const bool apron_aside = overlap && lt.resize_band && batch < 8;
-    if (apron_aside) {
-        CK(cudaEventRecord(ws.ev_fork0, s));
-        CK(cudaStreamWaitEvent(ws.side, ws.ev_fork0, 0));
-        const int n = launch_apron(lt, d, 1, ws.side);
-        h->launches += n;
-        h->stage_launches[VXORB_STAGE_PYRAMID] += n;
-        CK(cudaEventRecord(ws.ev_apron, ws.side));
-    }
     {
         StageScope sc(h, s, VXORB_STAGE_PYRAMID);
         sc.end(launch_pyramid(lt, d, s, !apron_aside));
     }
-    if (apron_aside) CK(cudaStreamWaitEvent(s, ws.ev_apron, 0));
     if (overlap) {
         CK(cudaEventRecord(ws.ev_fork, s));
         CK(cudaStreamWaitEvent(ws.side, ws.ev_fork, 0));
+        if (apron_aside) {
+            const int na = launch_apron(lt, d, lt.n_levels, ws.side);
+            h->launches += na;
+            h->stage_launches[VXORB_STAGE_PYRAMID] += na;
+        }
         const int n = launch_blur(lt, d, ws.side);
         h->launches += n;
         h->stage_launches[VXORB_STAGE_BLUR] += n;

@@ -259,7 +259,7 @@ __global__ void __launch_bounds__(256)
 resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, size_t sfstride,
                    uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
                    const uint32_t* __restrict__ ytab, const uint4* __restrict__ xw4, const uint2* __restrict__ xw2,
-                   int words, int band_rows, int n_bands, int pairs_par) {
+                   int words, int band_rows, int n_bands, int pairs_par, int write_apron) {
     extern __shared__ __align__(128) uint8_t rows_sm[];
     __shared__ __align__(8) unsigned long long bar;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -426,6 +426,10 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
             row_out(min(y + 1, y_end - 1), has_word && y + 1 < y_end);
         }
     }
+    // A few frames: the apron is only read by the blur, which runs on the side stream — the caller builds it there
+    // (apron_kernel) and the level chain, the critical path of a single-frame call, does not pay for reading its own
+    // pixels back twice per level.
+    if (!write_apron) return;
     __syncthreads();  // the band's pixels are visible to this CTA
 
     // reflect-101 apron, left / right: x = -1,-2,-3 <- 1,2,3 ; x = w,w+1,w+2 <- w-2,w-3,w-4
@@ -537,12 +541,12 @@ bool plan_resize_bands(const uint32_t* ytaps, int dh, int sh, int spitch, int* b
 // rows == 16 selects the throughput shape, 8 / 4 the latency shape.
 void launch_resize_band(const uint8_t* src_plane, int sh, int spitch, size_t sfstride, uint8_t* dst, int dw, int dh,
                         int dpitch, size_t dfstride, const uint32_t* ytab, const uint4* xw4, const uint2* xw2, int rows,
-                        int n_bands, int smem, int batch, cudaStream_t s) {
+                        int n_bands, int smem, int batch, cudaStream_t s, bool write_apron) {
     const int words = (dw + 3) / 4;
     dim3 grid(n_bands, batch);
     auto kern = rows == 16 ? resize_band_kernel<true> : resize_band_kernel<false>;
     kern<<<grid, 256, smem, s>>>(src_plane, sh, spitch, sfstride, dst, dw, dh, dpitch, dfstride, ytab, xw4, xw2, words, rows,
-                                 n_bands, rows / 2);
+                                 n_bands, rows / 2, write_apron ? 1 : 0);
 }
 
 cudaError_t init_pyramid_kernels() {
@@ -552,8 +556,11 @@ cudaError_t init_pyramid_kernels() {
 }
 
 // Builds levels 1.. of every frame and the reflect-101 apron of every level.  Returns launches.
-int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, bool level0_apron) {
+int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, bool aprons_inline) {
     int launches = 0;
+    // aprons_inline == false (only for fewer than 8 frames on the band path): the caller builds the apron of EVERY level
+    // itself (launch_apron over all levels, beside the chain's consumers that do not read it)
+    const bool level0_apron = aprons_inline;
     if (lt.resize_band) {
         // level 0 comes from the upload; the bands write their own apron.  The resampling reads no apron byte of
         // its source, so a caller may build level 0's apron elsewhere (beside the chain) and pass false.
@@ -572,7 +579,7 @@ int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, 
             const int nb = small ? std::max(1, lt.h[l] / 4) : lt.n_bands[l];
             launch_resize_band(src_plane, lt.h[l - 1], lt.pitch[l - 1], (size_t)lt.fstride[l - 1], db.pyr + lt.off[l], lt.w[l],
                                lt.h[l], lt.pitch[l], (size_t)lt.fstride[l], tab + lt.w[l], xw4, xw2, rows, nb, lt.band_smem[l],
-                               lt.batch, s);
+                               lt.batch, s, aprons_inline || lt.batch >= 8);
             ++launches;
         }
         return launches;

@@ -133,7 +133,7 @@ int launch_gray_from_bgr(const uint8_t* bgr, size_t bgr_pitch, size_t bgr_fstrid
 // w must be a multiple of 16; src holds `batch` frames of w*h bytes back to back (16 B aligned)
 int launch_unpack_frames(const uint8_t* src, uint8_t* dst, int w, int h, int pitch, size_t fstride, int batch,
                          cudaStream_t s);
-int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, bool level0_apron = true);
+int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, bool aprons_inline = true);
 int launch_resize_single(const uint8_t* src, int sw, int sh, int spitch, uint8_t* dst, int dw, int dh,
                          int dpitch, const uint32_t* xtab, const uint32_t* ytab, bool fast, cudaStream_t s);
 bool resize_taps_fit_fast_path(const uint32_t* xtaps, int dw);
@@ -144,7 +144,7 @@ void resize_band_extent(const uint32_t* ytaps, int dh, int sh, int spitch, int r
 // src_plane = start of the source plane allocation (apron included); rows 16 = throughput shape, 8 / 4 = latency shape
 void launch_resize_band(const uint8_t* src_plane, int sh, int spitch, size_t sfstride, uint8_t* dst, int dw, int dh,
                         int dpitch, size_t dfstride, const uint32_t* ytab, const uint4* xw4, const uint2* xw2, int rows,
-                        int n_bands, int smem, int batch, cudaStream_t s);
+                        int n_bands, int smem, int batch, cudaStream_t s, bool write_apron = true);
 cudaError_t init_pyramid_kernels();
 int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s);
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
