@@ -21,7 +21,6 @@ namespace vxorb {
 
 namespace {
 
-constexpr int kThreads = 256;
 constexpr int kSortCap = 2048;
 
 __device__ __forceinline__ uint32_t float_key(float v) {
@@ -141,7 +140,10 @@ __device__ __forceinline__ void top_bin_scan(const int* hist, int k, int lane, i
 #ifndef VXORB_SELECT_CTAS
 #define VXORB_SELECT_CTAS 4
 #endif
-__global__ void __launch_bounds__(kThreads, VXORB_SELECT_CTAS)
+// kThreads = 256 (4 CTAs per SM) for batches; 1024 for a few frames, where the eight CTAs of a frame are alone on the GPU
+// and the level-0 CTA's loops over ~2400 candidates are the critical path of the call.
+template <int kThreads>
+__global__ void __launch_bounds__(kThreads, kThreads == 256 ? VXORB_SELECT_CTAS : 1)
 select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t* __restrict__ cand,
               const int* __restrict__ cand_n, float* __restrict__ resp, uint32_t* __restrict__ fin_key,
               float* __restrict__ fin_resp, int* __restrict__ fin_n, int* __restrict__ status) {
@@ -173,7 +175,7 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
     const uint8_t* img = pyr + lt.off[l] + (size_t)f * lt.fstride[l];
 
     // ---- step 1: retainBest(2q) on the FAST score ---------------------------------------------
-    hist[tid] = 0;
+    if (tid < 256) hist[tid] = 0;
     if (tid == 0) {
         s_thr1 = 0;
         s_ns = n;
@@ -233,7 +235,7 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
         }
         uint32_t mask = 0;
         for (int pass = 3; pass >= 0; --pass) {
-            hist[tid] = 0;
+            if (tid < 256) hist[tid] = 0;
             __syncthreads();
             const uint32_t prefix = s_prefix;
             if (listed) {
@@ -345,7 +347,12 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
 
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
     dim3 grid(lt.batch, lt.n_levels);
-    select_kernel<<<grid, kThreads, 0, s>>>(lt, db.pyr, db.cand, db.cand_n, db.resp, db.fin_key, db.fin_resp,
+    if (lt.batch < 8) {
+        select_kernel<1024><<<grid, 1024, 0, s>>>(lt, db.pyr, db.cand, db.cand_n, db.resp, db.fin_key, db.fin_resp, db.fin_n,
+                                                   db.status);
+        return 1;
+    }
+    select_kernel<256><<<grid, 256, 0, s>>>(lt, db.pyr, db.cand, db.cand_n, db.resp, db.fin_key, db.fin_resp,
                                            db.fin_n, db.status);
     return 1;
 }
