@@ -20,8 +20,14 @@ namespace vxorb {
 
 namespace {
 
-constexpr int kQPerBlock = 128;
-constexpr int kTrainTile = 256;
+#ifndef VXORB_KNN_QPB
+#define VXORB_KNN_QPB 128
+#endif
+#ifndef VXORB_KNN_TILE
+#define VXORB_KNN_TILE 256
+#endif
+constexpr int kQPerBlock = VXORB_KNN_QPB;   // queries (threads) per CTA
+constexpr int kTrainTile = VXORB_KNN_TILE;  // train rows staged in shared memory at a time
 constexpr uint32_t kNoKey = 0x7fffffffu;
 // Packed 2-NN key of the brute-force kernels: distance * kKeyMul + train index, ordered like the pair (distance,
 // index), so ties go to the lowest index.  kKeyMul is 2^20 + 1 rather than 2^20: with a power of two ptxas turns
