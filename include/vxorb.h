@@ -194,6 +194,19 @@ int vxorb_match_masked(vxorb_handle* h, const uint8_t* query, int nq, const uint
                        const uint8_t* mask, size_t mask_stride, float nn_ratio, int out_cap, vxorb_match_t* out,
                        int* n_out);
 
+/* vxorb_knn2 for callers that may not allocate.  No counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same rows
+ * as vxorb_knn2 (brute force, ties to the lowest train index), host buffers in and out, no handle.  The device staging
+ * and the kernel's partial-key scratch live in one static __device__ array (~1.7 MiB, held by every GPU that loads
+ * the library until the process exits); the call runs on the current device's default stream and calls no cudaMalloc,
+ * cudaFree or allocating library routine.  Limits: nq <= VXORB_STATIC_MAX_QUERY and nt <= VXORB_STATIC_MAX_TRAIN,
+ * beyond which it returns VXORB_E_INVALID with the limits spelled out in `err` (NUL-terminated, at most err_cap
+ * bytes; err may be NULL).  All calls share the array: calls that overlap on one GPU race, so serialise them. */
+#define VXORB_STATIC_MAX_QUERY 4096
+#define VXORB_STATIC_MAX_TRAIN 16384
+int vxorb_knn2_static(const uint8_t* query, int nq, const uint8_t* train, int nt, vxorb_knn2_t* knn_out,
+                      char* err, size_t err_cap);
+
 /* cv::BFMatcher(NORM_HAMMING, crossCheck=true).match: (i, j) kept iff j is i's nearest train
  * row and i is j's nearest query row, both with lowest-index tie-break. */
 int vxorb_match_crosscheck(vxorb_handle* h, const uint8_t* query, int nq, const uint8_t* train,

@@ -76,6 +76,7 @@ _SYMBOLS = [
     ("vxorb_match_boxed", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _f, _i, _vp, _vp]),
     ("vxorb_knn2_masked", _i, [_vp, _vp, _i, _vp, _i, _vp, _sz, _vp]),
     ("vxorb_match_masked", _i, [_vp, _vp, _i, _vp, _i, _vp, _sz, _f, _i, _vp, _vp]),
+    ("vxorb_knn2_static", _i, [_vp, _i, _vp, _i, _vp, _vp, _sz]),
     ("vxorb_depth_lookup", _i, [_vp, C.c_longlong, _vp, _i, _i, _i, _sz, _i, _vp, _vp]),
     ("vxorb_match_crosscheck", _i, [_vp, _vp, _i, _vp, _i, _i, _vp, _vp]),
     ("vxorb_match_filtered", _i, [_vp, _vp, _i, _vp, _i, _f, _i, _vp, _vp]),
@@ -141,6 +142,22 @@ def _desc(a):
 
 def _xy(a):
     return np.ascontiguousarray(a, dtype=np.float32).reshape(-1, 2)
+
+
+STATIC_MAX_QUERY, STATIC_MAX_TRAIN = 4096, 16384  # VXORB_STATIC_MAX_QUERY / _TRAIN of include/vxorb.h
+
+
+def knn2_static(q, t):
+    """vxorb_knn2_static: the rows of VxOrb.knn2 without a handle and without any allocation inside the call (the
+    scratch is a static device array of the library).  Raises VxOrbError with the library's text beyond the limits."""
+    lib = load_library()
+    q, t = _desc(q), _desc(t)
+    out = np.zeros(len(q), KNN2_DTYPE)
+    err = C.create_string_buffer(256)
+    rc = lib.vxorb_knn2_static(_ptr(q), len(q), _ptr(t), len(t), _ptr(out), C.addressof(err), len(err))
+    if rc != 0:
+        raise VxOrbError(rc, err.value.decode())
+    return out
 
 
 class PinnedArray:
