@@ -1,7 +1,7 @@
 // adapter_main.cpp — drives the C++ adapters the way the reference's front end does
 // (tracking.cpp:42 Extract on every frame; tracking.cpp:208 Match(init, current)).
 //
-//   adapter_main <in.bin> <out.bin>
+//   adapter_main <in.bin> <out.bin> [initial_max_side]
 // in.bin : int32 n_frames, w, h, channels; then n_frames * h * w * channels bytes
 // out.bin: per frame: int32 n; n * (double x, double y, float response); n * 32 descriptor bytes
 //          then per consecutive pair (i-1 -> i): int32 m; m * (int32 q, int32 t, float dist)
@@ -17,14 +17,16 @@
 using namespace visionx;
 
 int main(int argc, char** argv) {
-    if (argc != 3) return 2;
+    if (argc != 3 && argc != 4) return 2;
+    const int initial_max = argc == 4 ? atoi(argv[3]) : 0;  // > 0: start with a handle too small for the frames
     FILE* fi = fopen(argv[1], "rb");
     if (!fi) return 3;
     int hdr[4];
     if (fread(hdr, 4, 4, fi) != 4) return 3;
     const int n = hdr[0], w = hdr[1], h = hdr[2], ch = hdr[3];
     std::vector<unsigned char> pix((size_t)w * h * ch);
-    auto cuda_extractor = std::make_shared<CudaORBExtractor>();
+    auto cuda_extractor = initial_max > 0 ? std::make_shared<CudaORBExtractor>(1000, 1.2f, 8, 0, initial_max, initial_max)
+                                          : std::make_shared<CudaORBExtractor>();
     std::shared_ptr<FeatureExtractor> extractor = cuda_extractor;                                       // system.cpp:15
     std::shared_ptr<FeatureMatcher> matcher = std::make_shared<CudaORBMatcher>(cuda_extractor);         // system.cpp:16
     std::shared_ptr<FeatureMatcher> standalone = std::make_shared<CudaORBMatcher>();  // own handle: always uploads
@@ -95,6 +97,7 @@ int main(int argc, char** argv) {
             }
         }
     fclose(fo);
+    fprintf(stderr, "REBUILDS %d\n", cuda_extractor->rebuilds());
     fprintf(stderr, "MATCHPATH resident=%d upload=%d standalone_upload=%d\n", cm->resident_calls(), cm->upload_calls(),
             dynamic_cast<CudaORBMatcher*>(standalone.get())->upload_calls());
     return 0;

@@ -36,14 +36,15 @@ def test_adapters_derive_from_reference_interfaces():
     assert "int Match(const Frame::Ptr& last, const Frame::Ptr& curr, std::vector<cv::DMatch>& matches) override;" in m
 
 
-def _run_adapter(tmp_path, frames):
+def _run_adapter(tmp_path, frames, initial_max=None):
     n, hh, w = frames.shape[:3]
     ch = frames.shape[3] if frames.ndim == 4 else 1
     fin, fout = tmp_path / "in.bin", tmp_path / "out.bin"
     with open(fin, "wb") as f:
         f.write(struct.pack("<4i", n, w, hh, ch))
         f.write(np.ascontiguousarray(frames).tobytes())
-    r = subprocess.run([EXE, str(fin), str(fout)], capture_output=True, text=True, timeout=300)
+    cmd = [EXE, str(fin), str(fout)] + ([str(initial_max)] if initial_max else [])
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr
     buf = open(fout, "rb").read()
     pos = 0
@@ -138,3 +139,21 @@ def test_cpp_adapter_bgr(tmp_path):
     om = oracle.match(odesc, odesc2, 0.8)
     assert len(m_plain[0]) == len(om)
     assert ("Too few matches" in log) == (len(om) < 50)  # orb_matcher.cpp:38-40 warning kept
+
+
+@pytest.mark.gpu
+def test_cpp_adapter_grows_to_the_frame_size(tmp_path):
+    """cv::ORB takes frames of any size: an extractor built for 96 x 96 rebuilds its handle on the first 640 x 480
+    frame and then gives exactly what one built large enough gives, resident matching included."""
+    from visionx_slam_b200.synth import synth_sequence
+    _build()
+    frames = synth_sequence(640, 480, 3, seed=33)
+    feats, m_plain, m_filt, log = _run_adapter(tmp_path, frames)
+    feats2, m_plain2, m_filt2, log2 = _run_adapter(tmp_path, frames, initial_max=96)
+    assert "REBUILDS 0" in log and "REBUILDS 1" in log2
+    for (a, da), (b, db) in zip(feats, feats2):
+        assert len(a) > 900 and np.array_equal(a, b) and np.array_equal(da, db)
+    for a, b in zip(m_plain + m_filt, m_plain2 + m_filt2):
+        assert len(a) > 0 and np.array_equal(a, b)
+    path = [l for l in log2.splitlines() if l.startswith("MATCHPATH")][0]
+    assert "resident=4 upload=0" in path, path

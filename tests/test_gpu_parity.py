@@ -695,6 +695,35 @@ def test_reference_interface_flow_resident(golden_c1):
     assert np.array_equal(rows, g["matches"])
 
 
+def test_reference_interface_grows_to_the_frame_size(golden_c1):
+    """cv::ORB takes frames of any size: an extractor built for 96 x 96 rebuilds its handle on the first larger
+    frame; ids of the old handle are void (the pair straddling the rebuild takes the upload path), later pairs are
+    matched from the device again, and every result equals the golden one."""
+    g = golden_c1
+    small = np.ascontiguousarray(g["frame_a"][:90, :90])
+    extractor = vx.ORBExtractor(max_width=96, max_height=96)
+    matcher = vx.ORBMatcher(extractor=extractor)
+    tiny = vx.Frame(0, 0.0, small)
+    extractor.Extract(tiny)
+    assert extractor.rebuilds == 0
+    okp, odesc = oracle.orb_extract(small)
+    assert len(tiny.Features()) == len(okp) and np.array_equal(tiny.Descriptors(), odesc)
+    last, curr = vx.Frame(1, 0.1, g["frame_a"]), vx.Frame(2, 0.2, g["frame_b"])
+    extractor.Extract(last)
+    assert extractor.rebuilds == 1 and extractor.resident_id(tiny) == 0 and extractor.resident_id(last) != 0
+    extractor.Extract(curr)
+    assert extractor.rebuilds == 1
+    assert_kp_equal(last._keypoints, g["kp_a"])
+    assert np.array_equal(last.Descriptors(), g["desc_a"]) and np.array_equal(curr.Descriptors(), g["desc_b"])
+    matches = []
+    assert matcher.Match(last, curr, matches) == len(g["matches"]) and matcher.resident_calls == 1
+    rows = np.array([(m.queryIdx, m.trainIdx, int(m.distance)) for m in matches], np.int32)
+    assert np.array_equal(rows, g["matches"])
+    if len(odesc):  # the frame of the old handle is still matchable: its descriptors go up from the host
+        n = matcher.Match(tiny, curr, matches)
+        assert n == len(oracle.match(odesc, g["desc_b"], 0.8)) and matcher.upload_calls == 1
+
+
 def test_match_ids_vs_oracle(golden_c1):
     """vxorb_extract_id + vxorb_match_ids (ratio, post-filter, cross-check, window) and an uploaded map set."""
     g = golden_c1

@@ -674,21 +674,36 @@ class ORBExtractor:
     def __init__(self, n_features=1000, scale_factor=1.2, n_levels=8, **handle_kw):
         handle_kw.setdefault("max_width", 1920)
         handle_kw.setdefault("max_height", 1088)
-        self._vx = VxOrb(n_features=n_features, scale_factor=scale_factor, n_levels=n_levels, **handle_kw)
+        self._kw = dict(handle_kw, n_features=n_features, scale_factor=scale_factor, n_levels=n_levels)
+        self._vx = VxOrb(**self._kw)
+        self.rebuilds = 0  # handles rebuilt for frames beyond max_width x max_height (cv::ORB takes any size)
+
+    def _reserve(self, width, height):
+        if width <= self._kw["max_width"] and height <= self._kw["max_height"]:
+            return
+        kw = dict(self._kw, max_width=max(self._kw["max_width"], (width + 63) // 64 * 64),
+                  max_height=max(self._kw["max_height"], (height + 63) // 64 * 64))
+        bigger = VxOrb(**kw)  # raises, and keeps the old handle, if the device cannot hold it
+        self._vx.close()
+        self._vx, self._kw = bigger, kw
+        self.rebuilds += 1  # ids handed out by the old handle are void from here on
 
     def Extract(self, frame):
-        kp, desc, fid = self._vx.extract_id(frame.Image())
+        img = frame.Image()
+        self._reserve(img.shape[1], img.shape[0])
+        kp, desc, fid = self._vx.extract_id(img)
         feats = frame.Features()
         feats.clear()
         feats.extend(Feature(k["x"], k["y"], k["response"]) for k in kp)
         frame._descriptors = desc
         frame._keypoints = kp
-        frame._vx_id = fid  # the descriptors also stay on the device under this id (ring of 8 frames)
+        # the descriptors also stay on the device under this id (ring of 8 frames) of this generation of the handle
+        frame._vx_id = (self.rebuilds, fid)
 
     def resident_id(self, frame):
         """Device-resident id of the frame's descriptors, or 0 when they are no longer (or never were) there."""
-        fid = getattr(frame, "_vx_id", 0)
-        return fid if fid and self._vx.set_size(fid) == len(frame.Descriptors()) else 0
+        gen, fid = getattr(frame, "_vx_id", None) or (-1, 0)
+        return fid if fid and gen == self.rebuilds and self._vx.set_size(fid) == len(frame.Descriptors()) else 0
 
 
 class ORBMatcher:
@@ -704,10 +719,15 @@ class ORBMatcher:
         it left on the device (vxorb_match_ids); other descriptor arrays are uploaded."""
         self.options_ = options or ORBMatcher.Options()
         self._extractor = extractor
-        self._vx = extractor._vx if extractor is not None else VxOrb(
+        self._own = None if extractor is not None else VxOrb(
             nn_ratio=self.options_.nn_ratio, min_matches=self.options_.min_matches, **handle_kw)
         self.warnings = []
         self.resident_calls = self.upload_calls = 0
+
+    @property
+    def _vx(self):
+        # read per call: the extractor rebuilds its handle when a larger frame arrives
+        return self._extractor._vx if self._extractor is not None else self._own
 
     def Match(self, last, curr, matches):
         matches.clear()

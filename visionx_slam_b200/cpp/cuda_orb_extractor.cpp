@@ -4,6 +4,7 @@
 
 #include <glog/logging.h>
 
+#include <algorithm>
 #include <cstring>
 #include <stdexcept>
 
@@ -11,19 +12,45 @@ namespace visionx {
 
 CudaORBExtractor::CudaORBExtractor(int n_features, float scale_factor, int n_levels, int device_id,
                                    int max_width, int max_height) {
-    vxorb_params p;
-    vxorb_default_params(&p);
-    p.n_features = n_features;      // orb_extractor.cpp:6 cv::ORB::create(n_features, scale, levels)
-    p.scale_factor = scale_factor;
-    p.n_levels = n_levels;
-    p.device_id = device_id;
-    p.max_width = max_width;
-    p.max_height = max_height;
-    const int rc = vxorb_create(&p, &handle_);
+    vxorb_default_params(&params_);
+    params_.n_features = n_features;      // orb_extractor.cpp:6 cv::ORB::create(n_features, scale, levels)
+    params_.scale_factor = scale_factor;
+    params_.n_levels = n_levels;
+    params_.device_id = device_id;
+    params_.max_width = max_width;
+    params_.max_height = max_height;
+    const int rc = vxorb_create(&params_, &handle_);
     if (rc != VXORB_OK)
         throw std::runtime_error(std::string("CudaORBExtractor: vxorb_create failed: ") + vxorb_last_error(nullptr));
     kp_cap_ = vxorb_keypoint_capacity(handle_);
     kp_.resize(static_cast<size_t>(kp_cap_));
+}
+
+// cv::ORB takes frames of any size; a vxorb handle is sized at creation.  A frame beyond the current limits gets a
+// new, larger handle (limits rounded up to 64 px); the old one is destroyed only after the new one exists, and the
+// frames it kept resident are forgotten (a later Match of those frames uploads their descriptors instead).
+bool CudaORBExtractor::Reserve(int width, int height) {
+    if (width <= params_.max_width && height <= params_.max_height) return true;
+    vxorb_params p = params_;
+    p.max_width = std::max(p.max_width, (width + 63) / 64 * 64);
+    p.max_height = std::max(p.max_height, (height + 63) / 64 * 64);
+    vxorb_handle* bigger = nullptr;
+    if (vxorb_create(&p, &bigger) != VXORB_OK) {
+        last_error_ = std::string("cannot grow to ") + std::to_string(width) + "x" + std::to_string(height) + ": " +
+                      vxorb_last_error(nullptr);
+        return false;
+    }
+    LOG(INFO) << "[CudaORBExtractor] frame " << width << "x" << height << " exceeds " << params_.max_width << "x"
+              << params_.max_height << ": handle rebuilt for " << p.max_width << "x" << p.max_height;
+    vxorb_destroy(handle_);
+    handle_ = bigger;
+    params_ = p;
+    for (Resident& r : resident_) r = Resident{};
+    resident_next_ = 0;
+    kp_cap_ = vxorb_keypoint_capacity(handle_);
+    kp_.resize(static_cast<size_t>(kp_cap_));
+    ++rebuilds_;
+    return true;
 }
 
 CudaORBExtractor::~CudaORBExtractor() { vxorb_destroy(handle_); }
@@ -67,11 +94,13 @@ void CudaORBExtractor::Extract(Frame& frame) {
     auto& features = frame.Features();
     features.clear();  // orb_extractor.cpp:16
     const cv::Mat& image = frame.Image();
+    const bool usable = !image.empty() && image.depth() == CV_8U && (image.channels() == 1 || image.channels() == 3);
+    const bool fits = usable && Reserve(image.cols, image.rows);  // may replace handle_ and kp_cap_
     cv::Mat desc(kp_cap_, VXORB_DESC_BYTES, CV_8UC1);
     int n = 0;
     int rc = VXORB_E_INVALID;
     long long vx_id = 0;
-    if (!image.empty() && image.depth() == CV_8U && (image.channels() == 1 || image.channels() == 3)) {
+    if (fits) {
         // cv::ORB converts 3-channel input to gray itself; system.cpp:46 feeds IMREAD_COLOR frames
         rc = vxorb_extract_id(handle_, image.data, image.channels(), image.cols, image.rows,
                               static_cast<size_t>(image.step), kp_cap_, kp_.data(), desc.data, &n, &info_, &vx_id);
@@ -79,7 +108,8 @@ void CudaORBExtractor::Extract(Frame& frame) {
     if (rc != VXORB_OK && rc != VXORB_E_CAPACITY) info_ = vxorb_frame_info{};
     last_status_ = rc;
     if (rc != VXORB_OK && rc != VXORB_E_CAPACITY) {
-        last_error_ = image.empty() ? "empty or unsupported image" : vxorb_last_error(handle_);
+        if (!usable) last_error_ = "empty or unsupported image";
+        else if (fits) last_error_ = vxorb_last_error(handle_);  // else: Reserve left its message
         LOG(ERROR) << "[CudaORBExtractor] " << last_error_;
         frame.Descriptors() = cv::Mat();
         return;

@@ -47,7 +47,12 @@ public:
     const std::string& last_error() const { return last_error_; }
     // A CudaORBMatcher constructed with this extractor shares the handle (one device context, one set of
     // streams) and matches the descriptors Extract left on the device instead of uploading them again.
+    // The pointer changes when a frame larger than the current limits makes Extract rebuild the handle: read it per
+    // call, do not keep it.
     vxorb_handle* handle() const { return handle_; }
+    // Frames larger than max_width x max_height are accepted like cv::ORB accepts them: the handle is rebuilt for
+    // the larger size on the first such frame (a one-off cost of a few milliseconds).  Number of rebuilds so far:
+    int rebuilds() const { return rebuilds_; }
     // Device-resident id of the descriptors Extract produced for `frame` (vxorb_extract_id), or 0 when the
     // frame was not extracted here, has been overwritten (ring of 8 frames) or its descriptor matrix no longer
     // is what Extract wrote (row count and a fingerprint of the first and last rows are compared).
@@ -67,6 +72,9 @@ private:
         uint64_t fingerprint = 0;
     };
     static uint64_t Fingerprint(const cv::Mat& desc);
+    bool Reserve(int width, int height);
+    vxorb_params params_{};
+    int rebuilds_ = 0;
     Resident resident_[8];
     int resident_next_ = 0;
     vxorb_handle* handle_ = nullptr;

@@ -42,6 +42,7 @@ int CudaORBMatcher::Run(bool filtered, const Frame::Ptr& last, const Frame::Ptr&
     const cv::Mat t = desc2.isContinuous() ? desc2 : desc2.clone();
     buf_.resize(static_cast<size_t>(q.rows));
     int n = 0;
+    if (extractor_) handle_ = extractor_->handle();  // the extractor rebuilds its handle for larger frames
     const long long id_q = extractor_ ? extractor_->ResidentId(*last) : 0;
     const long long id_t = extractor_ ? extractor_->ResidentId(*curr) : 0;
     if (id_q != 0 && id_t != 0) {  // both descriptor sets are still on the device
