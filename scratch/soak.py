@@ -45,7 +45,13 @@ with vx.VxOrb(max_train=9000) as h:
         q = t[rng.integers(0, nt, nq)].copy(); q[:, int(rng.integers(0, 32))] ^= rng.integers(0, 16, nq).astype(np.uint8)
         qxy = (rng.uniform(0, 500, (nq, 2))).astype(np.float32); txy = (rng.uniform(0, 500, (nt, 2))).astype(np.float32)
         mode = case % 3
-        if mode == 0: a, o = h.knn2(q, t), oracle.knn2(q, t)
+        if mode == 0:
+            a, o = h.knn2(q, t), oracle.knn2(q, t)
+            if nq <= vx.STATIC_MAX_QUERY and nt <= vx.STATIC_MAX_TRAIN:  # the allocation-free entry point, same rows
+                st = vx.knn2_static(q, t)
+                if not (np.array_equal(st["idx"], o["idx"]) and np.array_equal(np.where(st["idx"] >= 0, st["dist"], 0), np.where(o["idx"] >= 0, o["dist"], 0))):
+                    bad += 1
+                    print("STATIC MISMATCH", case, nq, nt)
         elif mode == 1:
             r = float(rng.choice([8, 32, 100])); a, o = h.knn2(q, t, qxy, txy, r), oracle.knn2(q, t, qxy, txy, r)
         else:
