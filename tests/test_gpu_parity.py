@@ -58,15 +58,33 @@ def test_resize_band_stage(h, shape, dst, band_rows):
     assert np.array_equal(got, oracle.resize_linear_exact(src, dst[1], dst[0]))
 
 
-def test_pyramid_chain_golden(h, golden_c1):
+BLUR_MARGIN = 13  # kBlurMargin: edge threshold 31 - descriptor window reach 18
+
+
+def _interior(img, m=BLUR_MARGIN):
+    return img[m:img.shape[0] - m, m:img.shape[1] - m]
+
+
+def test_pyramid_chain_golden(h, golden_c1, monkeypatch):
+    """cv2's pyramid levels and blurred levels of the C1 frame.  The production path blurs only what a descriptor
+    window can read (BLUR_MARGIN px inside every level); VXORB_FULL_BLUR=1 makes a handle blur whole levels from
+    aproned planes — the same kernel — so that cv2's whole-level hashes can be checked, and the interior of the
+    production planes must equal the interior of those."""
     g = golden_c1
     a = g["frame_a"]
     h.extract(a)
-    for l in range(8):
-        lvl = h.debug_level(0, l, 640, 480)
-        assert sha256(lvl) == str(g[f"a_level{l}_sha"]), f"pyramid level {l}"
-        bl = h.debug_level(0, l, 640, 480, blurred=True)
-        assert sha256(bl) == str(g[f"a_blur{l}_sha"]), f"blurred level {l}"
+    monkeypatch.setenv("VXORB_FULL_BLUR", "1")
+    with vx.VxOrb() as hf:
+        monkeypatch.delenv("VXORB_FULL_BLUR")
+        kp, desc = hf.extract(a)
+        assert_kp_equal(kp, g["kp_a"])
+        assert np.array_equal(desc, g["desc_a"])
+        for l in range(8):
+            lvl = h.debug_level(0, l, 640, 480)
+            assert sha256(lvl) == str(g[f"a_level{l}_sha"]), f"pyramid level {l}"
+            full = hf.debug_level(0, l, 640, 480, blurred=True)
+            assert sha256(full) == str(g[f"a_blur{l}_sha"]), f"blurred level {l}"
+            assert np.array_equal(_interior(h.debug_level(0, l, 640, 480, blurred=True)), _interior(full)), f"level {l}"
 
 
 @pytest.mark.parametrize("kind,shape,border,thr", [
@@ -586,8 +604,8 @@ def test_bench_batch_shapes_vs_oracle(batch):
             levels = oracle.pyramid(frames[f])
             for l in range(8):
                 assert np.array_equal(hx.debug_level(f, l, 640, 480), levels[l]), f"frame {f} level {l}"
-                assert np.array_equal(hx.debug_level(f, l, 640, 480, blurred=True), oracle.blur7(levels[l])), \
-                    f"frame {f} blurred level {l}"
+                assert np.array_equal(_interior(hx.debug_level(f, l, 640, 480, blurred=True)),
+                                      _interior(oracle.blur7(levels[l]))), f"frame {f} blurred level {l}"
         for radius in (32.0, 0.0):
             ref_m = _oracle_pairs(ext, radius)
             hx.track_reset()

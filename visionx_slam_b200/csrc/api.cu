@@ -129,6 +129,7 @@ struct vxorb_handle {
     long long next_frame_id = 1, next_set_id = kFirstSetId;
     std::map<long long, ResidentSet> sets;
     bool no_graph = false, no_overlap = false, no_flat_upload = false;  // VXORB_NO_* switches, read once in vxorb_create
+    bool full_blur = false;  // VXORB_FULL_BLUR: blur whole levels (with aprons) instead of what descriptors can read
     uint8_t* x_stage = nullptr;  // pinned staging block of the synchronous extract calls
     size_t x_bytes = 0;
     uint8_t* flush_buf = nullptr;
@@ -224,6 +225,7 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
     std::vector<uint32_t> coef;
     lt.fast_tile_begin[0] = lt.blur_tile_begin[0] = 0;
     lt.resize_band = 1;
+    lt.blur_margin = h->full_blur ? 0 : kBlurMargin;
     for (int l = 0; l < p.n_levels; ++l) {
         if (lt.w[l] < 1 || lt.h[l] < 1) {  // pyramid bottoms out: drop the remaining levels
             lt.n_levels = l;
@@ -244,9 +246,7 @@ int ensure_geometry(vxorb_handle* h, int W, int H) {
         lt.fast_tiles_x[l] = lt.active[l] ? fast_tiles_x(lt.w[l], kEdge) : 0;
         const int fty = lt.active[l] ? fast_tiles_y(lt.h[l], kEdge) : 0;
         lt.fast_tile_begin[l + 1] = lt.fast_tile_begin[l] + lt.fast_tiles_x[l] * fty;
-        lt.blur_tiles_x[l] = (lt.w[l] + kBlurCols - 1) / kBlurCols;
-        lt.blur_tile_begin[l + 1] =
-            lt.blur_tile_begin[l] + (lt.blur_tiles_x[l] * ((lt.h[l] + kBlurRows - 1) / kBlurRows) + 255) / 256;
+        lt.blur_tile_begin[l + 1] = lt.blur_tile_begin[l] + (set_blur_extent(lt, l, lt.blur_margin, lt.active[l] != 0) + 255) / 256;
         lt.coef_off[l] = coef_off;
         if (l > 0) {
             coef.resize((size_t)coef_off + lt.w[l] + lt.h[l]);
@@ -372,7 +372,8 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch, const ResidentSet
     // the level chain is the critical path of the call, the level kernels therefore skip their apron phase and the
     // aprons of all levels are built on the side stream just before the blur, beside FAST + select.  Large batches
     // keep them in the band kernels (a separate pass over the planes costs more than it hides there).
-    const bool apron_aside = overlap && lt.resize_band && batch < 8;
+    const bool need_apron = lt.blur_margin < kApronY;  // the interior-only blur never reaches the border
+    const bool apron_aside = need_apron && overlap && lt.resize_band && batch < 8;
     {
         StageScope sc(h, s, VXORB_STAGE_PYRAMID);
         sc.end(launch_pyramid(lt, d, s, !apron_aside));
@@ -892,6 +893,7 @@ int vxorb_create(const vxorb_params* p, vxorb_handle** out) {
     h->no_graph = getenv("VXORB_NO_GRAPH") != nullptr;
     h->no_overlap = getenv("VXORB_NO_OVERLAP") != nullptr;
     h->no_flat_upload = getenv("VXORB_NO_FLAT_UPLOAD") != nullptr;
+    h->full_blur = getenv("VXORB_FULL_BLUR") != nullptr;
     h->kp_cap = p->max_keypoints > 0 ? p->max_keypoints : p->n_features + p->n_features / 4 + 64;
     auto bail = [&](cudaError_t err, const char* what) {
         g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
@@ -1864,8 +1866,8 @@ static int single_level_tab(vxorb_handle* h, int W, int H, int border, LevelTab*
     lt.cand_cap[0] = lt.active[0] ? ((ew + 1) / 2 + 1) * ((eh + 1) / 2 + 1) : 0;
     lt.fast_tiles_x[0] = lt.active[0] ? fast_tiles_x(W, border) : 0;
     lt.fast_tile_begin[1] = lt.active[0] ? lt.fast_tiles_x[0] * fast_tiles_y(H, border) : 0;
-    lt.blur_tiles_x[0] = (W + kBlurCols - 1) / kBlurCols;
-    lt.blur_tile_begin[1] = (lt.blur_tiles_x[0] * ((H + kBlurRows - 1) / kBlurRows) + 255) / 256;
+    lt.blur_margin = 0;  // stage isolation: the whole image, from an aproned plane
+    lt.blur_tile_begin[1] = (set_blur_extent(lt, 0, 0, true) + 255) / 256;
     for (int l = 1; l < kMaxLevels; ++l) {
         lt.fast_tile_begin[l + 1] = lt.fast_tile_begin[1];
         lt.blur_tile_begin[l + 1] = lt.blur_tile_begin[1];

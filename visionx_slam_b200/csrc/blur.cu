@@ -9,8 +9,9 @@
 //
 // Register-resident separable filter, no shared memory.  One thread owns a strip of 4 adjacent
 // columns x kBlurRows output rows and walks down the source rows:
-//   * per source row: three aligned 32-bit loads (columns x0-4 .. x0+7; the reflect-101 apron
-//     written by apron_kernel makes the border a plain read), ten byte->float conversions
+//   * per source row: three aligned 32-bit loads (columns x0-4 .. x0+7; the production extent stays kBlurMargin px
+//     inside the level — only what a descriptor window can read — so no border is ever touched; whole-level runs
+//     read the reflect-101 apron written by apron_kernel as plain pixels), ten byte->float conversions
 //     (I2F.U8 with a byte selector, on the conversion unit), 4 x 7 row-pass FMAs with the taps as immediates;
 //   * the last seven row-pass rows live in registers (window rotated by unrolling x7);
 //   * per output row: 4 x 7 column-pass ops, round-half-even by adding 1.5*2^23, pack, one
@@ -73,14 +74,14 @@ blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restr
     }
     int l = 0;
     while (l + 1 < lt.n_levels && (int)blockIdx.x >= lt.blur_tile_begin[l + 1]) ++l;
-    const int h = lt.h[l], pitch = lt.pitch[l];
+    const int y_end = lt.blur_y1[l], pitch = lt.pitch[l];
     const int words = lt.blur_tiles_x[l];
     const int item = ((int)blockIdx.x - lt.blur_tile_begin[l]) * 256 + (int)threadIdx.x;
     const int band = item / words;
-    const int y0 = band * kBlurRows;
-    if (y0 >= h) return;
-    const int x0 = (item - band * words) * kBC;
-    const int rows_out = min(kBlurRows, h - y0);
+    const int y0 = lt.blur_y0[l] + band * kBlurRows;
+    if (y0 >= y_end) return;
+    const int x0 = lt.blur_x0[l] + (item - band * words) * kBC;
+    const int rows_out = min(kBlurRows, y_end - y0);
     const size_t plane = lt.off[l] + (size_t)blockIdx.y * lt.fstride[l];
     // source row r (0-based in the strip) is image row y0 - 3 + r; the first word starts at x0 - 4
     const uint8_t* src = pyr + plane + (ptrdiff_t)(y0 - kApronY) * pitch + (x0 - 4);

@@ -560,7 +560,8 @@ int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, 
     int launches = 0;
     // aprons_inline == false (only for fewer than 8 frames on the band path): the caller builds the apron of EVERY level
     // itself (launch_apron over all levels, beside the chain's consumers that do not read it)
-    const bool level0_apron = aprons_inline;
+    const bool need = lt.blur_margin < kApronY;  // the apron is read by a whole-level blur only
+    const bool level0_apron = aprons_inline && need;
     if (lt.resize_band) {
         // level 0 comes from the upload; the bands write their own apron.  The resampling reads no apron byte of
         // its source, so a caller may build level 0's apron elsewhere (beside the chain) and pass false.
@@ -579,7 +580,7 @@ int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, 
             const int nb = small ? std::max(1, lt.h[l] / 4) : lt.n_bands[l];
             launch_resize_band(src_plane, lt.h[l - 1], lt.pitch[l - 1], (size_t)lt.fstride[l - 1], db.pyr + lt.off[l], lt.w[l],
                                lt.h[l], lt.pitch[l], (size_t)lt.fstride[l], tab + lt.w[l], xw4, xw2, rows, nb, lt.band_smem[l],
-                               lt.batch, s, aprons_inline || lt.batch >= 8);
+                               lt.batch, s, need && (aprons_inline || lt.batch >= 8));
             ++launches;
         }
         return launches;
@@ -590,7 +591,7 @@ int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, 
                       db.coef + lt.coef_off[l], db.coef + lt.coef_off[l] + lt.w[l], lt.batch, lt.resize_fast[l] != 0, s);
         ++launches;
     }
-    launches += launch_apron(lt, db, lt.n_levels, s);
+    if (need) launches += launch_apron(lt, db, lt.n_levels, s);
     return launches;
 }
 

@@ -40,6 +40,7 @@ namespace vxorb {
 
 constexpr int kMaxLevels = VXORB_MAX_LEVELS;
 constexpr int kEdge = 31;        // cv::ORB edgeThreshold (only value supported)
+constexpr int kBlurMargin = kEdge - 18;  // no descriptor window reads a blurred pixel closer than this to the border
 constexpr int kHalfPatch = 15;   // patchSize 31
 constexpr int kPitchAlign = 32;
 // Every pyramid / blurred plane carries a reflect-101 apron so stencil kernels need no border
@@ -77,6 +78,19 @@ inline int fast_tiles_y(int h, int border) {
 
 inline int plane_pitch(int w) { return (kApronX + w + kApronRight + kPitchAlign - 1) / kPitchAlign * kPitchAlign; }
 inline size_t plane_bytes(int w, int h) { return (size_t)plane_pitch(w) * (size_t)(h + 2 * kApronY); }
+// Fills the blur extent of level l (see LevelTab::blur_margin) and returns its strip count.
+template <class LT>
+inline int set_blur_extent(LT& lt, int l, int margin, bool active) {
+    if (margin > 0 && !active) {  // no keypoints on this level: nothing reads its blurred plane
+        lt.blur_x0[l] = lt.blur_y0[l] = lt.blur_y1[l] = lt.blur_tiles_x[l] = 0;
+        return 0;
+    }
+    lt.blur_x0[l] = margin / kBlurCols * kBlurCols;
+    lt.blur_y0[l] = margin;
+    lt.blur_y1[l] = lt.h[l] - margin;
+    lt.blur_tiles_x[l] = (lt.w[l] - margin - lt.blur_x0[l] + kBlurCols - 1) / kBlurCols;
+    return lt.blur_tiles_x[l] * ((lt.blur_y1[l] - lt.blur_y0[l] + kBlurRows - 1) / kBlurRows);
+}
 inline size_t plane_origin(int w) { return (size_t)kApronY * plane_pitch(w) + kApronX; }
 
 // Per-geometry tables passed to kernels by value (kernel parameters live in the constant bank).
@@ -97,6 +111,14 @@ struct LevelTab {
     int fast_tiles_x[kMaxLevels], fast_tile_begin[kMaxLevels + 1];
     // blur strips: blur_tiles_x = strips of kBlurCols px per row; CTAs of level l are [blur_tile_begin[l], [l+1])
     int blur_tiles_x[kMaxLevels], blur_tile_begin[kMaxLevels + 1];
+    // The blurred planes are read by the descriptor windows alone: +-18 px (the rBRIEF pattern reaches 13 px, rotated
+    // sqrt(2) * 13 -> 18) around keypoints that sit kEdge = 31 px inside the level.  With blur_margin = kBlurMargin only
+    // the pixels [margin, w - margin) x [margin, h - margin) of the active levels are filtered (x rounded down to a
+    // strip), nothing of the reflect-101 apron is ever read and nobody builds it; blur_margin = 0 filters whole levels
+    // from aproned planes (stage-isolation entry points and VXORB_FULL_BLUR=1).  blur_x0[l] is the first strip's
+    // column, blur_tiles_x[l] the strips per row, rows [blur_y0[l], blur_y1[l]).
+    int blur_margin;
+    int blur_x0[kMaxLevels], blur_y0[kMaxLevels], blur_y1[kMaxLevels];
     int coef_off[kMaxLevels];        // offset (in u32) of level l's resize tables: x[w_l] then y[h_l]
     int resize_fast[kMaxLevels];     // level l's x taps fit the register-resident resize kernel
     // band kernel (pyramid.cu): per-word tap table at coef + xw_off[l] (uint4[words] then uint2[words]),
