@@ -2,10 +2,10 @@
 """One serial resident pass of the benchmark's 128-frame chunk per matcher, for ncu.
 
     python profiles/prof_step.py [batch]                       # plain run (must exit 0 before the ncu run)
-    ncu --set full --clock-control none --import-source on -s 45 -c 28 -o gpurun_out/r2x python profiles/prof_step.py
+    ncu --set full --clock-control none --import-source on -s 42 -c 26 -o gpurun_out/r2x python profiles/prof_step.py
 
-Launch order after the warm-up (3 unpack launches of the upload + 3 passes x 14 launches = 45 to skip):
-pass A (brute-force matcher, radius 0): apron, 7 x resize_band, fast, select, blur, describe, knn2<1>, match_compact;
+Launch order after the warm-up (3 unpack launches of the upload + 3 passes x 13 launches = 42 to skip):
+pass A (brute-force matcher, radius 0): 7 x resize_band, fast, select, blur, describe, knn2<1>, match_compact;
 pass B (windowed matcher, radius 32): the same with knn2_window.  Stage instrumentation is on, so the stages run
 one after another on one stream (the production schedule overlaps the blur with FAST + select)."""
 import os

@@ -15,7 +15,7 @@ timeout 600 python bench.py --steps 20 --warmup 3 > $OUT/${TAG}_bench.json 2> $O
 tail -c 600 $OUT/${TAG}_bench.json
 timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/${TAG}_bench_reference.json 2>> $OUT/${TAG}_bench.err; echo "ref rc=$?"
 timeout 300 python profiles/prof_step.py > $OUT/${TAG}_prof_plain.log 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -s 45 -c 28 -f -o $OUT/${TAG}_full python profiles/prof_step.py > $OUT/${TAG}_ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -s 42 -c 26 -f -o $OUT/${TAG}_full python profiles/prof_step.py > $OUT/${TAG}_ncu_full.log 2>&1
 echo "ncu full rc=$?"; cat $OUT/${TAG}_prof_plain.log
 if [ "${3:-}" == "no_launchlist" ]; then kill $SMI 2>/dev/null; ls -la $OUT | head -40; exit 0; fi
 timeout 300 python bench.py --steps 2 --warmup 3 --no-configs --no-cpu-baseline > $OUT/${TAG}_bench_short.json 2>> $OUT/${TAG}_bench.err && \
