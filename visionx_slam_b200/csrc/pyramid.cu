@@ -11,6 +11,7 @@
 #include <math.h>
 
 #include <algorithm>
+#include <type_traits>
 
 #include "vxorb_internal.h"
 
@@ -250,12 +251,15 @@ namespace {
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 }  // namespace
 
-// FULL: 16-row bands of a large batch — eight row pairs side by side, one warp each (the throughput shape, 32
-// registers).  !FULL: any band height, pairs_par pairs side by side and the per-word tables prefetched while the
+// FULL: 16-row bands of a large batch — eight row pairs side by side, one warp each, rows outside and word groups
+// inside (the throughput shape, 40 registers).  !FULL: any band height, pairs_par pairs side by side and the per-word tables prefetched while the
 // band is in flight (the latency shape for a few frames: 39 registers, which would cost the batched case a CTA
 // per SM).
+#ifndef VXORB_PYR_FULL_CTAS
+#define VXORB_PYR_FULL_CTAS 6  // resident CTAs per SM asked of the throughput shape: 40 registers (1: 83, 4: 64, 8: 32 + spills; measured)
+#endif
 template <bool FULL>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, FULL ? VXORB_PYR_FULL_CTAS : 1)
 resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, size_t sfstride,
                    uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
                    const uint32_t* __restrict__ ytab, const uint4* __restrict__ xw4, const uint2* __restrict__ xw2,
@@ -312,7 +316,82 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
     const int rem = words & 31;
     const int seg = (FULL && rem != 0 && rem <= 16) ? (rem <= 8 ? 8 : 16) : 0;
     const int words_main = seg ? words - rem : words;
-    for (int k0 = gw * 32; k0 < words_main; k0 += gstep) {
+    if (FULL) {
+        // Throughput shape: a warp owns one row pair of the band (two in the taller last band), so everything that
+        // depends on the rows alone — tap rows, their shared-memory bases, the vertical weights, which horizontal
+        // passes the second row can reuse, the output row pointers — is worked out once per pair, and the loop over
+        // the word groups inside carries only the per-word tables, the passes and the stores (the other loop order
+        // redid the row bookkeeping for every group of 32 words: 22 thread-instructions per output pixel against 12).
+        for (int y = y_begin + 2 * warp; y < y_end; y += 16) {
+            const uint32_t ty = __ldg(ytab + y);
+            const bool two = y + 1 < y_end;
+            const uint32_t tz = two ? __ldg(ytab + y + 1) : ty;
+            const int j0 = (int)(ty & 0xffffu), j1 = min(j0 + 1, sh - 1);
+            const int i0 = (int)(tz & 0xffffu), i1 = min(i0 + 1, sh - 1);
+            VX_CHECK(j0 >= jlo && i1 <= jhi);
+            const uint32_t* const rj0 = sm_w + (j0 - jlo) * spitch_w;
+            const uint32_t* const rj1 = sm_w + (j1 - jlo) * spitch_w;
+            const uint32_t* const ri0 = sm_w + (i0 - jlo) * spitch_w;
+            const uint32_t* const ri1 = sm_w + (i1 - jlo) * spitch_w;
+            const bool reuse = i0 == j1, clamped = i1 == i0;  // warp-uniform: rows only
+            const uint32_t cya1 = ty >> 16, cya0 = 256u - cya1, cyb1 = tz >> 16, cyb0 = 256u - cyb1;
+            uint8_t* const drow = dst + (size_t)y * dpitch;
+            // MODE 0: one output row (the odd last row of a band); 1: two rows, the second one's upper source row is
+            // the first one's lower one (five pairs out of six at scale 1.2: three horizontal passes); 2: two rows
+            // with four passes.  The mode depends on the rows only, so each is a straight-line loop over the word groups.
+            auto groups = [&](auto mode_tag) {
+                constexpr int MODE = decltype(mode_tag)::value;
+                for (int k0 = 0; k0 < words_main; k0 += 32) {
+                    const int k = k0 + lane;
+                    const bool active = k < words;
+                    const int kk = active ? k : words - 1;
+                    const uint4 wg = __ldg(xw4 + kk);
+                    const uint2 sx = __ldg(xw2 + kk);
+                    const uint32_t sel01 = sx.x & 0xffffu, sel23 = sx.x >> 16;
+                    const int wofs = (int)(sx.y & 0xffffu);
+                    const uint32_t shift = sx.y >> 16;
+                    VX_CHECK(wofs + 2 < spitch_w);
+                    auto hpass = [&](const uint32_t* row, uint32_t (&hv)[4]) {
+                        const uint32_t* p = row + wofs;
+                        const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+                        const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
+                        const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
+                        hv[0] = __dp2a_lo(wg.x, b01, 0u);
+                        hv[1] = __dp2a_hi(wg.y, b01, 0u);
+                        hv[2] = __dp2a_lo(wg.z, b23, 0u);
+                        hv[3] = __dp2a_hi(wg.w, b23, 0u);
+                    };
+                    auto vpass_store = [&](uint8_t* out, const uint32_t (&h0)[4], const uint32_t (&h1)[4], uint32_t c0,
+                                           uint32_t c1) {
+                        uint32_t v[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) v[j] = h1[j] * c1 + (h0[j] * c0 + (1u << 15));  // 16.16, byte 2 = result
+                        if (active)
+                            *reinterpret_cast<uint32_t*>(out + 4 * k) =
+                                __byte_perm(__byte_perm(v[0], v[1], 0x0062u), __byte_perm(v[2], v[3], 0x0062u), 0x5410u);
+                    };
+                    uint32_t ha[4], hb[4];
+                    hpass(rj0, ha);
+                    hpass(rj1, hb);
+                    vpass_store(drow, ha, hb, cya0, cya1);
+                    if (MODE == 1) {
+                        uint32_t hc[4];
+                        hpass(ri1, hc);
+                        vpass_store(drow + dpitch, hb, hc, cyb0, cyb1);
+                    } else if (MODE == 2) {
+                        uint32_t hc[4], hd[4];
+                        hpass(ri0, hc);
+                        hpass(ri1, hd);
+                        vpass_store(drow + dpitch, hc, hd, cyb0, cyb1);
+                    }
+                }
+            };
+            if (!two) groups(std::integral_constant<int, 0>());
+            else if (reuse && !clamped) groups(std::integral_constant<int, 1>());
+            else groups(std::integral_constant<int, 2>());
+        }
+    }
+    for (int k0 = FULL ? words_main : gw * 32; k0 < words_main; k0 += gstep) {
         const int k = k0 + lane;
         const bool active = k < words;
         uint4 wg;
