@@ -348,7 +348,10 @@ int vxorb_debug_fast(vxorb_handle* h, const uint8_t* img, int width, int height,
                      int threshold, int border, int cap, vxorb_corner* out, int* n_out);
 int vxorb_debug_blur(vxorb_handle* h, const uint8_t* src, int width, int height, size_t stride,
                      uint8_t* dst, size_t dstride);
-/* Pyramid / blurred-pyramid level of frame `frame` of the most recent extract call. */
+/* Pyramid / blurred-pyramid level of frame `frame` of the most recent extract call.  A blurred level is defined only
+ * where a descriptor can read it: pixels at least 13 px (edge threshold 31 - window reach 18) inside the level, and only
+ * on levels that can hold keypoints; the rest of the plane is not computed (set VXORB_FULL_BLUR=1 before vxorb_create
+ * for whole-level blurring, as cv::GaussianBlur(BORDER_REFLECT_101) would give it). */
 int vxorb_debug_level(vxorb_handle* h, int frame, int level, int blurred, uint8_t* dst,
                       size_t dstride);
 
