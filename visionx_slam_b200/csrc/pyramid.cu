@@ -251,72 +251,19 @@ namespace {
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 }  // namespace
 
-// FULL: 16-row bands of a large batch — eight row pairs side by side, one warp each, rows outside and word groups
-// inside (the throughput shape, 40 registers).  !FULL: any band height, pairs_par pairs side by side and the per-word tables prefetched while the
-// band is in flight (the latency shape for a few frames: 39 registers, which would cost the batched case a CTA
-// per SM).
-#ifndef VXORB_PYR_FULL_CTAS
-#define VXORB_PYR_FULL_CTAS 6  // resident CTAs per SM asked of the throughput shape: 40 registers (1: 83, 4: 64, 8: 32 + spills; measured)
-#endif
-template <bool FULL>
-__global__ void __launch_bounds__(256, FULL ? VXORB_PYR_FULL_CTAS : 1)
-resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, size_t sfstride,
-                   uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
-                   const uint32_t* __restrict__ ytab, const uint4* __restrict__ xw4, const uint2* __restrict__ xw2,
-                   int words, int band_rows, int n_bands, int pairs_par, int write_apron) {
-    extern __shared__ __align__(128) uint8_t rows_sm[];
-    __shared__ __align__(8) unsigned long long bar;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int b = blockIdx.x;
-    const int y_begin = b * band_rows, y_end = (b == n_bands - 1) ? dh : y_begin + band_rows;
-    const int jlo = (int)(__ldg(ytab + y_begin) & 0xffffu);
-    const int jhi = min((int)(__ldg(ytab + y_end - 1) & 0xffffu) + 1, sh - 1);
-    dst += (size_t)blockIdx.y * dfstride;
-    if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(&bar)), "r"(1) : "memory");
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        const uint32_t bytes = (uint32_t)(jhi - jlo + 1) * (uint32_t)spitch;
-        const uint8_t* g = src_plane + (size_t)blockIdx.y * sfstride + (size_t)(jlo + kApronY) * spitch;
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&bar)), "r"(bytes) : "memory");
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                         smem_addr(rows_sm)),
-                     "l"(g), "r"(bytes), "r"(smem_addr(&bar))
-                     : "memory");
-    }
-    // pairs_par (8, 4, 2 or 1) row pairs are worked on side by side; the 8 / pairs_par warps of a pair split
-    // its words 32 at a time, so a short band (small batches: more, shorter bands) still occupies all 8 warps
-    if (FULL) pairs_par = 8;
-    const int pw = warp & (pairs_par - 1), gw = warp / pairs_par, gstep = (8 / pairs_par) * 32;
-    // the per-word tables of the first group are fetched while the band is still in flight
-    uint4 wg_next = make_uint4(0, 0, 0, 0);
-    uint2 sx_next = make_uint2(0, 0);
-    if (!FULL && gw * 32 < words) {
-        const int kk = min(gw * 32 + lane, words - 1);
-        wg_next = __ldg(xw4 + kk);
-        sx_next = __ldg(xw2 + kk);
-    }
-    __syncthreads();  // barrier initialised before anyone polls it
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "RW_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra RD_%=;\n"
-        "bra RW_%=;\n"
-        "RD_%=:\n"
-        "}\n" ::"r"(smem_addr(&bar)),
-        "r"(0)
-        : "memory");
-
-    const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(rows_sm);
-    const int spitch_w = spitch >> 2;
-    // FULL: when the last group of 32 words of a row is at most half full, it is not given a warp-iteration per
-    // row pair; the tails of 2 (<= 16 words) or 4 (<= 8 words) row pairs share one iteration below.
+// The throughput shape's work on one band of one frame: output rows [y_begin, y_end) of `dst` from the source rows
+// [jlo, jhi] that sit in shared memory at sm_w (spitch_w words per row).  Called by all 256 threads of the CTA.
+__device__ __forceinline__ void band_rows_full(const uint32_t* sm_w, int jlo, int jhi, int sh, int spitch_w,
+                                               uint8_t* __restrict__ dst, int dpitch, int y_begin, int y_end,
+                                               const uint32_t* __restrict__ ytab, const uint4* __restrict__ xw4,
+                                               const uint2* __restrict__ xw2, int words, int lane, int warp) {
+    // when the last group of 32 words of a row is at most half full, it is not given a warp-iteration per row pair;
+    // the tails of 2 (<= 16 words) or 4 (<= 8 words) row pairs share one iteration below
     const int rem = words & 31;
-    const int seg = (FULL && rem != 0 && rem <= 16) ? (rem <= 8 ? 8 : 16) : 0;
+    const int seg = (rem != 0 && rem <= 16) ? (rem <= 8 ? 8 : 16) : 0;
     const int words_main = seg ? words - rem : words;
-    if (FULL) {
+    (void)jhi;
+    {
         // Throughput shape: a warp owns one row pair of the band (two in the taller last band), so everything that
         // depends on the rows alone — tap rows, their shared-memory bases, the vertical weights, which horizontal
         // passes the second row can reuse, the output row pointers — is worked out once per pair, and the loop over
@@ -391,7 +338,111 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
             else groups(std::integral_constant<int, 2>());
         }
     }
-    for (int k0 = FULL ? words_main : gw * 32; k0 < words_main; k0 += gstep) {
+    if (seg) {
+        const int sub = lane / seg, kq = lane & (seg - 1), ppi = 32 / seg;
+        const bool has_word = kq < rem;
+        const int k = words_main + (has_word ? kq : 0);
+        const uint4 wg = __ldg(xw4 + k);
+        const uint2 sx = __ldg(xw2 + k);
+        const uint32_t sel01 = sx.x & 0xffffu, sel23 = sx.x >> 16;
+        const int wofs = (int)(sx.y & 0xffffu);
+        const uint32_t shift = sx.y >> 16;
+        uint8_t* const dcol = dst + 4 * k;
+        auto hpass = [&](int j, uint32_t (&hv)[4]) {
+            const uint32_t* p = sm_w + (j - jlo) * spitch_w + wofs;
+            const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+            const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
+            const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
+            hv[0] = __dp2a_lo(wg.x, b01, 0u);
+            hv[1] = __dp2a_hi(wg.y, b01, 0u);
+            hv[2] = __dp2a_lo(wg.z, b23, 0u);
+            hv[3] = __dp2a_hi(wg.w, b23, 0u);
+        };
+        auto row_out = [&](int y, bool on) {  // rows differ between the lanes of the warp here: no reuse of passes
+            const uint32_t ty = __ldg(ytab + y);
+            const int j0 = (int)(ty & 0xffffu);
+            const int j1 = min(j0 + 1, sh - 1);
+            uint32_t h0[4], h1[4], v[4];
+            hpass(j0, h0);
+            hpass(j1, h1);
+            const uint32_t cy1 = ty >> 16, cy0 = 256u - cy1;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = h1[j] * cy1 + (h0[j] * cy0 + (1u << 15));
+            if (on)
+                *reinterpret_cast<uint32_t*>(dcol + (uint32_t)(y * dpitch)) =
+                    __byte_perm(__byte_perm(v[0], v[1], 0x0062u), __byte_perm(v[2], v[3], 0x0062u), 0x5410u);
+        };
+        const int n_pairs = (y_end - y_begin + 1) >> 1;
+        for (int p0 = warp * ppi; p0 < n_pairs; p0 += 8 * ppi) {
+            const int y = y_begin + 2 * (p0 + sub);
+            row_out(min(y, y_end - 1), has_word && y < y_end);
+            row_out(min(y + 1, y_end - 1), has_word && y + 1 < y_end);
+        }
+    }
+}
+
+// FULL: 16-row bands of a large batch — eight row pairs side by side, one warp each, rows outside and word groups
+// inside (the throughput shape, 40 registers).  !FULL: any band height, pairs_par pairs side by side and the per-word tables prefetched while the
+// band is in flight (the latency shape for a few frames: 39 registers, which would cost the batched case a CTA
+// per SM).
+#ifndef VXORB_PYR_FULL_CTAS
+#define VXORB_PYR_FULL_CTAS 6  // resident CTAs per SM asked of the throughput shape: 40 registers (1: 83, 4: 64, 8: 32 + spills; measured)
+#endif
+template <bool FULL>
+__global__ void __launch_bounds__(256, FULL ? VXORB_PYR_FULL_CTAS : 1)
+resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, size_t sfstride,
+                   uint8_t* __restrict__ dst, int dw, int dh, int dpitch, size_t dfstride,
+                   const uint32_t* __restrict__ ytab, const uint4* __restrict__ xw4, const uint2* __restrict__ xw2,
+                   int words, int band_rows, int n_bands, int pairs_par, int write_apron) {
+    extern __shared__ __align__(128) uint8_t rows_sm[];
+    __shared__ __align__(8) unsigned long long bar;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.x;
+    const int y_begin = b * band_rows, y_end = (b == n_bands - 1) ? dh : y_begin + band_rows;
+    const int jlo = (int)(__ldg(ytab + y_begin) & 0xffffu);
+    const int jhi = min((int)(__ldg(ytab + y_end - 1) & 0xffffu) + 1, sh - 1);
+    dst += (size_t)blockIdx.y * dfstride;
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(&bar)), "r"(1) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const uint32_t bytes = (uint32_t)(jhi - jlo + 1) * (uint32_t)spitch;
+        const uint8_t* g = src_plane + (size_t)blockIdx.y * sfstride + (size_t)(jlo + kApronY) * spitch;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(&bar)), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         smem_addr(rows_sm)),
+                     "l"(g), "r"(bytes), "r"(smem_addr(&bar))
+                     : "memory");
+    }
+    // pairs_par (8, 4, 2 or 1) row pairs are worked on side by side; the 8 / pairs_par warps of a pair split
+    // its words 32 at a time, so a short band (small batches: more, shorter bands) still occupies all 8 warps
+    if (FULL) pairs_par = 8;
+    const int pw = warp & (pairs_par - 1), gw = warp / pairs_par, gstep = (8 / pairs_par) * 32;
+    // the per-word tables of the first group are fetched while the band is still in flight
+    uint4 wg_next = make_uint4(0, 0, 0, 0);
+    uint2 sx_next = make_uint2(0, 0);
+    if (!FULL && gw * 32 < words) {
+        const int kk = min(gw * 32 + lane, words - 1);
+        wg_next = __ldg(xw4 + kk);
+        sx_next = __ldg(xw2 + kk);
+    }
+    __syncthreads();  // barrier initialised before anyone polls it
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "RW_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra RD_%=;\n"
+        "bra RW_%=;\n"
+        "RD_%=:\n"
+        "}\n" ::"r"(smem_addr(&bar)),
+        "r"(0)
+        : "memory");
+
+    const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(rows_sm);
+    const int spitch_w = spitch >> 2;
+    if (FULL) band_rows_full(sm_w, jlo, jhi, sh, spitch_w, dst, dpitch, y_begin, y_end, ytab, xw4, xw2, words, lane, warp);
+    for (int k0 = FULL ? words : gw * 32; k0 < words; k0 += gstep) {
         const int k = k0 + lane;
         const bool active = k < words;
         uint4 wg;
@@ -462,47 +513,6 @@ resize_band_kernel(const uint8_t* __restrict__ src_plane, int sh, int spitch, si
                     vpass_store(y + 1, ha, hc, tz >> 16);
                 }
             }
-        }
-    }
-    if (seg) {
-        const int sub = lane / seg, kq = lane & (seg - 1), ppi = 32 / seg;
-        const bool has_word = kq < rem;
-        const int k = words_main + (has_word ? kq : 0);
-        const uint4 wg = __ldg(xw4 + k);
-        const uint2 sx = __ldg(xw2 + k);
-        const uint32_t sel01 = sx.x & 0xffffu, sel23 = sx.x >> 16;
-        const int wofs = (int)(sx.y & 0xffffu);
-        const uint32_t shift = sx.y >> 16;
-        uint8_t* const dcol = dst + 4 * k;
-        auto hpass = [&](int j, uint32_t (&hv)[4]) {
-            const uint32_t* p = sm_w + (j - jlo) * spitch_w + wofs;
-            const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
-            const uint32_t lo = __funnelshift_r(w0, w1, shift), hi = __funnelshift_r(w1, w2, shift);
-            const uint32_t b01 = __byte_perm(lo, hi, sel01), b23 = __byte_perm(lo, hi, sel23);
-            hv[0] = __dp2a_lo(wg.x, b01, 0u);
-            hv[1] = __dp2a_hi(wg.y, b01, 0u);
-            hv[2] = __dp2a_lo(wg.z, b23, 0u);
-            hv[3] = __dp2a_hi(wg.w, b23, 0u);
-        };
-        auto row_out = [&](int y, bool on) {  // rows differ between the lanes of the warp here: no reuse of passes
-            const uint32_t ty = __ldg(ytab + y);
-            const int j0 = (int)(ty & 0xffffu);
-            const int j1 = min(j0 + 1, sh - 1);
-            uint32_t h0[4], h1[4], v[4];
-            hpass(j0, h0);
-            hpass(j1, h1);
-            const uint32_t cy1 = ty >> 16, cy0 = 256u - cy1;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) v[j] = h1[j] * cy1 + (h0[j] * cy0 + (1u << 15));
-            if (on)
-                *reinterpret_cast<uint32_t*>(dcol + (uint32_t)(y * dpitch)) =
-                    __byte_perm(__byte_perm(v[0], v[1], 0x0062u), __byte_perm(v[2], v[3], 0x0062u), 0x5410u);
-        };
-        const int n_pairs = (y_end - y_begin + 1) >> 1;
-        for (int p0 = warp * ppi; p0 < n_pairs; p0 += 8 * ppi) {
-            const int y = y_begin + 2 * (p0 + sub);
-            row_out(min(y, y_end - 1), has_word && y < y_end);
-            row_out(min(y + 1, y_end - 1), has_word && y + 1 < y_end);
         }
     }
     // A few frames: the apron is only read by the blur, which runs on the side stream — the caller builds it there
@@ -629,7 +639,7 @@ void launch_resize_band(const uint8_t* src_plane, int sh, int spitch, size_t sfs
 }
 
 cudaError_t init_pyramid_kernels() {
-    const cudaError_t e = cudaFuncSetAttribute(resize_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(resize_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(resize_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
