@@ -77,8 +77,8 @@ __device__ __forceinline__ uint32_t hamming_key(const uint32_t (&q)[8], const ui
 
 }  // namespace
 
-// QPT queries per thread: the plain all-pairs path keeps two query descriptors in registers so that one
-// pair of broadcast LDS.128 and one loop step serve two distances; the masked paths use one.
+// QPT queries per thread (1 in the shipped build; 2 keeps two query descriptors in registers so that one pair of
+// broadcast LDS.128 and one loop step serve two distances — see launch_knn2 for why it is not used).
 template <int QPT>
 __global__ void __launch_bounds__(kQPerBlock)
 knn2_kernel(const MatchArgs a) {
@@ -591,21 +591,23 @@ int launch_knn2(const MatchArgs& a, cudaStream_t s) {
         knn2_window_kernel<<<grid, kWinThreads, window_smem_bytes(a.max_t, a.max_q), s>>>(a, a.max_t, a.max_q);
         return 1;
     }
-    // few pairs: split the train rows over gridDim.z so that the launch still covers the GPU (two CTAs of
-    // 4 warps per SM at least), then merge the partial top-2 keys
+    // few pairs: split the train rows over gridDim.z so that the launch fills the GPU (towards sixteen CTAs of
+    // 4 warps per SM), then merge the partial top-2 keys
     MatchArgs b = a;
     const bool masked = a.mask != nullptr || ((a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr);
-    // two queries per thread pay off once a pair alone brings enough query blocks (measured: 4000 x 16384
-    // 0.303 -> 0.242 ms; 128 pairs of 1000 x 1000 lose occupancy with it)
-#ifndef VXORB_KNN_QPT2_MIN
-#define VXORB_KNN_QPT2_MIN 2048
+    // One query per thread everywhere.  Two per thread (one pair of broadcast loads and one loop step for two distances,
+    // 72 registers) were in use for sets of 2048 queries and more; measured again with the split target below they lose
+    // on every shape but one: 4000 x 4000 0.0437 -> 0.0385 ms, 2500 x 16384 0.106 -> 0.077, 4000 x 16384 0.135 -> 0.101,
+    // 8000 x 8000 0.135 -> 0.112 (0.108 with two), 32 pairs of 4000 x 4000 0.0341 -> 0.0249 ms per pair.
+#ifndef VXORB_KNN_QPT
+#define VXORB_KNN_QPT 1
 #endif
-    const int qpt = (masked || a.max_q < VXORB_KNN_QPT2_MIN) ? 1 : 2;
+    const int qpt = masked ? 1 : VXORB_KNN_QPT;
     const int qblocks = (a.max_q + kQPerBlock * qpt - 1) / (kQPerBlock * qpt);
     const int tiles = (a.max_t + kTrainTile - 1) / kTrainTile;
     int splits = 1;
 #ifndef VXORB_KNN_CTA_TARGET
-#define VXORB_KNN_CTA_TARGET (2 * 148)
+#define VXORB_KNN_CTA_TARGET (16 * 148)  // a single pair is split towards 16 CTAs of 4 warps per SM (4000 x 16384: 2 per SM 0.154 ms, 4: 0.118, 8 and 16: 0.101; 8000 x 8000: 0.124 / 0.118 / 0.112 / 0.100)
 #endif
     if (a.part && a.max_t > 0) {
         splits = (VXORB_KNN_CTA_TARGET + qblocks * a.pairs - 1) / (qblocks * a.pairs);
@@ -616,10 +618,12 @@ int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     }
     b.splits = splits;
     dim3 grid(qblocks, a.pairs, splits);
-    if (qpt == 1)
-        knn2_kernel<1><<<grid, kQPerBlock, 0, s>>>(b);
-    else
+#if VXORB_KNN_QPT == 2
+    if (qpt == 2)
         knn2_kernel<2><<<grid, kQPerBlock, 0, s>>>(b);
+    else
+#endif
+        knn2_kernel<1><<<grid, kQPerBlock, 0, s>>>(b);
     if (splits == 1) return 1;
     dim3 mgrid((a.max_q + 255) / 256, a.pairs);
     knn2_merge_kernel<<<mgrid, 256, 0, s>>>(b);
