@@ -56,7 +56,8 @@ typedef struct vxorb_params {
     float nn_ratio;     /* 0.8f */
     int min_matches;    /* 50; advisory (the adapter logs a warning below it)                   */
     int device_id;      /* CUDA device ordinal                                                  */
-    int max_width;      /* largest frame the handle accepts (device buffers are sized for it)   */
+    int max_width;      /* largest frame the handle accepts (device buffers are sized for it);
+                           at most 4095 x 4095: corner positions travel as 12-bit fields          */
     int max_height;
     int max_batch;      /* largest number of frames per batched call                            */
     int max_keypoints;  /* per-frame output capacity; 0 = n_features + n_features/4 + 64        */
