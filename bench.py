@@ -723,7 +723,9 @@ def run_ours(args, rank, world, local_rank):
             "schedule": {"ms_per_chunk_pipelined": ms_resident / passes, "ms_per_chunk_serial_instrumented": ms_serial / n_instr,
                          "note": "value is timed on the production schedule: passes pipelined over the handle's pipeline slots, the blur on "
                                  "a side stream beside FAST + select; the stage table and the roofline come from a serial "
-                                 "pass on one stream with events around every stage"},
+                                 "pass on one stream with events around every stage.  In the production schedule FAST's "
+                                 "persistent grid takes 3 CTAs per SM, leaving room for the other slots' kernels (8 % slower "
+                                 "alone, 2 % faster pipelined); alone, as in the serial pass, it takes all 5"},
             "roofline": roofline, "stages": table, "cpu_baseline": cpu, "clocks": clocks,
             "per_call": per_call, "c3": c3, "c4": c4,
         }

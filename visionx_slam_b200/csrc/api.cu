@@ -393,7 +393,7 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch, const ResidentSet
     }
     {
         StageScope sc(h, s, VXORB_STAGE_FAST);
-        const int n = launch_fast(lt, d, h->p.fast_threshold, kEdge, s);
+        const int n = launch_fast(lt, d, h->p.fast_threshold, kEdge, s, overlap && batch >= 8);
         if (n < 0) return fail(h, VXORB_E_CUDA, "cuTensorMapEncodeTiled failed for the FAST tile maps");
         sc.end(n);
     }

@@ -422,13 +422,23 @@ bool cached_fast_maps(const LevelTab& lt, const uint8_t* planes, FastMaps* out) 
 
 }  // namespace
 
-int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s) {
+// shared: the launch runs beside the kernels of other pipeline slots (the production schedule of a chunk).  The
+// persistent grid then takes kFastSharedCtas CTAs per SM instead of all kFastCtasPerSm: at five, FAST holds every
+// byte of an SM's shared memory for its whole run and nothing but the register-only blur can join it; at three it is
+// 8 % slower alone (0.205 against 0.190 ms per 128 frames) and the pipelined step 2 % faster (216 k against 211 k
+// frames/s; two CTAs: the same, four: +1 %).  Alone — instrumented passes, single frames, stage isolation — it
+// takes the whole SM.
+int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s, bool shared) {
     const int tiles = lt.fast_tile_begin[lt.n_levels];
     if (tiles == 0 || lt.batch <= 0) return 0;
     FastMaps maps;
     if (!cached_fast_maps(lt, db.pyr, &maps)) return -1;
     const int total = tiles * lt.batch;
-    const int grid = total < 148 * kFastCtasPerSm ? total : 148 * kFastCtasPerSm;  // persistent CTAs of 8 warps
+#ifndef VXORB_FAST_SHARED_CTAS
+#define VXORB_FAST_SHARED_CTAS 3
+#endif
+    const int per_sm = shared ? VXORB_FAST_SHARED_CTAS : kFastCtasPerSm;
+    const int grid = total < 148 * per_sm ? total : 148 * per_sm;  // persistent CTAs of 8 warps
     if (threshold >= 128)
         fast_kernel<true><<<grid, 256, 0, s>>>(lt, maps, db.cand, db.cand_n, threshold, border, tiles, total);
     else

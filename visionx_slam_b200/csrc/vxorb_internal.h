@@ -168,7 +168,7 @@ void launch_resize_band(const uint8_t* src_plane, int sh, int spitch, size_t sfs
                         int dpitch, size_t dfstride, const uint32_t* ytab, const uint4* xw4, const uint2* xw2, int rows,
                         int n_bands, int smem, int batch, cudaStream_t s, bool write_apron = true);
 cudaError_t init_pyramid_kernels();
-int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s);
+int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s, bool shared = false);
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_blur(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_describe(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, cudaStream_t s);
