@@ -79,8 +79,11 @@ __device__ __forceinline__ uint32_t hamming_key(const uint32_t (&q)[8], const ui
 
 // QPT queries per thread (1 in the shipped build; 2 keeps two query descriptors in registers so that one pair of
 // broadcast LDS.128 and one loop step serve two distances — see launch_knn2 for why it is not used).
+#ifndef VXORB_KNN_MINCTAS
+#define VXORB_KNN_MINCTAS 8  // asks ptxas for <= 64 registers; measured per 128 pairs of 1000 x 1000 alone / pipelined step: no second argument (64 registers, another schedule) 0.208 ms / 215.9 k frames/s, 1 (83) 0.185 / 215.2 k, 8 (64) 0.2015 / 217.8 k, 9 (56) 0.220 / 216.9 k, 10 (48) 0.222 / 217.0 k, 11 (40, spills) 0.241 / 214.0 k
+#endif
 template <int QPT>
-__global__ void __launch_bounds__(kQPerBlock)
+__global__ void __launch_bounds__(kQPerBlock, VXORB_KNN_MINCTAS)
 knn2_kernel(const MatchArgs a) {
     __shared__ __align__(16) uint32_t tdesc[kTrainTile][8];
     __shared__ float2 txy[kTrainTile];
