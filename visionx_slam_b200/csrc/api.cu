@@ -351,6 +351,23 @@ struct StageScope {
     }
 };
 
+// Switches the L1 / shared-memory preference of every pipeline kernel (vxorb_internal.h: kSharedCarveout) when the
+// mode changes: pct = kSharedCarveout while chunks overlap over the pipeline slots, -1 (the driver's per-kernel
+// choice) for everything that runs alone.  The preference is read when a launch is queued, so launches already in a
+// stream keep theirs.  Function attributes are per device and per process: one entry per device here.
+int apply_carveout(vxorb_handle* h, int pct) {
+    static int current[64] = {0};  // 0 = never set (the library never asks for 0 %)
+    const int dev = h->p.device_id & 63;
+    if (current[dev] == pct) return VXORB_OK;
+    cudaError_t e;
+    if ((e = carveout_pyramid(pct)) != cudaSuccess || (e = carveout_fast(pct)) != cudaSuccess ||
+        (e = carveout_select(pct)) != cudaSuccess || (e = carveout_blur(pct)) != cudaSuccess ||
+        (e = carveout_describe(pct)) != cudaSuccess || (e = carveout_match(pct)) != cudaSuccess)
+        return fail(h, VXORB_E_CUDA, cudaGetErrorString(e));
+    current[dev] = pct;
+    return VXORB_OK;
+}
+
 // Queues the extraction kernels for `batch` frames whose level 0 already sits in ws.db.pyr.
 // Outputs go to frame slots 1..batch of kp/desc/xy/kp_n (slot 0 is the streaming carry).
 int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch, const ResidentSet* out = nullptr) {
@@ -367,6 +384,10 @@ int enqueue_extract(vxorb_handle* h, Workspace& ws, int batch, const ResidentSet
     // the issue slots FAST's barriers and select's tails leave idle.  Instrumented runs stay serial so a
     // stage's events bracket that stage alone.
     const bool overlap = !h->stage_enabled && ws.side != nullptr && !h->no_overlap;
+    {
+        const int rc = apply_carveout(h, (overlap && batch >= 8) ? kSharedCarveout : -1);
+        if (rc) return rc;
+    }
     // The reflect apron of the planes is read by the blur alone (FAST's tiles take it in but never score a ring that
     // touches it; the resampling, Harris and the descriptor windows stay inside the image).  For a few frames, where
     // the level chain is the critical path of the call, the level kernels therefore skip their apron phase and the
@@ -437,6 +458,10 @@ int launch_extract_graph(vxorb_handle* h, Workspace& ws, ResidentSet& rs) {
         const long long before = h->launches;
         int stage_before[VXORB_STAGE_COUNT];
         for (int i = 0; i < VXORB_STAGE_COUNT; ++i) stage_before[i] = h->stage_launches[i];
+        {
+            const int rc = apply_carveout(h, -1);  // a single frame runs alone; not inside the capture
+            if (rc) return rc;
+        }
         CK(cudaStreamBeginCapture(ws.stream, cudaStreamCaptureModeThreadLocal));
         const int rc = enqueue_extract(h, ws, 1, &rs);
         cudaGraph_t graph = nullptr;
@@ -704,6 +729,7 @@ int run_knn_device(vxorb_handle* h, const DevSet& q, const DevSet& t, float radi
         return fail(h, VXORB_E_INVALID, "descriptor count must stay below 2^20 (index field of the packed 2-NN key)");
     int rc = ensure_match_scratch(h, std::max(std::max(q.n, t.n), 1));  // grows on demand: no fixed limit per side
     if (rc) return rc;
+    if ((rc = apply_carveout(h, -1)) != VXORB_OK) return rc;  // a single pair runs alone
     cudaStream_t s = h->ws[0].stream;
     const bool win = (radius > 0.f || box) && q.xy && t.xy;
     if (box && !win) return fail(h, VXORB_E_INVALID, "box mask needs query and train positions");

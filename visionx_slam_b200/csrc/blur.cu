@@ -159,6 +159,11 @@ blur_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, uint8_t* __restr
     }
 }
 
+cudaError_t carveout_blur(int pct) {
+    const cudaError_t e = set_carveout(blur_kernel<true>, pct);
+    return e != cudaSuccess ? e : set_carveout(blur_kernel<false>, pct);
+}
+
 int launch_blur(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
     const int ctas = lt.blur_tile_begin[lt.n_levels];
     if (ctas == 0) return 0;

@@ -340,6 +340,8 @@ cudaError_t init_device_tables() {
     return cudaMemcpyToSymbol(g_pattern, &host, sizeof(host));
 }
 
+cudaError_t carveout_describe(int pct) { return set_carveout(describe_kernel, pct); }
+
 int launch_describe(const LevelTab& lt, const DeviceBuffers& db, int kp_cap, cudaStream_t s) {
     // 16 keypoints per warp amortise the per-group trigonometry; tiny batches use 4 so that one
     // frame still spreads over ~80 CTAs

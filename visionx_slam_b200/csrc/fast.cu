@@ -422,6 +422,11 @@ bool cached_fast_maps(const LevelTab& lt, const uint8_t* planes, FastMaps* out) 
 
 }  // namespace
 
+cudaError_t carveout_fast(int pct) {
+    const cudaError_t e = set_carveout(fast_kernel<true>, pct);
+    return e != cudaSuccess ? e : set_carveout(fast_kernel<false>, pct);
+}
+
 // shared: the launch runs beside the kernels of other pipeline slots (the production schedule of a chunk).  The
 // persistent grid then takes kFastSharedCtas CTAs per SM instead of all kFastCtasPerSm: at five, FAST holds every
 // byte of an SM's shared memory for its whole run and nothing but the register-only blur can join it; at three it is

@@ -578,6 +578,14 @@ cudaError_t init_match_kernels() {
     return cudaFuncSetAttribute(knn2_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
 }
 
+cudaError_t carveout_match(int pct) {
+    cudaError_t e;
+    if ((e = set_carveout(knn2_kernel<1>, pct)) != cudaSuccess) return e;
+    if ((e = set_carveout(knn2_merge_kernel, pct)) != cudaSuccess) return e;
+    if ((e = set_carveout(knn2_window_kernel, pct)) != cudaSuccess) return e;
+    return set_carveout(match_compact_kernel, pct);
+}
+
 int launch_knn2(const MatchArgs& a, cudaStream_t s) {
     if (a.pairs <= 0 || a.max_q <= 0) return 0;
     const bool windowed = a.mask == nullptr && (a.radius > 0.0f || a.boxed) && a.q_xy != nullptr && a.t_xy != nullptr;

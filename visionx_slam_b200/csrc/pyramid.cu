@@ -644,6 +644,11 @@ cudaError_t init_pyramid_kernels() {
     return cudaFuncSetAttribute(resize_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
+cudaError_t carveout_pyramid(int pct) {
+    const cudaError_t e = set_carveout(resize_band_kernel<true>, pct);
+    return e != cudaSuccess ? e : set_carveout(resize_band_kernel<false>, pct);
+}
+
 // Builds levels 1.. of every frame and the reflect-101 apron of every level.  Returns launches.
 int launch_pyramid(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s, bool aprons_inline) {
     int launches = 0;

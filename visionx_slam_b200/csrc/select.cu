@@ -345,6 +345,11 @@ select_kernel(const LevelTab lt, const uint8_t* __restrict__ pyr, const uint32_t
     }
 }
 
+cudaError_t carveout_select(int pct) {
+    const cudaError_t e = set_carveout(select_kernel<256>, pct);
+    return e != cudaSuccess ? e : set_carveout(select_kernel<1024>, pct);
+}
+
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s) {
     dim3 grid(lt.batch, lt.n_levels);
     if (lt.batch < 8) {

@@ -168,6 +168,28 @@ void launch_resize_band(const uint8_t* src_plane, int sh, int spitch, size_t sfs
                         int dpitch, size_t dfstride, const uint32_t* ytab, const uint4* xw4, const uint2* xw2, int rows,
                         int n_bands, int smem, int batch, cudaStream_t s, bool write_apron = true);
 cudaError_t init_pyramid_kernels();
+// L1 / shared-memory split of the pipeline's kernels.  Left to the driver, every kernel gets the split that suits it
+// alone (FAST all shared memory, the blur none), and CTAs of kernels with different splits cannot share an SM: it has
+// to drain and be reconfigured.  In the production schedule of a chunk, where the pipeline slots overlap their
+// kernels, every kernel therefore asks for the SAME split, kSharedCarveout percent shared memory (measured: 62 %
+// 218.5 k, 68 % 219.7 k, 75 % 223.7 k, 82 % 222.1 k, 90 % 216.8 k, 100 % 215.7 k against 216.6-218.2 k frames/s
+// with the driver's choice; windowed matcher 278.3 k against 267.5 k).  Alone — serial instrumented passes, single
+// frames, per-call matching — the driver's choice stays, which is 1-6 % faster per kernel.
+// carveout_*(pct) set the preference of one file's kernels (pct < 0: the driver's default); api.cu switches on change.
+#ifndef VXORB_SHARED_CARVEOUT
+#define VXORB_SHARED_CARVEOUT 75
+#endif
+constexpr int kSharedCarveout = VXORB_SHARED_CARVEOUT;
+cudaError_t carveout_pyramid(int pct);
+cudaError_t carveout_fast(int pct);
+cudaError_t carveout_select(int pct);
+cudaError_t carveout_blur(int pct);
+cudaError_t carveout_describe(int pct);
+cudaError_t carveout_match(int pct);
+template <class K>
+inline cudaError_t set_carveout(K kernel, int pct) {
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct < 0 ? -1 : pct);
+}
 int launch_fast(const LevelTab& lt, const DeviceBuffers& db, int threshold, int border, cudaStream_t s, bool shared = false);
 int launch_select(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
 int launch_blur(const LevelTab& lt, const DeviceBuffers& db, cudaStream_t s);
