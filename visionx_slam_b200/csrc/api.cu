@@ -357,7 +357,9 @@ struct StageScope {
 // stream keep theirs.  Function attributes are per device and per process: one entry per device here.
 int apply_carveout(vxorb_handle* h, int pct) {
     static int current[64] = {0};  // 0 = never set (the library never asks for 0 %)
+    static std::mutex guard;       // handles of different host threads may share a device
     const int dev = h->p.device_id & 63;
+    std::lock_guard<std::mutex> lock(guard);
     if (current[dev] == pct) return VXORB_OK;
     cudaError_t e;
     if ((e = carveout_pyramid(pct)) != cudaSuccess || (e = carveout_fast(pct)) != cudaSuccess ||
