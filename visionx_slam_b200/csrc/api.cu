@@ -42,7 +42,7 @@ struct Workspace {
     // side stream of the slot: the blur of a chunk runs here beside FAST + select (both only read the
     // pyramid); forked after the pyramid and joined before the descriptors
     cudaStream_t side = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork0 = nullptr, ev_apron = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int batch = 0;          // frames of the chunk in flight / last processed
     bool in_flight = false;
     int* h_status = nullptr;  // pinned: status word copied back with every chunk
@@ -942,8 +942,6 @@ int vxorb_create(const vxorb_params* p, vxorb_handle** out) {
         if ((e = cudaStreamCreateWithFlags(&w.side, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "side stream");
         if ((e = cudaEventCreateWithFlags(&w.ev_fork, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
         if ((e = cudaEventCreateWithFlags(&w.ev_join, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
-        if ((e = cudaEventCreateWithFlags(&w.ev_fork0, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
-        if ((e = cudaEventCreateWithFlags(&w.ev_apron, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "event");
         if ((e = cudaHostAlloc(&w.h_status, sizeof(int) * 4, cudaHostAllocDefault)) != cudaSuccess) return bail(e, "pinned");
         w.h_status[0] = 0;
         if ((e = cudaHostAlloc(&w.h_counts, sizeof(int) * 2 * (size_t)p->max_batch, cudaHostAllocDefault)) != cudaSuccess)
@@ -969,8 +967,6 @@ void vxorb_destroy(vxorb_handle* h) {
         if (w.side) cudaStreamDestroy(w.side);
         if (w.ev_fork) cudaEventDestroy(w.ev_fork);
         if (w.ev_join) cudaEventDestroy(w.ev_join);
-        if (w.ev_fork0) cudaEventDestroy(w.ev_fork0);
-        if (w.ev_apron) cudaEventDestroy(w.ev_apron);
         if (w.h_status) cudaFreeHost(w.h_status);
         if (w.h_counts) cudaFreeHost(w.h_counts);
     }
