@@ -725,7 +725,9 @@ def run_ours(args, rank, world, local_rank):
                                  "a side stream beside FAST + select; the stage table and the roofline come from a serial "
                                  "pass on one stream with events around every stage.  In the production schedule FAST's "
                                  "persistent grid takes 3 CTAs per SM, leaving room for the other slots' kernels (8 % slower "
-                                 "alone, 2 % faster pipelined); alone, as in the serial pass, it takes all 5"},
+                                 "alone, 2 % faster pipelined) and every kernel asks for the same 75 % shared-memory split so that "
+                                 "CTAs of different kernels can share an SM (+3 %); alone, as in the serial pass, FAST takes "
+                                 "all 5 and every kernel the driver's own split"},
             "roofline": roofline, "stages": table, "cpu_baseline": cpu, "clocks": clocks,
             "per_call": per_call, "c3": c3, "c4": c4,
         }
